@@ -1,0 +1,148 @@
+"""Drop-in mirror of the reference's attack.py (same names, arguments and error behaviour), with the
+per-iteration work done by libadvb200 on the B200.
+
+    reference                       here
+    attack.py:10-17  normalize_batch    normalize_batch (torch; the native model fuses it into conv1)
+    attack.py:20-34  fgsm_attack        fgsm_attack      -> advb200_input_grad + advb200_linf_step_f32
+    attack.py:37-65  pgd_linf_attack    pgd_linf_attack  -> advb200_random_start_f32 + steps x (grad, step)
+    attack.py:72-75  CWResult           CWResult
+    attack.py:78-140 cw_l2_attack       cw_l2_attack     -> advb200_cw_init/step/finalize_f32
+
+`model` is the torchvision ResNet-50 nn.Module the reference passes (packed once, cached) or a
+NativeResNet50.  Inputs are never mutated; results are new detached tensors on x's device.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from . import _lib
+from .model import native_model
+
+
+def normalize_batch(x: torch.Tensor, mean: torch.Tensor, std: torch.Tensor) -> torch.Tensor:
+    if mean.ndim != 1 or std.ndim != 1:
+        raise ValueError("mean/std must be 1D tensors with shape [C]")
+    if x.ndim != 4:
+        raise ValueError("x must be a 4D tensor with shape [N, C, H, W]")
+    mean = mean.to(device=x.device, dtype=x.dtype).view(1, -1, 1, 1)
+    std = std.to(device=x.device, dtype=x.dtype).view(1, -1, 1, 1)
+    return (x - mean) / std
+
+
+def _check_common(x, mean, std):
+    if mean.ndim != 1 or std.ndim != 1:
+        raise ValueError("mean/std must be 1D tensors with shape [C]")
+    if x.ndim != 4:
+        raise ValueError("x must be a 4D tensor with shape [N, C, H, W]")
+
+
+def _linf_step(x_adv, x_orig, grad, alpha, eps, project):
+    lib = _lib.load()
+    rc = lib.advb200_linf_step_f32(_lib.ptr(x_adv), _lib.ptr(x_orig), _lib.ptr(grad), float(alpha), float(eps),
+                                   x_adv.numel(), int(project), _lib.stream_ptr())
+    _lib.check(rc, "advb200_linf_step_f32")
+
+
+def fgsm_attack(model, x: torch.Tensor, y_true: torch.Tensor, *, eps: float, mean: torch.Tensor,
+                std: torch.Tensor, inv_n_global: Optional[float] = None) -> torch.Tensor:
+    _check_common(x, mean, std)
+    nm = native_model(model)
+    with torch.cuda.device(x.device):
+        x_adv = x.detach().to(torch.float32).clone().contiguous()
+        if x_adv.shape[0] == 0:
+            return x_adv
+        g = nm.input_grad(x_adv, mean, std, y_true, loss="ce", inv_n_global=inv_n_global)["grad"]
+        _linf_step(x_adv, None, g, eps, eps, project=False)
+    return x_adv
+
+
+def pgd_linf_attack(model, x: torch.Tensor, y_true: torch.Tensor, *, eps: float, alpha: float, steps: int,
+                    mean: torch.Tensor, std: torch.Tensor, random_start: bool = True,
+                    inv_n_global: Optional[float] = None) -> torch.Tensor:
+    _check_common(x, mean, std)
+    nm = native_model(model)
+    lib = _lib.load()
+    with torch.cuda.device(x.device):
+        x_orig = x.detach().to(torch.float32).contiguous()
+        x_adv = torch.empty_like(x_orig)
+        if x_orig.shape[0] == 0:
+            return x_adv
+        if random_start:
+            noise = torch.empty_like(x_orig).uniform_(-eps, eps)      # attack.py:51, torch's generator
+            rc = lib.advb200_random_start_f32(_lib.ptr(x_adv), _lib.ptr(x_orig), _lib.ptr(noise),
+                                              x_adv.numel(), _lib.stream_ptr())
+            _lib.check(rc, "advb200_random_start_f32")
+        else:
+            x_adv.copy_(x_orig)
+        grad = torch.empty_like(x_orig)
+        for _ in range(int(steps)):
+            nm.input_grad(x_adv, mean, std, y_true, loss="ce", inv_n_global=inv_n_global, grad_out=grad)
+            _linf_step(x_adv, x_orig, grad, alpha, eps, project=True)
+    return x_adv
+
+
+@dataclass(frozen=True)
+class CWResult:
+    x_adv: torch.Tensor
+    success: torch.Tensor
+
+
+def cw_l2_attack(model, x: torch.Tensor, y_true: torch.Tensor, *, mean: torch.Tensor, std: torch.Tensor,
+                 c: float = 1.0, kappa: float = 0.0, steps: int = 1000, lr: float = 1e-2,
+                 targeted: bool = False, y_target: Optional[torch.Tensor] = None,
+                 return_l2: bool = False):
+    if targeted and y_target is None:
+        raise ValueError("y_target must be provided when targeted=True")
+    _check_common(x, mean, std)
+    nm = native_model(model)
+    lib = _lib.load()
+    beta1, beta2, adam_eps = 0.9, 0.999, 1e-8          # torch.optim.Adam defaults (attack.py:101)
+    with torch.cuda.device(x.device):
+        xin = x.detach().to(torch.float32).contiguous()
+        n = xin.shape[0]
+        dev = xin.device
+        if n == 0:
+            return CWResult(x_adv=xin.clone(), success=torch.zeros((0,), dtype=torch.bool, device=dev))
+        per = xin[0].numel()
+        parts = int(lib.advb200_cw_parts(per))
+        x0, w, m, v, x_adv, best_adv = (torch.empty_like(xin) for _ in range(6))
+        best_l2 = torch.empty((n,), dtype=torch.float32, device=dev)
+        best_success = torch.empty((n,), dtype=torch.uint8, device=dev)
+        success = torch.empty((n,), dtype=torch.uint8, device=dev)
+        l2_now = torch.empty((n,), dtype=torch.float32, device=dev)
+        # [N*parts floats] + N flag bytes (the step kernel keeps its `improved` flags in the tail)
+        pa = torch.empty((n * parts + (n + 3) // 4 + 1,), dtype=torch.float32, device=dev)
+        pb = torch.empty_like(pa)
+        grad = torch.empty_like(xin)
+        rc = lib.advb200_cw_init_f32(_lib.ptr(xin), _lib.ptr(x0), _lib.ptr(w), _lib.ptr(m), _lib.ptr(v),
+                                     _lib.ptr(x_adv), _lib.ptr(best_adv), _lib.ptr(best_l2),
+                                     _lib.ptr(best_success), _lib.ptr(pa), n, per, _lib.stream_ptr())
+        _lib.check(rc, "advb200_cw_init_f32")
+        y_cmp = y_target if targeted else y_true
+        loss = "cw_targeted" if targeted else "cw"
+        for t in range(1, int(steps) + 1):
+            # forward + margin-loss input gradient at the current iterate; success flags of attack.py:121,124
+            nm.input_grad(x_adv, mean, std, y_cmp, loss=loss, c=c, kappa=kappa, grad_out=grad,
+                          success_out=success)
+            # Adam scalars in double on the host, like torch's single-tensor path
+            step_size = lr / (1.0 - beta1 ** t)
+            bc2_sqrt = math.sqrt(1.0 - beta2 ** t)
+            rc = lib.advb200_cw_step_f32(_lib.ptr(w), _lib.ptr(m), _lib.ptr(v), _lib.ptr(x0), _lib.ptr(grad),
+                                         _lib.ptr(x_adv), _lib.ptr(best_adv), _lib.ptr(best_l2),
+                                         _lib.ptr(best_success), _lib.ptr(success), _lib.ptr(pa), _lib.ptr(pb),
+                                         _lib.ptr(l2_now), n, per, step_size, bc2_sqrt, beta1, beta2, adam_eps,
+                                         _lib.stream_ptr())
+            _lib.check(rc, "advb200_cw_step_f32")
+            pa, pb = pb, pa
+        final = torch.empty_like(xin)
+        rc = lib.advb200_cw_finalize_f32(_lib.ptr(x_adv), _lib.ptr(best_adv), _lib.ptr(best_success),
+                                         _lib.ptr(final), n, per, _lib.stream_ptr())
+        _lib.check(rc, "advb200_cw_finalize_f32")
+    res = CWResult(x_adv=final, success=best_success.to(torch.bool))
+    if return_l2:
+        return res, best_l2
+    return res

@@ -1,0 +1,226 @@
+"""Native ResNet-50 handle: packs a torchvision-shaped ResNet-50 into libadvb200 and exposes the two
+calls the attack loop needs — logits (+ detector score) and the input gradient.
+
+Replaces `model(normalize_batch(x, mean, std))` (attack.py:30,57,111), the autograd input gradient
+(attack.py:32,59,130) and the layer3 partial forward (defense_experiments.py:232-238).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import weakref
+from ctypes import c_float, c_void_p
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+_DEFAULT_PRECISION = os.environ.get("ADVB200_PRECISION", "bf16")
+_MAX_CHUNK = int(os.environ.get("ADVB200_MAX_CHUNK", "256"))
+
+
+def set_default_precision(p: str) -> None:
+    global _DEFAULT_PRECISION
+    if p not in ("bf16", "fp32"):
+        raise ValueError("precision must be 'bf16' or 'fp32'")
+    _DEFAULT_PRECISION = p
+
+
+def get_default_precision() -> str:
+    return _DEFAULT_PRECISION
+
+
+def _conv_bn_pairs(module):
+    """(conv, bn) pairs of a torchvision ResNet-50 in libadvb200's canonical order."""
+    try:
+        pairs = [(module.conv1, module.bn1)]
+        counts = []
+        for layer in (module.layer1, module.layer2, module.layer3, module.layer4):
+            counts.append(len(layer))
+            for blk in layer:
+                pairs += [(blk.conv1, blk.bn1), (blk.conv2, blk.bn2), (blk.conv3, blk.bn3)]
+                if blk.downsample is not None:
+                    pairs.append((blk.downsample[0], blk.downsample[1]))
+        fc = module.fc
+    except AttributeError as e:  # not a ResNet-shaped module
+        raise TypeError("advb200 accelerates torchvision ResNet-50 only (no generic-model fallback)") from e
+    shapes_ok = (counts == [3, 4, 6, 3] and len(pairs) == _lib.NUM_CONVS
+                 and tuple(module.conv1.weight.shape) == (64, 3, 7, 7)
+                 and tuple(fc.weight.shape) == (1000, 2048)
+                 and module.layer1[0].conv2.stride == (1, 1) and module.layer2[0].conv2.stride == (2, 2))
+    if not shapes_ok:
+        raise TypeError("advb200 accelerates torchvision ResNet-50 (v1.5, 1000 classes) only")
+    return pairs, fc
+
+
+class NativeResNet50:
+    """Device-resident packed ResNet-50 (eval mode, frozen weights)."""
+
+    def __init__(self, module: torch.nn.Module, precision: Optional[str] = None, device=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("advb200 needs a CUDA device (B200); there is no CPU fallback")
+        self.lib = _lib.load()
+        self.precision = precision or _DEFAULT_PRECISION
+        if self.precision not in ("bf16", "fp32"):
+            raise ValueError("precision must be 'bf16' or 'fp32'")
+        if module.training:
+            raise ValueError("the model must be in eval() mode (BatchNorm uses running statistics)")
+        dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        if dev.type != "cuda":
+            raise RuntimeError("advb200 needs a CUDA device (B200); there is no CPU fallback")
+        if dev.index is None:
+            dev = torch.device("cuda", torch.cuda.current_device())
+        self.device = dev
+        pairs, fc = _conv_bn_pairs(module)
+        keep = []
+
+        def to_dev(t):
+            t = t.detach().to(device=self.device, dtype=torch.float32).contiguous()
+            keep.append(t)
+            return t
+
+        arr = lambda ts: (c_void_p * len(ts))(*[t.data_ptr() for t in ts])
+        with torch.cuda.device(self.device):
+            ws = [to_dev(c.weight) for c, _ in pairs]
+            ga = [to_dev(b.weight) for _, b in pairs]
+            be = [to_dev(b.bias) for _, b in pairs]
+            mu = [to_dev(b.running_mean) for _, b in pairs]
+            va = [to_dev(b.running_var) for _, b in pairs]
+            eps = (c_float * len(pairs))(*[float(b.eps) for _, b in pairs])
+            fcw, fcb = to_dev(fc.weight), to_dev(fc.bias)
+            handle = c_void_p()
+            rc = self.lib.advb200_model_create(arr(ws), arr(ga), arr(be), arr(mu), arr(va), eps,
+                                               _lib.ptr(fcw), _lib.ptr(fcb),
+                                               _lib.PREC_BF16 if self.precision == "bf16" else _lib.PREC_FP32,
+                                               _lib.stream_ptr(), ctypes.byref(handle))
+            _lib.check(rc, "advb200_model_create")
+        self.handle = handle
+        self._ws = {}   # n -> (raw tensor, aligned ptr, bytes)
+        self._finalizer = weakref.finalize(self, self.lib.advb200_model_destroy, handle)
+        self.max_chunk = _MAX_CHUNK
+
+    # -- workspace ---------------------------------------------------------------------------
+    def _workspace(self, n: int):
+        ent = self._ws.get(n)
+        if ent is None:
+            nbytes = int(self.lib.advb200_workspace_bytes(self.handle, n))
+            if nbytes <= 0:
+                raise RuntimeError("advb200_workspace_bytes failed")
+            # keep at most two workspaces alive (full chunk + tail chunk) to bound memory
+            while len(self._ws) >= 2:
+                self._ws.pop(next(iter(self._ws)))
+            raw = torch.empty(nbytes + 1024, dtype=torch.uint8, device=self.device)
+            base = (raw.data_ptr() + 1023) // 1024 * 1024
+            ent = (raw, base, nbytes)
+            self._ws[n] = ent
+        return ent
+
+    @staticmethod
+    def _vec3(t: torch.Tensor, device) -> torch.Tensor:
+        if t.ndim != 1:
+            raise ValueError("mean/std must be 1D tensors with shape [C]")
+        if t.numel() != 3:
+            raise ValueError("mean/std must have 3 entries for an RGB ResNet-50")
+        return t.detach().to(device=device, dtype=torch.float32).contiguous()
+
+    def _check_x(self, x: torch.Tensor) -> torch.Tensor:
+        if x.ndim != 4:
+            raise ValueError("x must be a 4D tensor with shape [N, C, H, W]")
+        if tuple(x.shape[1:]) != (3, 224, 224):
+            raise ValueError("advb200 handles [N,3,224,224] inputs (the reference's CenterCrop(224) pipeline)")
+        if not x.is_cuda:
+            raise ValueError("x must live on the CUDA device of the native model (no CPU fallback)")
+        return x.detach().to(dtype=torch.float32).contiguous()
+
+    # -- forward -----------------------------------------------------------------------------
+    def forward(self, x, mean, std, *, want_logits=True, want_preds=False, want_score=False,
+                stop_at_layer3=False):
+        """Returns dict with any of 'logits' [N,1000], 'preds' [N] int64, 'score' [N]."""
+        x = self._check_x(x)
+        mean, std = self._vec3(mean, x.device), self._vec3(std, x.device)
+        n = x.shape[0]
+        out = {}
+        if want_logits and not stop_at_layer3:
+            out["logits"] = torch.empty((n, 1000), dtype=torch.float32, device=x.device)
+        if want_preds and not stop_at_layer3:
+            out["preds"] = torch.empty((n,), dtype=torch.int64, device=x.device)
+        if want_score:
+            out["score"] = torch.empty((n,), dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            for lo in range(0, n, self.max_chunk):
+                hi = min(n, lo + self.max_chunk)
+                _, ws, nbytes = self._workspace(hi - lo)
+                sl = lambda k: _lib.ptr(out[k][lo:hi]) if k in out else None
+                rc = self.lib.advb200_forward(self.handle, _lib.ptr(x[lo:hi]), _lib.ptr(mean), _lib.ptr(std),
+                                              hi - lo, sl("logits"), sl("preds"), int(bool(stop_at_layer3)),
+                                              sl("score"), c_void_p(ws), nbytes, _lib.stream_ptr())
+                _lib.check(rc, "advb200_forward")
+        return out
+
+    # -- forward + input gradient ------------------------------------------------------------
+    def input_grad(self, x, mean, std, y_cmp, *, loss="ce", c=1.0, kappa=0.0, inv_n_global=None,
+                   grad_out=None, want_logits=False, want_preds=False, want_loss=False, want_success=False,
+                   success_out=None, preds_out=None, loss_out=None, logits_out=None):
+        x = self._check_x(x)
+        mean, std = self._vec3(mean, x.device), self._vec3(std, x.device)
+        n = x.shape[0]
+        y_cmp = y_cmp.detach().to(device=x.device, dtype=torch.int64).contiguous()
+        if y_cmp.shape != (n,):
+            raise ValueError("labels must have shape [N]")
+        kind = {"ce": _lib.LOSS_CE_MEAN, "cw": _lib.LOSS_CW_UNTGT, "cw_targeted": _lib.LOSS_CW_TGT}[loss]
+        if inv_n_global is None:
+            inv_n_global = 1.0 / n
+        grad = grad_out if grad_out is not None else torch.empty_like(x)
+        out = {"grad": grad}
+        if want_logits or logits_out is not None:
+            out["logits"] = logits_out if logits_out is not None else \
+                torch.empty((n, 1000), dtype=torch.float32, device=x.device)
+        if want_preds or preds_out is not None:
+            out["preds"] = preds_out if preds_out is not None else \
+                torch.empty((n,), dtype=torch.int64, device=x.device)
+        if want_loss or loss_out is not None:
+            out["loss"] = loss_out if loss_out is not None else \
+                torch.empty((n,), dtype=torch.float32, device=x.device)
+        if want_success or success_out is not None:
+            out["success"] = success_out if success_out is not None else \
+                torch.empty((n,), dtype=torch.uint8, device=x.device)
+        with torch.cuda.device(x.device):
+            for lo in range(0, n, self.max_chunk):
+                hi = min(n, lo + self.max_chunk)
+                _, ws, nbytes = self._workspace(hi - lo)
+                sl = lambda k: _lib.ptr(out[k][lo:hi]) if k in out else None
+                rc = self.lib.advb200_input_grad(self.handle, _lib.ptr(x[lo:hi]), _lib.ptr(mean), _lib.ptr(std),
+                                                 _lib.ptr(y_cmp[lo:hi]), hi - lo, kind, float(c), float(kappa),
+                                                 float(inv_n_global), sl("logits"), sl("preds"), sl("loss"),
+                                                 sl("success"), _lib.ptr(grad[lo:hi]), c_void_p(ws), nbytes,
+                                                 _lib.stream_ptr())
+                _lib.check(rc, "advb200_input_grad")
+        return out
+
+
+_CACHE: "weakref.WeakKeyDictionary[torch.nn.Module, dict]" = weakref.WeakKeyDictionary()
+
+
+def native_model(model, precision: Optional[str] = None) -> NativeResNet50:
+    """NativeResNet50 for `model` (an nn.Module or already a NativeResNet50), cached per module+precision.
+
+    The packed copy snapshots the module's weights at first use; the attack path treats the
+    classifier as frozen (no weight gradients)."""
+    if isinstance(model, NativeResNet50):
+        return model
+    if not isinstance(model, torch.nn.Module):
+        raise TypeError("model must be a torchvision ResNet-50 nn.Module or a NativeResNet50")
+    precision = precision or _DEFAULT_PRECISION
+    per = _CACHE.setdefault(model, {})
+    nm = per.get(precision)
+    if nm is None:
+        try:
+            dev = next(model.parameters()).device
+        except StopIteration:
+            raise TypeError("model has no parameters")
+        if dev.type != "cuda":
+            raise RuntimeError("the model must be on a CUDA device: advb200 has no CPU fallback")
+        nm = NativeResNet50(model, precision=precision, device=dev)
+        per[precision] = nm
+    return nm

@@ -1,0 +1,803 @@
+// ResNet-50 (torchvision v1.5, eval) forward + input-only backward engine behind the C ABI.
+//
+// The network is compiled once per (batch, workspace) into flat lists of kernel launches:
+// bf16 mode -> tcgen05 implicit-GEMM ops (tc_conv.cu) with pre-encoded TMA tensor maps,
+// fp32 mode -> CUDA-core implicit-GEMM ops (simt_conv.cu).  Activations are NHWC in a
+// caller-owned workspace; nothing is allocated or synchronised on the hot path.
+//
+// Reference: model(normalize_batch(x)) attack.py:30,57,111; autograd.grad(loss, x) attack.py:32,59;
+// loss.backward() attack.py:130 (without its unused weight gradients); _layer3_features
+// defense_experiments.py:221-257.
+#include <vector>
+
+#include "layers.cuh"
+#include "simt_conv.cuh"
+#include "tc_conv.cuh"
+
+namespace advb200 {
+
+thread_local std::string g_last_error;
+void set_error(const std::string& msg) { g_last_error = msg; }
+std::atomic<long long> g_launches{0};
+
+namespace {
+
+constexpr int kImg = 224;
+constexpr int kClasses = 1000;
+constexpr int kFeat = 2048;
+
+struct Act {          // NHWC activation view
+  void* p = nullptr;
+  int n = 0, h = 0, w = 0, c = 0;
+  long long elems() const { return (long long)n * h * w * c; }
+};
+
+struct ConvW {
+  int cin = 0, cout = 0, k = 0, stride = 1;
+  float* scale = nullptr;
+  float* shift = nullptr;
+  float* f_fwd = nullptr;   // fp32 [(rs*cin+ci), co]
+  float* f_dgrad = nullptr; // fp32 [(rs*cout+co), ci]
+  bf16* b_fwd = nullptr;    // bf16 [(rs*cout+co)][ci]
+  bf16* b_dgrad = nullptr;  // bf16 [(rs*cin+ci)][co]
+};
+
+struct TcOp {
+  int bn = 0;
+  int nmaps = 0;
+  CUtensorMap a[4];
+  CUtensorMap b;
+  ConvGemmParams p;
+};
+
+struct Op {
+  enum Kind { TC, SIMT, MEMSET } kind;
+  TcOp tc;
+  SimtConvParams simt;
+  void* ms_ptr = nullptr;
+  size_t ms_bytes = 0;
+};
+
+inline int pow2_div(int v, int cap) {
+  int b = 1;
+  while (b * 2 <= cap && v % (b * 2) == 0) b *= 2;
+  return b;
+}
+inline void tile_shape(int w, int h, int& bw, int& bh, int& bn) {
+  bw = pow2_div(w, 16);
+  bh = pow2_div(h, 128 / bw < 8 ? 128 / bw : 8);
+  bn = 128 / (bw * bh);
+}
+inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+inline int pick_bn(int gemm_n, long long m_tiles) {
+  const int cands[3] = {256, 128, 64};
+  const double bonus[3] = {1.0, 0.97, 0.80};
+  int best = 64;
+  double best_score = -1;
+  for (int i = 0; i < 3; ++i) {
+    if (gemm_n % cands[i]) continue;
+    const long long tiles = m_tiles * (gemm_n / cands[i]);
+    const long long waves = (tiles + kNumSMs - 1) / kNumSMs;
+    const double eff = (double)tiles / (double)(waves * kNumSMs) * bonus[i];
+    if (eff > best_score) { best_score = eff; best = cands[i]; }
+  }
+  return best;
+}
+
+// ---- tcgen05 op construction ------------------------------------------------------------------
+// in : GEMM K side (activation for fwd, dY for dgrad); out: GEMM N side.  wpack: K-major packed
+// weights with k*k*out.c rows of in.c columns.
+int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride, bool dgrad, Act in, Act out,
+                 const float* bias, const bf16* add, const bf16* mask, int relu) {
+  const int gemm_n = out.c, gemm_k = in.c;
+  ADV_CHECK_ARG(gemm_k % 64 == 0 && gemm_n % 64 == 0, "tc conv: channels must be multiples of 64");
+  ADV_CHECK_ARG((ksize == 1 || ksize == 3) && (stride == 1 || stride == 2), "tc conv: unsupported geometry");
+  const int kk = ksize * ksize;
+
+  auto make_b = [&](CUtensorMap* m, int bn) {
+    const uint64_t dims[2] = {(uint64_t)gemm_k, (uint64_t)kk * gemm_n};
+    const uint64_t strides[1] = {(uint64_t)gemm_k * 2};
+    const uint32_t box[2] = {64, (uint32_t)bn};
+    return make_tmap_bf16(m, wpack, 2, dims, strides, box);
+  };
+  // 4-D map over an NHWC tensor or one of its stride-2 sub-lattices
+  auto make_a = [&](CUtensorMap* m, const Act& t, int sub, int ph, int pw, int bw, int bh, int bnimg) {
+    const bf16* base = reinterpret_cast<const bf16*>(t.p) + ((long long)ph * t.w + pw) * t.c;
+    const uint64_t dims[4] = {(uint64_t)t.c, (uint64_t)(t.w / sub), (uint64_t)(t.h / sub), (uint64_t)t.n};
+    const uint64_t strides[3] = {(uint64_t)t.c * 2 * sub, (uint64_t)t.w * t.c * 2 * sub,
+                                 (uint64_t)t.h * t.w * t.c * 2};
+    const uint32_t box[4] = {64, (uint32_t)bw, (uint32_t)bh, (uint32_t)bnimg};
+    return make_tmap_bf16(m, base, 4, dims, strides, box);
+  };
+
+  Op op;
+  op.kind = Op::TC;
+  TcOp& t = op.tc;
+  ConvGemmParams& p = t.p;
+  memset(&p, 0, sizeof p);
+  p.kblocks = gemm_k / 64;
+  p.bias = bias; p.add = add; p.mask = mask; p.relu = relu; p.epi = 0;
+  p.cout = gemm_n;
+  p.out = out.p;
+
+  if (ksize == 1 && stride == 1) {
+    // plain GEMM over all pixels
+    ADV_CHECK_ARG(in.n == out.n && in.h == out.h && in.w == out.w, "tc conv 1x1: shape mismatch");
+    const long long m = (long long)in.n * in.h * in.w;
+    ADV_CHECK_ARG(m < (1ll << 31), "tc conv: too many pixels");
+    p.bw = 128; p.bh = 1; p.bn = 1;
+    p.tiles_w = (int)((m + 127) / 128); p.tiles_h = 1; p.tiles_n = 1;
+    t.bn = pick_bn(gemm_n, p.tiles_w);
+    p.tiles_c = gemm_n / t.bn;
+    p.ntaps = 1;
+    p.out_w = (int)m; p.out_h = 1; p.out_n = 1;
+    p.o_sw = gemm_n; p.o_sh = 0; p.o_sn = 0;
+    const uint64_t dims[4] = {(uint64_t)gemm_k, (uint64_t)m, 1, 1};
+    const uint64_t strides[3] = {(uint64_t)gemm_k * 2, (uint64_t)gemm_k * 2 * (uint64_t)m,
+                                 (uint64_t)gemm_k * 2 * (uint64_t)m};
+    const uint32_t box[4] = {64, 128, 1, 1};
+    int rc = make_tmap_bf16(&t.a[0], in.p, 4, dims, strides, box);
+    if (rc) return rc;
+    t.nmaps = 1;
+    rc = make_b(&t.b, t.bn);
+    if (rc) return rc;
+    ops.push_back(op);
+    return ADVB200_OK;
+  }
+
+  if (!dgrad) {
+    // forward conv: tiles over the OUTPUT pixel grid
+    ADV_CHECK_ARG(out.h == in.h / stride && out.w == in.w / stride && in.n == out.n, "tc conv fwd: shape mismatch");
+    ADV_CHECK_ARG(stride == 1 || (in.h % 2 == 0 && in.w % 2 == 0), "tc conv fwd: stride 2 needs even sizes");
+    tile_shape(out.w, out.h, p.bw, p.bh, p.bn);
+    p.tiles_w = cdiv(out.w, p.bw); p.tiles_h = cdiv(out.h, p.bh); p.tiles_n = cdiv(out.n, p.bn);
+    t.bn = pick_bn(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n);
+    p.tiles_c = gemm_n / t.bn;
+    p.out_w = out.w; p.out_h = out.h; p.out_n = out.n;
+    p.o_sw = gemm_n; p.o_sh = (long long)out.w * gemm_n; p.o_sn = (long long)out.h * out.w * gemm_n;
+    int rc;
+    if (stride == 1) {
+      rc = make_a(&t.a[0], in, 1, 0, 0, p.bw, p.bh, p.bn);
+      if (rc) return rc;
+      t.nmaps = 1;
+    } else {
+      for (int ph = 0; ph < 2; ++ph)
+        for (int pw = 0; pw < 2; ++pw) {
+          rc = make_a(&t.a[ph * 2 + pw], in, 2, ph, pw, p.bw, p.bh, p.bn);
+          if (rc) return rc;
+        }
+      t.nmaps = 4;
+    }
+    p.ntaps = 0;
+    for (int r = 0; r < ksize; ++r)
+      for (int s = 0; s < ksize; ++s) {
+        const int i = p.ntaps++;
+        p.tap_brow[i] = (r * ksize + s) * gemm_n;
+        if (ksize == 1) { p.tap_map[i] = 0; p.tap_dh[i] = 0; p.tap_dw[i] = 0; }
+        else if (stride == 1) { p.tap_map[i] = 0; p.tap_dh[i] = r - 1; p.tap_dw[i] = s - 1; }
+        else {
+          // input row 2*ho + r - 1: r=0 -> odd row of ho-1, r=1 -> even row of ho, r=2 -> odd row of ho
+          const int ph = (r == 1) ? 0 : 1, pw = (s == 1) ? 0 : 1;
+          p.tap_map[i] = ph * 2 + pw;
+          p.tap_dh[i] = (r == 0) ? -1 : 0;
+          p.tap_dw[i] = (s == 0) ? -1 : 0;
+        }
+      }
+    rc = make_b(&t.b, t.bn);
+    if (rc) return rc;
+    ops.push_back(op);
+    return ADVB200_OK;
+  }
+
+  // ---- data gradient: in = dY [N,Ho,Wo,Cout], out = dX [N,H,W,Cin]
+  if (stride == 1) {
+    ADV_CHECK_ARG(out.h == in.h && out.w == in.w && in.n == out.n, "tc conv dgrad: shape mismatch");
+    tile_shape(out.w, out.h, p.bw, p.bh, p.bn);
+    p.tiles_w = cdiv(out.w, p.bw); p.tiles_h = cdiv(out.h, p.bh); p.tiles_n = cdiv(out.n, p.bn);
+    t.bn = pick_bn(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n);
+    p.tiles_c = gemm_n / t.bn;
+    p.out_w = out.w; p.out_h = out.h; p.out_n = out.n;
+    p.o_sw = gemm_n; p.o_sh = (long long)out.w * gemm_n; p.o_sn = (long long)out.h * out.w * gemm_n;
+    int rc = make_a(&t.a[0], in, 1, 0, 0, p.bw, p.bh, p.bn);
+    if (rc) return rc;
+    t.nmaps = 1;
+    p.ntaps = 0;
+    for (int r = 0; r < 3; ++r)
+      for (int s = 0; s < 3; ++s) {
+        const int i = p.ntaps++;
+        p.tap_map[i] = 0; p.tap_dh[i] = 1 - r; p.tap_dw[i] = 1 - s;   // dX[h,w] += dY[h+1-r, w+1-s] W[r,s]
+        p.tap_brow[i] = (r * 3 + s) * gemm_n;
+      }
+    rc = make_b(&t.b, t.bn);
+    if (rc) return rc;
+    ops.push_back(op);
+    return ADVB200_OK;
+  }
+
+  // stride-2 dgrad: one launch per input-pixel parity class (ph, pw); each class is a stride-1
+  // gather over dY with the subset of taps whose parity matches, written to that sub-lattice of dX.
+  ADV_CHECK_ARG(out.h == in.h * 2 && out.w == in.w * 2 && in.n == out.n, "tc conv dgrad s2: shape mismatch");
+  const int pad = (ksize == 3) ? 1 : 0;
+  for (int ph = 0; ph < 2; ++ph)
+    for (int pw = 0; pw < 2; ++pw) {
+      Op o2 = op;
+      TcOp& t2 = o2.tc;
+      ConvGemmParams& q = t2.p;
+      q.ntaps = 0;
+      for (int r = 0; r < ksize; ++r)
+        for (int s = 0; s < ksize; ++s) {
+          // 2*h2+ph = 2*ho + r - pad  ->  ho = h2 + (ph + pad - r)/2, needs (ph+pad-r) even
+          const int eh = ph + pad - r, ew = pw + pad - s;
+          if ((eh & 1) || (ew & 1)) continue;
+          const int i = q.ntaps++;
+          q.tap_map[i] = 0; q.tap_dh[i] = eh / 2; q.tap_dw[i] = ew / 2;
+          q.tap_brow[i] = (r * ksize + s) * gemm_n;
+        }
+      if (q.ntaps == 0) continue;   // 1x1/2: only the (0,0) lattice receives gradient
+      const int sw = out.w / 2, sh = out.h / 2;
+      tile_shape(sw, sh, q.bw, q.bh, q.bn);
+      q.tiles_w = cdiv(sw, q.bw); q.tiles_h = cdiv(sh, q.bh); q.tiles_n = cdiv(out.n, q.bn);
+      t2.bn = pick_bn(gemm_n, (long long)q.tiles_w * q.tiles_h * q.tiles_n);
+      q.tiles_c = gemm_n / t2.bn;
+      q.out_w = sw; q.out_h = sh; q.out_n = out.n;
+      q.o_sw = 2ll * gemm_n; q.o_sh = 2ll * out.w * gemm_n; q.o_sn = (long long)out.h * out.w * gemm_n;
+      const long long sub_off = ((long long)ph * out.w + pw) * gemm_n;
+      q.out = reinterpret_cast<bf16*>(out.p) + sub_off;
+      if (add) q.add = add + sub_off;
+      if (mask) q.mask = mask + sub_off;
+      int rc = make_a(&t2.a[0], in, 1, 0, 0, q.bw, q.bh, q.bn);
+      if (rc) return rc;
+      t2.nmaps = 1;
+      rc = make_b(&t2.b, t2.bn);
+      if (rc) return rc;
+      ops.push_back(o2);
+    }
+  return ADVB200_OK;
+}
+
+int build_simt_op(std::vector<Op>& ops, const float* wm, int ksize, int stride, bool dgrad, Act in, Act out,
+                  const float* bias, const float* add, const float* mask, int relu, int pad = -1) {
+  Op op;
+  op.kind = Op::SIMT;
+  SimtConvParams& s = op.simt;
+  s.in = reinterpret_cast<const float*>(in.p); s.wm = wm; s.out = reinterpret_cast<float*>(out.p);
+  s.bias = bias; s.add = add; s.mask = mask;
+  s.n = in.n; s.hi = in.h; s.wi = in.w; s.ci = in.c; s.ho = out.h; s.wo = out.w; s.co = out.c;
+  s.kh = s.kw = ksize; s.stride = stride; s.pad = pad >= 0 ? pad : (ksize - 1) / 2;
+  s.relu = relu; s.dgrad = dgrad ? 1 : 0;
+  ops.push_back(op);
+  return ADVB200_OK;
+}
+
+int run_ops(const std::vector<Op>& ops, cudaStream_t st) {
+  for (const Op& op : ops) {
+    int rc = ADVB200_OK;
+    switch (op.kind) {
+      case Op::TC: rc = launch_conv_gemm(op.tc.bn, op.tc.a, op.tc.nmaps, op.tc.b, op.tc.p, st); break;
+      case Op::SIMT: rc = launch_simt_conv(op.simt, st); break;
+      case Op::MEMSET: {
+        cudaError_t e = cudaMemsetAsync(op.ms_ptr, 0, op.ms_bytes, st);
+        if (e != cudaSuccess) rc = fail(ADVB200_ERR_CUDA, std::string("memset: ") + cudaGetErrorString(e));
+        break;
+      }
+    }
+    if (rc) return rc;
+  }
+  return ADVB200_OK;
+}
+
+struct BlockSpec { int layer, idx, cin, width, stride, hin; bool down; int conv_base; };
+
+}  // namespace
+}  // namespace advb200
+
+using namespace advb200;
+
+struct advb200_model {
+  int precision = ADVB200_PREC_BF16;
+  int device = 0;
+  ConvW conv[ADVB200_NUM_CONVS];
+  std::vector<BlockSpec> blocks;
+  float* fc_w = nullptr;    // [1000, 2048] (dgrad matrix)
+  float* fc_wt = nullptr;   // [2048, 1000] (forward matrix)
+  float* fc_b = nullptr;
+  std::vector<void*> owned;
+
+  // ---- plan (per batch size + workspace) ----
+  int plan_n = -1;
+  void* plan_ws = nullptr;
+  size_t esz = 2;
+  // tensors
+  Act t_in, c1, p1, l3out, l4out;
+  uint8_t* pool_idx = nullptr;
+  float *feat = nullptr, *logits = nullptr, *dlogits = nullptr, *dfeat = nullptr;
+  void* g_final = nullptr;      // gradient w.r.t. p1 lives here after the body backward
+  void* g_c1 = nullptr;
+  void* g_top = nullptr;        // gradient w.r.t. layer4 output (masked) is written here
+  float* g_img_nhwc = nullptr;  // fp32 mode only
+  std::vector<Op> ops_conv1, ops_l123, ops_l4, ops_bwd, ops_conv1_bwd;
+};
+
+namespace advb200 {
+namespace {
+
+struct Bump {
+  uint8_t* base; size_t off = 0;
+  explicit Bump(void* b) : base(reinterpret_cast<uint8_t*>(b)) {}
+  void* take(size_t bytes) {
+    void* p = base ? base + off : nullptr;
+    off += (bytes + 1023) & ~size_t(1023);
+    return p;
+  }
+};
+
+void make_blocks(advb200_model* m) {
+  const int nblk[4] = {3, 4, 6, 3}, width[4] = {64, 128, 256, 512}, strd[4] = {1, 2, 2, 2};
+  int cin = 64, h = 56, ci = 1;
+  for (int l = 0; l < 4; ++l)
+    for (int b = 0; b < nblk[l]; ++b) {
+      BlockSpec s;
+      s.layer = l; s.idx = b; s.cin = cin; s.width = width[l]; s.stride = (b == 0) ? strd[l] : 1;
+      s.hin = h; s.down = (b == 0); s.conv_base = ci;
+      m->blocks.push_back(s);
+      ci += s.down ? 4 : 3;
+      cin = width[l] * 4;
+      h /= s.stride;
+    }
+}
+
+// Lays out the workspace and (when ws != null) builds the launch lists.  Returns bytes needed.
+int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
+  const bool tc = m->precision == ADVB200_PREC_BF16;
+  const size_t esz = tc ? 2 : 4;
+  m->esz = esz;
+  Bump bump(ws);
+  const bool build = ws != nullptr;
+  int rc = ADVB200_OK;
+  auto act = [&](int h, int w, int c) {
+    Act a; a.n = n; a.h = h; a.w = w; a.c = c;
+    a.p = bump.take((size_t)a.elems() * esz);
+    return a;
+  };
+  if (build) {
+    m->ops_conv1.clear(); m->ops_l123.clear(); m->ops_l4.clear(); m->ops_bwd.clear(); m->ops_conv1_bwd.clear();
+  }
+
+  // ---- stem
+  if (tc) { m->t_in.n = n; m->t_in.h = 115; m->t_in.w = 112; m->t_in.c = 64;
+            m->t_in.p = bump.take((size_t)m->t_in.elems() * 2); }
+  else m->t_in = act(kImg, kImg, 3);
+  m->c1 = act(112, 112, 64);
+  m->pool_idx = reinterpret_cast<uint8_t*>(bump.take((size_t)n * 56 * 56 * 64));
+  m->p1 = act(56, 56, 64);
+
+  // gradient buffers (4 rotating, each large enough for the biggest gradient tensor)
+  const size_t gmax = (size_t)n * 112 * 112 * 64 * esz;
+  void* gbuf[4];
+  for (int i = 0; i < 4; ++i) gbuf[i] = bump.take(gmax);
+  bool gbusy[4] = {false, false, false, false};
+  auto gacquire = [&]() { for (int i = 0; i < 4; ++i) if (!gbusy[i]) { gbusy[i] = true; return i; } return -1; };
+
+  m->feat = reinterpret_cast<float*>(bump.take((size_t)n * kFeat * 4));
+  m->logits = reinterpret_cast<float*>(bump.take((size_t)n * kClasses * 4));
+  m->dlogits = reinterpret_cast<float*>(bump.take((size_t)n * kClasses * 4));
+  m->dfeat = reinterpret_cast<float*>(bump.take((size_t)n * kFeat * 4));
+  m->g_img_nhwc = tc ? nullptr : reinterpret_cast<float*>(bump.take((size_t)n * kImg * kImg * 3 * 4));
+
+  // ---- conv1 forward
+  const ConvW& w0 = m->conv[0];
+  if (build) {
+    if (tc) {
+      Op op; op.kind = Op::TC;
+      TcOp& t = op.tc; ConvGemmParams& p = t.p;
+      memset(&p, 0, sizeof p);
+      p.bw = 16; p.bh = 8; p.bn = 1;
+      p.tiles_w = 7; p.tiles_h = 14; p.tiles_n = n; p.tiles_c = 1;
+      t.bn = 64;
+      p.ntaps = 4; p.kblocks = 1;
+      for (int i = 0; i < 4; ++i) { p.tap_map[i] = 0; p.tap_dw[i] = 0; p.tap_dh[i] = i; p.tap_brow[i] = i * 64; }
+      p.out_w = 112; p.out_h = 112; p.out_n = n; p.cout = 64;
+      p.o_sw = 64; p.o_sh = 112 * 64; p.o_sn = 112ll * 112 * 64;
+      p.out = m->c1.p; p.bias = w0.shift; p.relu = 1; p.epi = 0;
+      const uint64_t dims[4] = {64, 112, 115, (uint64_t)n};
+      const uint64_t strides[3] = {128, 128ull * 112, 128ull * 112 * 115};
+      const uint32_t box[4] = {64, 16, 8, 1};
+      rc = make_tmap_bf16(&t.a[0], m->t_in.p, 4, dims, strides, box);
+      t.nmaps = 1;
+      const uint64_t bd[2] = {64, 256};
+      const uint64_t bs[1] = {128};
+      const uint32_t bb[2] = {64, 64};
+      if (!rc) rc = make_tmap_bf16(&t.b, w0.b_fwd, 2, bd, bs, bb);
+      m->ops_conv1.push_back(op);
+    } else {
+      rc = build_simt_op(m->ops_conv1, w0.f_fwd, 7, 2, false, m->t_in, m->c1, w0.shift, nullptr, nullptr, 1, 3);
+    }
+  }
+
+  // ---- residual stages: forward ops, and the tensors the backward pass needs
+  struct BlkT { Act x, a, b, out, idn; };
+  std::vector<BlkT> bt(m->blocks.size());
+  Act x = m->p1;
+  for (size_t bi = 0; bi < m->blocks.size() && !rc; ++bi) {
+    const BlockSpec& s = m->blocks[bi];
+    const int hout = s.hin / s.stride;
+    BlkT& t = bt[bi];
+    t.x = x;
+    t.a = act(s.hin, s.hin, s.width);
+    t.b = act(hout, hout, s.width);
+    t.out = act(hout, hout, s.width * 4);
+    if (s.down) t.idn = act(hout, hout, s.width * 4);
+    if (build) {
+      std::vector<Op>& ops = (s.layer < 3) ? m->ops_l123 : m->ops_l4;
+      const ConvW& c1 = m->conv[s.conv_base], &c2 = m->conv[s.conv_base + 1], &c3 = m->conv[s.conv_base + 2];
+      if (tc) {
+        rc = build_tc_ops(ops, c1.b_fwd, 1, 1, false, t.x, t.a, c1.shift, nullptr, nullptr, 1);
+        if (!rc) rc = build_tc_ops(ops, c2.b_fwd, 3, s.stride, false, t.a, t.b, c2.shift, nullptr, nullptr, 1);
+        const bf16* res = reinterpret_cast<const bf16*>(t.x.p);
+        if (!rc && s.down) {
+          const ConvW& cd = m->conv[s.conv_base + 3];
+          rc = build_tc_ops(ops, cd.b_fwd, 1, s.stride, false, t.x, t.idn, cd.shift, nullptr, nullptr, 0);
+          res = reinterpret_cast<const bf16*>(t.idn.p);
+        }
+        if (!rc) rc = build_tc_ops(ops, c3.b_fwd, 1, 1, false, t.b, t.out, c3.shift, res, nullptr, 1);
+      } else {
+        rc = build_simt_op(ops, c1.f_fwd, 1, 1, false, t.x, t.a, c1.shift, nullptr, nullptr, 1);
+        if (!rc) rc = build_simt_op(ops, c2.f_fwd, 3, s.stride, false, t.a, t.b, c2.shift, nullptr, nullptr, 1);
+        const float* res = reinterpret_cast<const float*>(t.x.p);
+        if (!rc && s.down) {
+          const ConvW& cd = m->conv[s.conv_base + 3];
+          rc = build_simt_op(ops, cd.f_fwd, 1, s.stride, false, t.x, t.idn, cd.shift, nullptr, nullptr, 0);
+          res = reinterpret_cast<const float*>(t.idn.p);
+        }
+        if (!rc) rc = build_simt_op(ops, c3.f_fwd, 1, 1, false, t.b, t.out, c3.shift, res, nullptr, 1);
+      }
+    }
+    x = t.out;
+    if (s.layer == 2 && s.idx == 5) m->l3out = t.out;
+  }
+  m->l4out = x;
+
+  // ---- backward through the residual stages (reverse order)
+  // g_sum = gradient w.r.t. the block output, already gated by the output ReLU
+  int cur = gacquire();               // holds g_sum of the last block (written by avgpool_bwd)
+  m->g_top = gbuf[cur];
+  for (int bi = (int)m->blocks.size() - 1; bi >= 0 && !rc; --bi) {
+    const BlockSpec& s = m->blocks[bi];
+    const BlkT& t = bt[bi];
+    const ConvW& c1 = m->conv[s.conv_base], &c2 = m->conv[s.conv_base + 1], &c3 = m->conv[s.conv_base + 2];
+    Act g_sum = t.out; g_sum.p = gbuf[cur];
+    const int ib = gacquire(); Act g_b = t.b; g_b.p = gbuf[ib];
+    const int ia = gacquire(); Act g_a = t.a; g_a.p = gbuf[ia];
+    const bool first = bi == 0;   // block input is the max-pool output: its ReLU is handled there
+    int nxt;
+    if (build) {
+      if (tc) {
+        typedef const bf16* B;
+        rc = build_tc_ops(m->ops_bwd, c3.b_dgrad, 1, 1, true, g_sum, g_b, nullptr, nullptr, (B)t.b.p, 0);
+        if (!rc) rc = build_tc_ops(m->ops_bwd, c2.b_dgrad, 3, s.stride, true, g_b, g_a, nullptr, nullptr, (B)t.a.p, 0);
+      } else {
+        typedef const float* F;
+        rc = build_simt_op(m->ops_bwd, c3.f_dgrad, 1, 1, true, g_sum, g_b, nullptr, nullptr, (F)t.b.p, 0);
+        if (!rc) rc = build_simt_op(m->ops_bwd, c2.f_dgrad, 3, s.stride, true, g_b, g_a, nullptr, nullptr, (F)t.a.p, 0);
+      }
+    }
+    gbusy[ib] = false;                                   // g_b is dead after conv2's dgrad
+    Act g_x = t.x;
+    if (s.down) {
+      const ConvW& cd = m->conv[s.conv_base + 3];
+      const int it = gacquire(); Act g_t = t.x; g_t.p = gbuf[it];      // downsample-branch gradient
+      if (build && !rc) {
+        if (tc) {
+          if (s.stride == 2) {
+            Op ms; ms.kind = Op::MEMSET; ms.ms_ptr = g_t.p; ms.ms_bytes = (size_t)g_t.elems() * esz;
+            m->ops_bwd.push_back(ms);
+          }
+          rc = build_tc_ops(m->ops_bwd, cd.b_dgrad, 1, s.stride, true, g_sum, g_t, nullptr, nullptr, nullptr, 0);
+        } else {
+          rc = build_simt_op(m->ops_bwd, cd.f_dgrad, 1, s.stride, true, g_sum, g_t, nullptr, nullptr, nullptr, 0);
+        }
+      }
+      gbusy[cur] = false;                                // g_sum consumed by both branches
+      nxt = gacquire(); g_x.p = gbuf[nxt];
+      if (build && !rc) {
+        if (tc) rc = build_tc_ops(m->ops_bwd, c1.b_dgrad, 1, 1, true, g_a, g_x, nullptr, (const bf16*)g_t.p,
+                                  first ? nullptr : (const bf16*)t.x.p, 0);
+        else rc = build_simt_op(m->ops_bwd, c1.f_dgrad, 1, 1, true, g_a, g_x, nullptr, (const float*)g_t.p,
+                                first ? nullptr : (const float*)t.x.p, 0);
+      }
+      gbusy[it] = false;
+    } else {
+      nxt = gacquire(); g_x.p = gbuf[nxt];
+      if (build && !rc) {
+        if (tc) rc = build_tc_ops(m->ops_bwd, c1.b_dgrad, 1, 1, true, g_a, g_x, nullptr, (const bf16*)g_sum.p,
+                                  (const bf16*)t.x.p, 0);
+        else rc = build_simt_op(m->ops_bwd, c1.f_dgrad, 1, 1, true, g_a, g_x, nullptr, (const float*)g_sum.p,
+                                (const float*)t.x.p, 0);
+      }
+      gbusy[cur] = false;
+    }
+    gbusy[ia] = false;
+    cur = nxt;
+  }
+  m->g_final = gbuf[cur];
+  // gradient w.r.t. conv1's (post-ReLU) output goes to another buffer
+  {
+    int ic = -1;
+    for (int i = 0; i < 4; ++i) if (i != cur) { ic = i; break; }
+    m->g_c1 = gbuf[ic];
+  }
+
+  // ---- conv1 input gradient
+  if (build && !rc) {
+    if (tc) {
+      Op op; op.kind = Op::TC;
+      TcOp& t = op.tc; ConvGemmParams& p = t.p;
+      memset(&p, 0, sizeof p);
+      p.bw = 16; p.bh = 8; p.bn = 1;
+      p.tiles_w = 7; p.tiles_h = 14; p.tiles_n = n; p.tiles_c = 1;
+      t.bn = 16;
+      p.ntaps = 16; p.kblocks = 1;
+      for (int tt = 0; tt < 4; ++tt)
+        for (int u = 0; u < 4; ++u) {
+          const int i = tt * 4 + u;
+          p.tap_map[i] = 0; p.tap_dh[i] = 2 - tt; p.tap_dw[i] = 2 - u; p.tap_brow[i] = i * 16;
+        }
+      p.out_w = 112; p.out_h = 112; p.out_n = n; p.cout = 16;
+      p.epi = 1; p.img_h = kImg; p.img_w = kImg;
+      p.out = nullptr;   // patched per call (grad_x_out)
+      const uint64_t dims[4] = {64, 112, 112, (uint64_t)n};
+      const uint64_t strides[3] = {128, 128ull * 112, 128ull * 112 * 112};
+      const uint32_t box[4] = {64, 16, 8, 1};
+      rc = make_tmap_bf16(&t.a[0], m->g_c1, 4, dims, strides, box);
+      t.nmaps = 1;
+      const uint64_t bd[2] = {64, 256};
+      const uint64_t bs[1] = {128};
+      const uint32_t bb[2] = {64, 16};
+      if (!rc) rc = make_tmap_bf16(&t.b, m->conv[0].b_dgrad, 2, bd, bs, bb);
+      m->ops_conv1_bwd.push_back(op);
+    } else {
+      Act gy = m->c1; gy.p = m->g_c1;
+      Act gx = m->t_in; gx.p = m->g_img_nhwc;
+      rc = build_simt_op(m->ops_conv1_bwd, m->conv[0].f_dgrad, 7, 2, true, gy, gx, nullptr, nullptr, nullptr, 0, 3);
+    }
+  }
+  if (rc_out) *rc_out = rc;
+  return (int64_t)bump.off;
+}
+
+int ensure_plan(advb200_model* m, int n, void* ws, int64_t ws_bytes) {
+  ADV_CHECK_ARG(m, "null model");
+  ADV_CHECK_ARG(n > 0, "batch must be positive");
+  ADV_CHECK_ARG(ws, "workspace is null");
+  ADV_CHECK_ARG((reinterpret_cast<uintptr_t>(ws) & 1023) == 0, "workspace must be 1024-byte aligned");
+  if (m->plan_n == n && m->plan_ws == ws) return ADVB200_OK;
+  const int64_t need = plan(m, n, nullptr, nullptr);
+  if (ws_bytes < need) return fail(ADVB200_ERR_ARG, "workspace too small: need " + std::to_string(need));
+  int rc = ADVB200_OK;
+  plan(m, n, ws, &rc);
+  if (rc) { m->plan_n = -1; return rc; }
+  m->plan_n = n; m->plan_ws = ws;
+  return ADVB200_OK;
+}
+
+int forward_impl(advb200_model* m, const float* x, const float* mean3, const float* std3, int n,
+                 bool stop_at_layer3, float* score_out, cudaStream_t st) {
+  const bool tc = m->precision == ADVB200_PREC_BF16;
+  int rc;
+  if (tc) rc = launch_prep_hcol(x, mean3, std3, reinterpret_cast<bf16*>(m->t_in.p), n, st);
+  else rc = launch_prep_nhwc(x, mean3, std3, reinterpret_cast<float*>(m->t_in.p), n, kImg, kImg, st);
+  if (rc) return rc;
+  if ((rc = run_ops(m->ops_conv1, st))) return rc;
+  if (tc) rc = launch_maxpool_fwd<bf16>((const bf16*)m->c1.p, (bf16*)m->p1.p, m->pool_idx, n, 112, 112, 64, st);
+  else rc = launch_maxpool_fwd<float>((const float*)m->c1.p, (float*)m->p1.p, m->pool_idx, n, 112, 112, 64, st);
+  if (rc) return rc;
+  if ((rc = run_ops(m->ops_l123, st))) return rc;
+  if (score_out) {
+    if (tc) rc = launch_detector_score<bf16>((const bf16*)m->l3out.p, score_out, n, 196, 1024, st);
+    else rc = launch_detector_score<float>((const float*)m->l3out.p, score_out, n, 196, 1024, st);
+    if (rc) return rc;
+  }
+  if (stop_at_layer3) return ADVB200_OK;
+  if ((rc = run_ops(m->ops_l4, st))) return rc;
+  if (tc) rc = launch_avgpool_fwd<bf16>((const bf16*)m->l4out.p, m->feat, n, 49, kFeat, st);
+  else rc = launch_avgpool_fwd<float>((const float*)m->l4out.p, m->feat, n, 49, kFeat, st);
+  if (rc) return rc;
+  // fc forward: logits = feat * W^T + b   (fp32 in both modes)
+  SimtConvParams f{};
+  f.in = m->feat; f.wm = m->fc_wt; f.out = m->logits; f.bias = m->fc_b;
+  f.n = n; f.hi = f.wi = f.ho = f.wo = 1; f.ci = kFeat; f.co = kClasses; f.kh = f.kw = 1; f.stride = 1;
+  return launch_simt_conv(f, st);
+}
+
+}  // namespace
+}  // namespace advb200
+
+extern "C" {
+
+const char* advb200_last_error(void) { return g_last_error.c_str(); }
+int advb200_version(void) { return 100; }
+int64_t advb200_launch_count(void) { return (int64_t)g_launches.load(); }
+
+int advb200_model_create(const float* const* conv_w, const float* const* bn_gamma, const float* const* bn_beta,
+                         const float* const* bn_mean, const float* const* bn_var, const float* bn_eps_host,
+                         const float* fc_w, const float* fc_b, int precision, void* stream,
+                         advb200_model** out) {
+  ADV_CHECK_ARG(conv_w && bn_gamma && bn_beta && bn_mean && bn_var && bn_eps_host && fc_w && fc_b && out,
+                "model_create: null argument");
+  ADV_CHECK_ARG(precision == ADVB200_PREC_BF16 || precision == ADVB200_PREC_FP32, "model_create: bad precision");
+  int dev = 0, major = 0;
+  ADV_CHECK_CUDA(cudaGetDevice(&dev));
+  ADV_CHECK_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  if (major != 10) return fail(ADVB200_ERR_UNSUPPORTED, "libadvb200 requires an sm_100 (B200) device");
+  cudaStream_t st = as_stream(stream);
+  advb200_model* m = new advb200_model();
+  m->precision = precision; m->device = dev;
+  make_blocks(m);
+  // geometry of the 53 convs in canonical order
+  m->conv[0].cin = 3; m->conv[0].cout = 64; m->conv[0].k = 7; m->conv[0].stride = 2;
+  for (const BlockSpec& s : m->blocks) {
+    ConvW* c = &m->conv[s.conv_base];
+    c[0].cin = s.cin; c[0].cout = s.width; c[0].k = 1; c[0].stride = 1;
+    c[1].cin = s.width; c[1].cout = s.width; c[1].k = 3; c[1].stride = s.stride;
+    c[2].cin = s.width; c[2].cout = s.width * 4; c[2].k = 1; c[2].stride = 1;
+    if (s.down) { c[3].cin = s.cin; c[3].cout = s.width * 4; c[3].k = 1; c[3].stride = s.stride; }
+  }
+  auto dalloc = [&](size_t bytes) -> void* {
+    void* p = nullptr;
+    if (cudaMalloc(&p, bytes) != cudaSuccess) return nullptr;
+    m->owned.push_back(p);
+    return p;
+  };
+  int rc = ADVB200_OK;
+  for (int i = 0; i < ADVB200_NUM_CONVS && !rc; ++i) {
+    ConvW& c = m->conv[i];
+    ADV_CHECK_ARG(conv_w[i] && bn_gamma[i] && bn_beta[i] && bn_mean[i] && bn_var[i], "model_create: null weight");
+    const size_t wn = (size_t)c.cout * c.cin * c.k * c.k;
+    c.scale = (float*)dalloc(c.cout * 4); c.shift = (float*)dalloc(c.cout * 4);
+    if (!c.scale || !c.shift) { rc = fail(ADVB200_ERR_CUDA, "model_create: cudaMalloc failed"); break; }
+    rc = launch_bn_fold(bn_gamma[i], bn_beta[i], bn_mean[i], bn_var[i], bn_eps_host[i], c.scale, c.shift, c.cout, st);
+    if (rc) break;
+    if (precision == ADVB200_PREC_FP32) {
+      c.f_fwd = (float*)dalloc(wn * 4); c.f_dgrad = (float*)dalloc(wn * 4);
+      if (!c.f_fwd || !c.f_dgrad) { rc = fail(ADVB200_ERR_CUDA, "model_create: cudaMalloc failed"); break; }
+      rc = launch_pack_f32(conv_w[i], c.scale, c.f_fwd, c.f_dgrad, c.cout, c.cin, c.k, st);
+    } else if (i == 0) {
+      c.b_fwd = (bf16*)dalloc(256 * 64 * 2); c.b_dgrad = (bf16*)dalloc(256 * 64 * 2);
+      if (!c.b_fwd || !c.b_dgrad) { rc = fail(ADVB200_ERR_CUDA, "model_create: cudaMalloc failed"); break; }
+      rc = launch_pack_conv1_bf16(conv_w[0], c.scale, c.b_fwd, c.b_dgrad, st);
+    } else {
+      c.b_fwd = (bf16*)dalloc(wn * 2); c.b_dgrad = (bf16*)dalloc(wn * 2);
+      if (!c.b_fwd || !c.b_dgrad) { rc = fail(ADVB200_ERR_CUDA, "model_create: cudaMalloc failed"); break; }
+      rc = launch_pack_bf16(conv_w[i], c.scale, c.b_fwd, c.b_dgrad, c.cout, c.cin, c.k, st);
+    }
+  }
+  if (!rc) {
+    m->fc_w = (float*)dalloc((size_t)kClasses * kFeat * 4);
+    m->fc_wt = (float*)dalloc((size_t)kClasses * kFeat * 4);
+    m->fc_b = (float*)dalloc(kClasses * 4);
+    if (!m->fc_w || !m->fc_wt || !m->fc_b) rc = fail(ADVB200_ERR_CUDA, "model_create: cudaMalloc failed");
+  }
+  if (!rc) {
+    cudaError_t e = cudaMemcpyAsync(m->fc_w, fc_w, (size_t)kClasses * kFeat * 4, cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(m->fc_b, fc_b, kClasses * 4, cudaMemcpyDeviceToDevice, st);
+    if (e != cudaSuccess) rc = fail(ADVB200_ERR_CUDA, std::string("model_create: ") + cudaGetErrorString(e));
+  }
+  if (!rc) rc = launch_transpose_f32(m->fc_w, m->fc_wt, kClasses, kFeat, st);
+  if (!rc) {
+    cudaError_t e = cudaStreamSynchronize(st);   // create-time only: the caller may free its tensors
+    if (e != cudaSuccess) rc = fail(ADVB200_ERR_CUDA, std::string("model_create: ") + cudaGetErrorString(e));
+  }
+  if (rc) { advb200_model_destroy(m); return rc; }
+  *out = m;
+  return ADVB200_OK;
+}
+
+int advb200_model_destroy(advb200_model* m) {
+  if (!m) return ADVB200_OK;
+  for (void* p : m->owned) cudaFree(p);
+  delete m;
+  return ADVB200_OK;
+}
+
+int advb200_model_precision(const advb200_model* m) { return m ? m->precision : ADVB200_ERR_ARG; }
+
+int64_t advb200_workspace_bytes(const advb200_model* m, int n) {
+  if (!m || n <= 0) return ADVB200_ERR_ARG;
+  return plan(const_cast<advb200_model*>(m), n, nullptr, nullptr);
+}
+
+int advb200_forward(advb200_model* m, const float* x, const float* mean3, const float* std3, int n,
+                    float* logits_out, int64_t* preds_out, int stop_at_layer3, float* score_out, void* workspace,
+                    int64_t workspace_bytes, void* stream) {
+  ADV_CHECK_ARG(m && x && mean3 && std3, "forward: null argument");
+  ADV_CHECK_ARG(stop_at_layer3 || logits_out || preds_out || score_out, "forward: no output requested");
+  int rc = ensure_plan(m, n, workspace, workspace_bytes);
+  if (rc) return rc;
+  cudaStream_t st = as_stream(stream);
+  rc = forward_impl(m, x, mean3, std3, n, stop_at_layer3 != 0, score_out, st);
+  if (rc || stop_at_layer3) return rc;
+  if (logits_out)
+    ADV_CHECK_CUDA(cudaMemcpyAsync(logits_out, m->logits, (size_t)n * kClasses * 4, cudaMemcpyDeviceToDevice, st));
+  if (preds_out) rc = launch_argmax(m->logits, n, kClasses, preds_out, st);
+  return rc;
+}
+
+int advb200_input_grad(advb200_model* m, const float* x, const float* mean3, const float* std3,
+                       const int64_t* y_cmp, int n, int loss_kind, float c, float kappa, float inv_n_global,
+                       float* logits_out, int64_t* preds_out, float* loss_out, uint8_t* success_out,
+                       float* grad_x_out, void* workspace, int64_t workspace_bytes, void* stream) {
+  ADV_CHECK_ARG(m && x && mean3 && std3 && y_cmp && grad_x_out, "input_grad: null argument");
+  ADV_CHECK_ARG(loss_kind >= ADVB200_LOSS_CE_MEAN && loss_kind <= ADVB200_LOSS_CW_TGT, "input_grad: bad loss kind");
+  int rc = ensure_plan(m, n, workspace, workspace_bytes);
+  if (rc) return rc;
+  cudaStream_t st = as_stream(stream);
+  const bool tc = m->precision == ADVB200_PREC_BF16;
+  if ((rc = forward_impl(m, x, mean3, std3, n, false, nullptr, st))) return rc;
+  if (logits_out)
+    ADV_CHECK_CUDA(cudaMemcpyAsync(logits_out, m->logits, (size_t)n * kClasses * 4, cudaMemcpyDeviceToDevice, st));
+  const float scale = (loss_kind == ADVB200_LOSS_CE_MEAN) ? inv_n_global : 1.0f;
+  if ((rc = launch_loss_grad(m->logits, y_cmp, n, kClasses, loss_kind, c, kappa, scale, m->dlogits, preds_out,
+                             loss_out, success_out, st)))
+    return rc;
+  // fc input gradient: dfeat = dlogits * W
+  SimtConvParams f{};
+  f.in = m->dlogits; f.wm = m->fc_w; f.out = m->dfeat;
+  f.n = n; f.hi = f.wi = f.ho = f.wo = 1; f.ci = kClasses; f.co = kFeat; f.kh = f.kw = 1; f.stride = 1;
+  if ((rc = launch_simt_conv(f, st))) return rc;
+  if (tc) rc = launch_avgpool_bwd<bf16>(m->dfeat, (const bf16*)m->l4out.p, (bf16*)m->g_top, n, 49, kFeat, st);
+  else rc = launch_avgpool_bwd<float>(m->dfeat, (const float*)m->l4out.p, (float*)m->g_top, n, 49, kFeat, st);
+  if (rc) return rc;
+  if ((rc = run_ops(m->ops_bwd, st))) return rc;
+  if (tc) rc = launch_maxpool_bwd<bf16>((const bf16*)m->g_final, m->pool_idx, (bf16*)m->g_c1, n, 112, 112, 64, st);
+  else rc = launch_maxpool_bwd<float>((const float*)m->g_final, m->pool_idx, (float*)m->g_c1, n, 112, 112, 64, st);
+  if (rc) return rc;
+  if (tc) {
+    // patch the per-call output / std pointers into the conv1-dgrad epilogue (host-side only)
+    Op& op = m->ops_conv1_bwd[0];
+    op.tc.p.out = grad_x_out;
+    op.tc.p.std_dev = std3;
+    rc = run_ops(m->ops_conv1_bwd, st);
+  } else {
+    if ((rc = run_ops(m->ops_conv1_bwd, st))) return rc;
+    rc = launch_grad_nhwc_to_nchw(m->g_img_nhwc, std3, grad_x_out, n, kImg, kImg, st);
+  }
+  return rc;
+}
+
+int advb200_test_conv(int precision, const void* x, const float* wgt, const float* bias, const void* add,
+                      const void* mask, void* out, int n, int h, int w, int cin, int cout, int ksize, int stride,
+                      int relu, int dgrad, void* stream) {
+  ADV_CHECK_ARG(x && wgt && out, "test_conv: null argument");
+  ADV_CHECK_ARG(n > 0 && h > 0 && w > 0 && cin > 0 && cout > 0, "test_conv: bad sizes");
+  cudaStream_t st = as_stream(stream);
+  const size_t wn = (size_t)cout * cin * ksize * ksize;
+  const int ho = h / stride, wo = w / stride;
+  Act a_in, a_out;
+  if (!dgrad) { a_in = Act{const_cast<void*>(x), n, h, w, cin}; a_out = Act{out, n, ho, wo, cout}; }
+  else { a_in = Act{const_cast<void*>(x), n, ho, wo, cout}; a_out = Act{out, n, h, w, cin}; }
+  std::vector<Op> ops;
+  void* pk_f = nullptr; void* pk_d = nullptr;
+  int rc = ADVB200_OK;
+  const size_t esz = precision == ADVB200_PREC_BF16 ? 2 : 4;
+  ADV_CHECK_CUDA(cudaMalloc(&pk_f, wn * esz));
+  ADV_CHECK_CUDA(cudaMalloc(&pk_d, wn * esz));
+  if (precision == ADVB200_PREC_BF16) {
+    rc = launch_pack_bf16(wgt, nullptr, (bf16*)pk_f, (bf16*)pk_d, cout, cin, ksize, st);
+    if (!rc && dgrad && stride == 2 && ksize == 1)
+      ADV_CHECK_CUDA(cudaMemsetAsync(out, 0, (size_t)a_out.elems() * 2, st));
+    if (!rc) rc = build_tc_ops(ops, dgrad ? (const bf16*)pk_d : (const bf16*)pk_f, ksize, stride, dgrad != 0, a_in, a_out,
+                               bias, (const bf16*)add, (const bf16*)mask, relu);
+  } else {
+    rc = launch_pack_f32(wgt, nullptr, (float*)pk_f, (float*)pk_d, cout, cin, ksize, st);
+    if (!rc) rc = build_simt_op(ops, dgrad ? (const float*)pk_d : (const float*)pk_f, ksize, stride, dgrad != 0, a_in,
+                                a_out, bias, (const float*)add, (const float*)mask, relu);
+  }
+  if (!rc) rc = run_ops(ops, st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  cudaFree(pk_f); cudaFree(pk_d);
+  if (!rc && e != cudaSuccess) rc = fail(ADVB200_ERR_CUDA, std::string("test_conv: ") + cudaGetErrorString(e));
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,507 @@
+// Non-GEMM layers of the ResNet-50 attack path.  See layers.cuh for the contracts.
+#include "layers.cuh"
+
+namespace advb200 {
+
+namespace {
+
+constexpr int kT = 256;
+inline int nblocks(long long work) { return (int)((work + kT - 1) / kT); }
+
+template <typename T> __device__ __forceinline__ float to_f(T v);
+template <> __device__ __forceinline__ float to_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f<bf16>(bf16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ bf16 from_f<bf16>(float v) { return __float2bfloat16_rn(v); }
+
+// ---------------------------------------------------------------- input preparation
+__global__ void __launch_bounds__(kT)
+prep_hcol_kernel(const float* __restrict__ x, const float* __restrict__ mean3, const float* __restrict__ std3,
+                 bf16* __restrict__ out, long long total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const int j8 = (int)(t & 7);
+  long long r = t >> 3;
+  const int wo = (int)(r % 112); r /= 112;
+  const int hp = (int)(r % 115);
+  const int n = (int)(r / 115);
+  const int u = j8 >> 1, q0 = (j8 & 1) * 8;
+  __align__(16) bf16 v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int q = q0 + i;
+    float val = 0.f;
+    if (q < 12) {
+      const int c = q % 3, pw = (q / 3) & 1, ph = q / 6;
+      const int row = 2 * (hp - 2) + ph, col = 2 * (wo - 2 + u) + pw;
+      if (row >= 0 && row < 224 && col >= 0 && col < 224) {
+        const float px = __ldg(x + (((long long)n * 3 + c) * 224 + row) * 224 + col);
+        val = __fdiv_rn(__fsub_rn(px, __ldg(mean3 + c)), __ldg(std3 + c));   // attack.py:17
+      }
+    }
+    v[i] = __float2bfloat16_rn(val);
+  }
+  *reinterpret_cast<uint4*>(out + t * 8) = *reinterpret_cast<const uint4*>(v);
+}
+
+__global__ void __launch_bounds__(kT)
+prep_nhwc_kernel(const float* __restrict__ x, const float* __restrict__ mean3, const float* __restrict__ std3,
+                 float* __restrict__ out, int h, int w, long long total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const int c = (int)(t % 3);
+  long long r = t / 3;
+  const int col = (int)(r % w); r /= w;
+  const int row = (int)(r % h);
+  const long long n = r / h;
+  const float px = __ldg(x + ((n * 3 + c) * h + row) * w + col);
+  out[t] = __fdiv_rn(__fsub_rn(px, __ldg(mean3 + c)), __ldg(std3 + c));
+}
+
+__global__ void __launch_bounds__(kT)
+grad_nhwc_to_nchw_kernel(const float* __restrict__ g, const float* __restrict__ std3, float* __restrict__ out,
+                         int h, int w, long long total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // NCHW index
+  if (t >= total) return;
+  const int col = (int)(t % w);
+  long long r = t / w;
+  const int row = (int)(r % h); r /= h;
+  const int c = (int)(r % 3);
+  const long long n = r / 3;
+  out[t] = __fdiv_rn(__ldg(g + ((n * h + row) * w + col) * 3 + c), __ldg(std3 + c));
+}
+
+// ---------------------------------------------------------------- max pool 3x3/2 pad 1
+template <typename T>
+__global__ void __launch_bounds__(kT)
+maxpool_fwd_kernel(const T* __restrict__ in, T* __restrict__ out, uint8_t* __restrict__ idx, int hi, int wi,
+                   int ho, int wo, int c, long long total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const int ch = (int)(t % c);
+  long long r = t / c;
+  const int ow = (int)(r % wo); r /= wo;
+  const int oh = (int)(r % ho);
+  const long long n = r / ho;
+  float best = -INFINITY;
+  int pos = 0;
+#pragma unroll
+  for (int dr = 0; dr < 3; ++dr) {
+    const int ih = 2 * oh - 1 + dr;
+    if (ih < 0 || ih >= hi) continue;
+#pragma unroll
+    for (int ds = 0; ds < 3; ++ds) {
+      const int iw = 2 * ow - 1 + ds;
+      if (iw < 0 || iw >= wi) continue;
+      const float v = to_f<T>(in[((n * hi + ih) * wi + iw) * c + ch]);
+      if (v > best) { best = v; pos = dr * 3 + ds; }   // first maximum wins (torch tie rule)
+    }
+  }
+  out[t] = from_f<T>(best);
+  idx[t] = best > 0.f ? (uint8_t)pos : (uint8_t)255;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kT)
+maxpool_bwd_kernel(const T* __restrict__ gout, const uint8_t* __restrict__ idx, T* __restrict__ gin, int hi,
+                   int wi, int ho, int wo, int c, long long total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const int ch = (int)(t % c);
+  long long r = t / c;
+  const int iw = (int)(r % wi); r /= wi;
+  const int ih = (int)(r % hi);
+  const long long n = r / hi;
+  float g = 0.f;
+  const int oh_lo = ih >> 1, oh_hi = (ih + 1) >> 1;    // windows whose rows 2oh-1..2oh+1 contain ih
+  const int ow_lo = iw >> 1, ow_hi = (iw + 1) >> 1;
+  for (int oh = oh_lo; oh <= oh_hi; ++oh) {
+    if (oh >= ho) continue;
+    const int dr = ih - (2 * oh - 1);
+    for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+      if (ow >= wo) continue;
+      const int ds = iw - (2 * ow - 1);
+      const long long o = ((n * ho + oh) * wo + ow) * c + ch;
+      if (idx[o] == (uint8_t)(dr * 3 + ds)) g += to_f<T>(gout[o]);
+    }
+  }
+  gin[t] = from_f<T>(g);
+}
+
+// ---------------------------------------------------------------- global average pool
+template <typename T>
+__global__ void __launch_bounds__(kT)
+avgpool_fwd_kernel(const T* __restrict__ in, float* __restrict__ feat, int hw, int c, long long total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // (n, c)
+  if (t >= total) return;
+  const int ch = (int)(t % c);
+  const long long n = t / c;
+  float s = 0.f;
+  for (int p = 0; p < hw; ++p) s += to_f<T>(in[(n * hw + p) * c + ch]);
+  feat[t] = s / (float)hw;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kT)
+avgpool_bwd_kernel(const float* __restrict__ dfeat, const T* __restrict__ act, T* __restrict__ gact, int hw,
+                   int c, long long total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // (n, p, c)
+  if (t >= total) return;
+  const int ch = (int)(t % c);
+  const long long n = t / ((long long)hw * c);
+  const float g = __ldg(dfeat + n * c + ch) / (float)hw;
+  gact[t] = from_f<T>(to_f<T>(act[t]) > 0.f ? g : 0.f);
+}
+
+// ---------------------------------------------------------------- losses
+// one block per image; classes <= 4096
+__global__ void __launch_bounds__(kT)
+loss_grad_kernel(const float* __restrict__ logits, const int64_t* __restrict__ y, int classes, int loss_kind,
+                 float cw_c, float kappa, float scale, float* __restrict__ dlogits,
+                 int64_t* __restrict__ preds, float* __restrict__ loss, uint8_t* __restrict__ success) {
+  __shared__ float s_val[kT];
+  __shared__ int s_idx[kT];
+  __shared__ float s_red[kT / 32];
+  __shared__ float s_bcast[4];
+  __shared__ int s_ibcast[2];
+  const int n = blockIdx.x, tid = threadIdx.x;
+  const float* z = logits + (long long)n * classes;
+  const int yy = (int)y[n];
+
+  // argmax (first maximum) and maximum over j != y
+  float bv = -INFINITY; int bi = 0x7fffffff;
+  float ov = -INFINITY;
+  for (int j = tid; j < classes; j += kT) {
+    const float v = z[j];
+    if (v > bv) { bv = v; bi = j; }
+    if (j != yy && v > ov) ov = v;
+  }
+  s_val[tid] = bv; s_idx[tid] = bi;
+  __syncthreads();
+  for (int o = kT / 2; o > 0; o >>= 1) {
+    if (tid < o) {
+      const float v2 = s_val[tid + o]; const int i2 = s_idx[tid + o];
+      if (v2 > s_val[tid] || (v2 == s_val[tid] && i2 < s_idx[tid])) { s_val[tid] = v2; s_idx[tid] = i2; }
+    }
+    __syncthreads();
+  }
+  const float zmax = s_val[0];
+  const int amax = s_idx[0];
+  __syncthreads();
+  s_val[tid] = ov;
+  __syncthreads();
+  for (int o = kT / 2; o > 0; o >>= 1) {
+    if (tid < o) s_val[tid] = fmaxf(s_val[tid], s_val[tid + o]);
+    __syncthreads();
+  }
+  const float other_raw = s_val[0];
+  __syncthreads();
+  if (tid == 0 && preds) preds[n] = amax;
+
+  if (loss_kind == ADVB200_LOSS_CE_MEAN) {
+    // softmax cross-entropy: d z_j = (p_j - [j==y]) * scale, with the true-class entry formed as
+    // -(sum_{j!=y} p_j) to avoid the cancellation in p_y - 1
+    float so = 0.f;
+    for (int j = tid; j < classes; j += kT)
+      if (j != yy) so += expf(z[j] - zmax);
+    const float tot_o = block_sum<kT>(so, s_red);
+    if (tid == 0) {
+      const float ey = expf(z[yy] - zmax);
+      s_bcast[0] = tot_o;
+      s_bcast[1] = tot_o + ey;
+    }
+    __syncthreads();
+    const float sum_other = s_bcast[0], sum_all = s_bcast[1];
+    if (dlogits)
+      for (int j = tid; j < classes; j += kT) {
+        const float pj = expf(z[j] - zmax) / sum_all;
+        dlogits[(long long)n * classes + j] = (j == yy ? -(sum_other / sum_all) : pj) * scale;
+      }
+    if (tid == 0) {
+      if (loss) loss[n] = logf(sum_all) - (z[yy] - zmax);
+      if (success) success[n] = amax != yy;
+    }
+  } else {
+    // CW margin (attack.py:114-124).  other = amax_j (z_j - 1e4*[j==y]); ties share the gradient.
+    const float real = z[yy];
+    const float other = fmaxf(other_raw, real - 1e4f);
+    int ties = 0;
+    for (int j = tid; j < classes; j += kT) {
+      const float v = (j == yy) ? real - 1e4f : z[j];
+      if (v == other) ++ties;
+    }
+    s_idx[tid] = ties;
+    __syncthreads();
+    for (int o = kT / 2; o > 0; o >>= 1) {
+      if (tid < o) s_idx[tid] += s_idx[tid + o];
+      __syncthreads();
+    }
+    const int nties = s_idx[0];
+    const bool targeted = loss_kind == ADVB200_LOSS_CW_TGT;
+    const float arg = targeted ? (other - real + kappa) : (real - other + kappa);
+    const bool active = arg >= 0.f;               // clamp(min=0) passes the gradient at exactly 0
+    const float sgn = targeted ? -1.f : 1.f;      // d f / d real
+    if (dlogits)
+      for (int j = tid; j < classes; j += kT) {
+        float g = 0.f;
+        if (active) {
+          const float v = (j == yy) ? real - 1e4f : z[j];
+          if (j == yy) g += sgn * cw_c;
+          if (v == other) g += -sgn * cw_c / (float)nties;
+        }
+        dlogits[(long long)n * classes + j] = g * scale;
+      }
+    if (tid == 0) {
+      if (loss) loss[n] = fmaxf(arg, 0.f);
+      if (success) success[n] = targeted ? (amax == yy) : (amax != yy);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kT)
+argmax_kernel(const float* __restrict__ logits, int classes, int64_t* __restrict__ preds) {
+  __shared__ float s_val[kT];
+  __shared__ int s_idx[kT];
+  const int n = blockIdx.x, tid = threadIdx.x;
+  const float* z = logits + (long long)n * classes;
+  float bv = -INFINITY; int bi = 0x7fffffff;
+  for (int j = tid; j < classes; j += kT) {
+    const float v = z[j];
+    if (v > bv) { bv = v; bi = j; }
+  }
+  s_val[tid] = bv; s_idx[tid] = bi;
+  __syncthreads();
+  for (int o = kT / 2; o > 0; o >>= 1) {
+    if (tid < o) {
+      const float v2 = s_val[tid + o]; const int i2 = s_idx[tid + o];
+      if (v2 > s_val[tid] || (v2 == s_val[tid] && i2 < s_idx[tid])) { s_val[tid] = v2; s_idx[tid] = i2; }
+    }
+    __syncthreads();
+  }
+  if (tid == 0) preds[n] = s_idx[0];
+}
+
+// ---------------------------------------------------------------- detector score
+template <typename T>
+__global__ void __launch_bounds__(kT)
+detector_score_kernel(const T* __restrict__ act, float* __restrict__ score, int hw, int c) {
+  __shared__ float s_red[kT / 32];
+  __shared__ float s_keep;
+  const long long n = blockIdx.x;
+  const T* a = act + n * (long long)hw * c;
+  float sq = 0.f, var_sum = 0.f;
+  for (int ch = threadIdx.x; ch < c; ch += kT) {
+    float s = 0.f;
+    for (int p = 0; p < hw; ++p) s += to_f<T>(a[(long long)p * c + ch]);
+    const float mean = s / (float)hw;
+    float d2 = 0.f;
+    for (int p = 0; p < hw; ++p) {
+      const float v = to_f<T>(a[(long long)p * c + ch]);
+      sq += v * v;
+      const float d = v - mean;
+      d2 += d * d;
+    }
+    var_sum += d2 / (float)(hw - 1);                       // unbiased (torch.var default)
+  }
+  const float tot_sq = block_sum<kT>(sq, s_red);
+  if (threadIdx.x == 0) s_keep = tot_sq;
+  __syncthreads();
+  const float tot_var = block_sum<kT>(var_sum, s_red);
+  if (threadIdx.x == 0) {
+    const float l2 = sqrtf(s_keep) / (float)c;             // defense_experiments.py:245
+    const float sc = l2 + (tot_var / (float)c) * 0.1f;     // :249-252
+    score[n] = fminf(fmaxf(sc, 0.f), 100.f);               // :255
+  }
+}
+
+// ---------------------------------------------------------------- weight packing
+__global__ void bn_fold_kernel(const float* gamma, const float* beta, const float* mean, const float* var,
+                               float eps, float* scale, float* shift, int c) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= c) return;
+  const float s = gamma[i] / sqrtf(var[i] + eps);
+  scale[i] = s;
+  shift[i] = beta[i] - mean[i] * s;
+}
+
+template <typename T>
+__global__ void pack_kernel(const float* __restrict__ w, const float* __restrict__ scale, T* __restrict__ fwd,
+                            T* __restrict__ dgrad, int cout, int cin, int k, int f32_layout, long long total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // index into w [co,ci,r,s]
+  if (t >= total) return;
+  const int kk = k * k;
+  const int rs = (int)(t % kk);
+  const int ci = (int)((t / kk) % cin);
+  const int co = (int)(t / ((long long)kk * cin));
+  const float v = w[t] * (scale ? scale[co] : 1.f);
+  if (f32_layout) {
+    if (fwd) fwd[((long long)rs * cin + ci) * cout + co] = from_f<T>(v);
+    if (dgrad) dgrad[((long long)rs * cout + co) * cin + ci] = from_f<T>(v);
+  } else {
+    if (fwd) fwd[((long long)rs * cout + co) * cin + ci] = from_f<T>(v);
+    if (dgrad) dgrad[((long long)rs * cin + ci) * cout + co] = from_f<T>(v);
+  }
+}
+
+__global__ void pack_conv1_kernel(const float* __restrict__ w, const float* __restrict__ scale,
+                                  bf16* __restrict__ fwd, bf16* __restrict__ dgrad) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;    // (tt, u, q, co) : 4*4*16*64
+  if (t >= 4 * 4 * 16 * 64) return;
+  const int co = t & 63, q = (t >> 6) & 15, u = (t >> 10) & 3, tt = t >> 12;
+  float v = 0.f;
+  if (q < 12) {
+    const int c = q % 3, pw = (q / 3) & 1, ph = q / 6;
+    const int r = 2 * tt + ph - 1, s = 2 * u + pw - 1;
+    if (r >= 0 && s >= 0) v = w[((co * 3 + c) * 7 + r) * 7 + s] * scale[co];
+  }
+  const bf16 b = __float2bfloat16_rn(v);
+  fwd[(tt * 64 + co) * 64 + u * 16 + q] = b;
+  dgrad[((tt * 4 + u) * 16 + q) * 64 + co] = b;
+}
+
+__global__ void transpose_kernel(const float* __restrict__ in, float* __restrict__ out, int rows, int cols) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)rows * cols) return;
+  const int r = (int)(t / cols), c = (int)(t % cols);
+  out[(long long)c * rows + r] = in[t];
+}
+
+__global__ void f32_to_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, long long n) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) out[t] = __float2bfloat16_rn(in[t]);
+}
+
+}  // namespace
+
+int launch_prep_hcol(const float* x, const float* mean3, const float* std3, bf16* out, int n, cudaStream_t st) {
+  const long long total = (long long)n * 115 * 112 * 8;
+  if (!total) return ADVB200_OK;
+  prep_hcol_kernel<<<nblocks(total), kT, 0, st>>>(x, mean3, std3, out, total);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+int launch_prep_nhwc(const float* x, const float* mean3, const float* std3, float* out, int n, int h, int w,
+                     cudaStream_t st) {
+  const long long total = (long long)n * h * w * 3;
+  if (!total) return ADVB200_OK;
+  prep_nhwc_kernel<<<nblocks(total), kT, 0, st>>>(x, mean3, std3, out, h, w, total);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+int launch_grad_nhwc_to_nchw(const float* g, const float* std3, float* out, int n, int h, int w,
+                             cudaStream_t st) {
+  const long long total = (long long)n * h * w * 3;
+  if (!total) return ADVB200_OK;
+  grad_nhwc_to_nchw_kernel<<<nblocks(total), kT, 0, st>>>(g, std3, out, h, w, total);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+
+template <typename T>
+int launch_maxpool_fwd(const T* in, T* out, uint8_t* idx, int n, int hi, int wi, int c, cudaStream_t st) {
+  const int ho = (hi + 2 - 3) / 2 + 1, wo = (wi + 2 - 3) / 2 + 1;
+  const long long total = (long long)n * ho * wo * c;
+  if (!total) return ADVB200_OK;
+  maxpool_fwd_kernel<T><<<nblocks(total), kT, 0, st>>>(in, out, idx, hi, wi, ho, wo, c, total);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+template <typename T>
+int launch_maxpool_bwd(const T* gout, const uint8_t* idx, T* gin, int n, int hi, int wi, int c,
+                       cudaStream_t st) {
+  const int ho = (hi + 2 - 3) / 2 + 1, wo = (wi + 2 - 3) / 2 + 1;
+  const long long total = (long long)n * hi * wi * c;
+  if (!total) return ADVB200_OK;
+  maxpool_bwd_kernel<T><<<nblocks(total), kT, 0, st>>>(gout, idx, gin, hi, wi, ho, wo, c, total);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+template <typename T>
+int launch_avgpool_fwd(const T* in, float* feat, int n, int hw, int c, cudaStream_t st) {
+  const long long total = (long long)n * c;
+  if (!total) return ADVB200_OK;
+  avgpool_fwd_kernel<T><<<nblocks(total), kT, 0, st>>>(in, feat, hw, c, total);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+template <typename T>
+int launch_avgpool_bwd(const float* dfeat, const T* act, T* gact, int n, int hw, int c, cudaStream_t st) {
+  const long long total = (long long)n * hw * c;
+  if (!total) return ADVB200_OK;
+  avgpool_bwd_kernel<T><<<nblocks(total), kT, 0, st>>>(dfeat, act, gact, hw, c, total);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+template <typename T>
+int launch_detector_score(const T* act, float* score, int n, int hw, int c, cudaStream_t st) {
+  if (!n) return ADVB200_OK;
+  detector_score_kernel<T><<<n, kT, 0, st>>>(act, score, hw, c);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+
+#define INSTANTIATE(T)                                                                                   \
+  template int launch_maxpool_fwd<T>(const T*, T*, uint8_t*, int, int, int, int, cudaStream_t);          \
+  template int launch_maxpool_bwd<T>(const T*, const uint8_t*, T*, int, int, int, int, cudaStream_t);    \
+  template int launch_avgpool_fwd<T>(const T*, float*, int, int, int, cudaStream_t);                     \
+  template int launch_avgpool_bwd<T>(const float*, const T*, T*, int, int, int, cudaStream_t);           \
+  template int launch_detector_score<T>(const T*, float*, int, int, int, cudaStream_t);
+INSTANTIATE(float)
+INSTANTIATE(bf16)
+
+int launch_loss_grad(const float* logits, const int64_t* y, int n, int classes, int loss_kind, float c,
+                     float kappa, float scale, float* dlogits, int64_t* preds, float* loss, uint8_t* success,
+                     cudaStream_t st) {
+  if (!n) return ADVB200_OK;
+  loss_grad_kernel<<<n, kT, 0, st>>>(logits, y, classes, loss_kind, c, kappa, scale, dlogits, preds, loss,
+                                     success);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+int launch_argmax(const float* logits, int n, int classes, int64_t* preds, cudaStream_t st) {
+  if (!n) return ADVB200_OK;
+  argmax_kernel<<<n, kT, 0, st>>>(logits, classes, preds);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+
+int launch_bn_fold(const float* gamma, const float* beta, const float* mean, const float* var, float eps,
+                   float* scale, float* shift, int c, cudaStream_t st) {
+  bn_fold_kernel<<<(c + 255) / 256, 256, 0, st>>>(gamma, beta, mean, var, eps, scale, shift, c);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+int launch_pack_f32(const float* w, const float* scale, float* fwd, float* dgrad, int cout, int cin, int k,
+                    cudaStream_t st) {
+  const long long total = (long long)cout * cin * k * k;
+  pack_kernel<float><<<nblocks(total), kT, 0, st>>>(w, scale, fwd, dgrad, cout, cin, k, 1, total);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+int launch_pack_bf16(const float* w, const float* scale, bf16* fwd, bf16* dgrad, int cout, int cin, int k,
+                     cudaStream_t st) {
+  const long long total = (long long)cout * cin * k * k;
+  pack_kernel<bf16><<<nblocks(total), kT, 0, st>>>(w, scale, fwd, dgrad, cout, cin, k, 0, total);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+int launch_pack_conv1_bf16(const float* w, const float* scale, bf16* fwd, bf16* dgrad, cudaStream_t st) {
+  pack_conv1_kernel<<<(4 * 4 * 16 * 64 + 255) / 256, 256, 0, st>>>(w, scale, fwd, dgrad);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+int launch_transpose_f32(const float* in, float* out, int rows, int cols, cudaStream_t st) {
+  const long long total = (long long)rows * cols;
+  transpose_kernel<<<nblocks(total), kT, 0, st>>>(in, out, rows, cols);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+int launch_f32_to_bf16(const float* in, bf16* out, int64_t n, cudaStream_t st) {
+  if (!n) return ADVB200_OK;
+  f32_to_bf16_kernel<<<nblocks(n), kT, 0, st>>>(in, out, n);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+
+}  // namespace advb200

@@ -1,0 +1,113 @@
+// fp32 validation-mode convolution: CUDA-core implicit GEMM (no tensor cores, no TF32).
+// Same semantics and fused epilogue as the tcgen05 kernel, arbitrary shapes with bounds checks,
+// also used for the fp32 classifier head (fc forward / input-gradient as 1x1 "convolutions").
+#include "simt_conv.cuh"
+
+namespace advb200 {
+
+namespace {
+
+constexpr int TM = 64, TN = 64, TK = 16;
+
+// out[pix, co] = sum_{r,s,ci} in[src(pix,r,s), ci] * wm[(r*kw+s)*ci_n + ci, co]
+__global__ void __launch_bounds__(256)
+simt_conv_kernel(const SimtConvParams p) {
+  __shared__ float As[TK][TM + 4];
+  __shared__ float Bs[TK][TN + 4];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const long long m_total = (long long)p.n * p.ho * p.wo;
+  const long long m0 = (long long)blockIdx.x * TM;
+  const int n0 = blockIdx.y * TN;
+  const int k_total = p.kh * p.kw * p.ci;
+
+  // A loader: thread -> (row = tid/4, 4 consecutive k)
+  const int a_row = tid >> 2, a_k = (tid & 3) * 4;
+  const long long a_m = m0 + a_row;
+  int a_n = 0, a_h = 0, a_w = 0;
+  const bool a_valid = a_m < m_total;
+  if (a_valid) {
+    a_w = (int)(a_m % p.wo);
+    a_h = (int)((a_m / p.wo) % p.ho);
+    a_n = (int)(a_m / ((long long)p.wo * p.ho));
+  }
+  // B loader: thread -> (k = tid/16, 4 consecutive co)
+  const int b_k = tid >> 4, b_c = (tid & 15) * 4;
+
+  float acc[4][4] = {};
+  for (int k0 = 0; k0 < k_total; k0 += TK) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = k0 + a_k + j;
+      float v = 0.f;
+      if (a_valid && k < k_total) {
+        const int rs = k / p.ci, ci = k - rs * p.ci;
+        const int r = rs / p.kw, s = rs - r * p.kw;
+        int sh, sw;
+        bool ok;
+        if (!p.dgrad) {
+          sh = a_h * p.stride - p.pad + r;
+          sw = a_w * p.stride - p.pad + s;
+          ok = sh >= 0 && sh < p.hi && sw >= 0 && sw < p.wi;
+        } else {
+          const int th = a_h + p.pad - r, tw = a_w + p.pad - s;
+          ok = th >= 0 && tw >= 0 && (th % p.stride) == 0 && (tw % p.stride) == 0;
+          sh = th / p.stride; sw = tw / p.stride;
+          ok = ok && sh < p.hi && sw < p.wi;
+        }
+        if (ok) v = __ldg(p.in + (((long long)a_n * p.hi + sh) * p.wi + sw) * p.ci + ci);
+      }
+      As[a_k + j][a_row] = v;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = k0 + b_k, co = n0 + b_c + j;
+      Bs[b_k][b_c + j] = (k < k_total && co < p.co) ? __ldg(p.wm + (long long)k * p.co + co) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < TK; ++kk) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = As[kk][ty * 4 + i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = Bs[kk][tx * 4 + j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const long long m = m0 + ty * 4 + i;
+    if (m >= m_total) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int co = n0 + tx * 4 + j;
+      if (co >= p.co) continue;
+      const long long o = m * p.co + co;
+      float v = acc[i][j];
+      if (p.bias) v += __ldg(p.bias + co);
+      if (p.add) v += __ldg(p.add + o);
+      if (p.relu) v = fmaxf(v, 0.f);
+      if (p.mask && !(__ldg(p.mask + o) > 0.f)) v = 0.f;
+      p.out[o] = v;
+    }
+  }
+}
+
+}  // namespace
+
+int launch_simt_conv(const SimtConvParams& p, cudaStream_t stream) {
+  const long long m_total = (long long)p.n * p.ho * p.wo;
+  if (m_total == 0) return ADVB200_OK;
+  dim3 grid((unsigned)((m_total + TM - 1) / TM), (unsigned)((p.co + TN - 1) / TN));
+  simt_conv_kernel<<<grid, 256, 0, stream>>>(p);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+
+}  // namespace advb200

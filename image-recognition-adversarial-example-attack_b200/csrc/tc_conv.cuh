@@ -1,0 +1,50 @@
+// tcgen05 / TMEM / TMA implicit-GEMM convolution for sm_100a — host-visible interface.
+//
+// One kernel covers every bf16 convolution of the ResNet-50 forward and input-gradient pass:
+//   D[128 pixels, BN channels] = sum over taps t, k-blocks kb of  A_t[pixels shifted by tap t, 64 ch]
+//                                                                  x B[t*rows + ch_out, 64 ch]^T
+// A tiles are TMA boxes (64 ch, bw, bh, bn) of an NHWC activation (or one of its stride-2
+// sub-lattices), out-of-bounds pixels are zero-filled by TMA (that is the conv padding);
+// B tiles are K-major packed weights; accumulators live in TMEM; the epilogue fuses
+// bias (folded BN shift), residual add, ReLU, and the ReLU mask of the input-gradient pass.
+#pragma once
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace advb200 {
+
+constexpr int kMaxTaps = 16;
+
+struct ConvGemmParams {
+  // tiling: a tile is bw x bh x bn pixels (product 128) by BN output channels
+  int tiles_w, tiles_h, tiles_n, tiles_c;
+  int bw, bh, bn;
+  int ntaps, kblocks;             // K loop: ntaps * kblocks blocks of 64 input channels
+  int tap_map[kMaxTaps];          // which A tensor map the tap reads
+  int tap_dw[kMaxTaps];           // pixel shift of the tap along w / h
+  int tap_dh[kMaxTaps];
+  int tap_brow[kMaxTaps];         // first row of the tap's weights in the packed B matrix
+  // output addressing (elements): off = n*o_sn + h*o_sh + w*o_sw + channel
+  int out_w, out_h, out_n, cout;
+  long long o_sn, o_sh, o_sw;
+  void* out;                      // bf16 (epi 0) or fp32 NCHW image gradient (epi 1)
+  const float* bias;              // [cout] or null
+  const __nv_bfloat16* add;       // residual / other-branch gradient, addressed like out, or null
+  const __nv_bfloat16* mask;      // forward activation whose sign gates the gradient, or null
+  int relu;
+  int epi;                        // 0: bf16 NHWC store; 1: conv1 input-gradient scatter (fp32 NCHW)
+  const float* std_dev;           // epi 1: device pointer to std[3]; gradient is divided by std[c]
+  int img_h, img_w;               // epi 1: full-resolution image size
+};
+
+// Launch on `stream`.  bn_cols in {16, 64, 128, 256}.  tmA: up to 4 maps; tmB: packed weights.
+int launch_conv_gemm(int bn_cols, const CUtensorMap* tmA, int n_maps, const CUtensorMap& tmB,
+                     const ConvGemmParams& p, cudaStream_t stream);
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda needed).
+// dims/strides innermost-first; strides in BYTES for dims 1..rank-1; bf16 elements; 128B swizzle.
+int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                   const uint64_t* strides_bytes, const uint32_t* box);
+
+}  // namespace advb200

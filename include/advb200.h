@@ -1,0 +1,174 @@
+/*
+ * advb200.h — C ABI of libadvb200.so, the B200 (sm_100a) attack hot path.
+ *
+ * The reference (picklerick422/Image-recognition-adversarial-example-attack) has no FFI layer:
+ * its boundary is the Python call surface of attack.py / defense_experiments.py.  Every entry
+ * point below names the reference lines whose arithmetic it replaces; the Python mirror in
+ * image-recognition-adversarial-example-attack_b200/advb200/ binds them with ctypes (see
+ * INTEGRATION.md for the stub a reference maintainer would add).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - images are fp32 NCHW [N,3,224,224] in [0,1], contiguous (attack.py:20-28 contract);
+ *   - labels are int64 [N];
+ *   - `stream` is a cudaStream_t passed as void*; all work is stream-ordered, nothing
+ *     synchronises internally, nothing allocates on the hot path (workspaces are caller-owned);
+ *   - return 0 = OK, negative = error, text via advb200_last_error() (thread-local);
+ *   - a model handle is bound to the device that was current at create time; not thread-safe.
+ */
+#ifndef ADVB200_H_
+#define ADVB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ADVB200_OK 0
+#define ADVB200_ERR_ARG (-1)
+#define ADVB200_ERR_CUDA (-2)
+#define ADVB200_ERR_UNSUPPORTED (-3)
+
+/* precision of the conv path */
+#define ADVB200_PREC_BF16 0 /* tcgen05/TMEM implicit GEMM, bf16 operands, fp32 accumulate   */
+#define ADVB200_PREC_FP32 1 /* fp32 validation mode (CUDA-core implicit GEMM, no TF32)      */
+
+/* loss kinds for advb200_input_grad */
+#define ADVB200_LOSS_CE_MEAN 0  /* F.cross_entropy(logits, y) mean-reduced: attack.py:31,58        */
+#define ADVB200_LOSS_CW_UNTGT 1 /* c*relu(real-other+kappa), summed: attack.py:114-127 (untargeted) */
+#define ADVB200_LOSS_CW_TGT 2   /* c*relu(other-real+kappa), summed: attack.py:119-121 (targeted)   */
+
+typedef struct advb200_model advb200_model;
+
+const char* advb200_last_error(void);
+int advb200_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Model (torchvision ResNet-50 v1.5, eval mode) — replaces `model(normalize_batch(x))` at
+ * attack.py:30,57,111 and the autograd input-gradient at attack.py:32,59,130.
+ *
+ * conv_w[i]  : fp32 [Cout,Cin,kh,kw] (torchvision layout), i in the canonical order
+ *              conv1, then per block of layer1..layer4: conv1, conv2, conv3, [downsample.0]
+ *              (53 entries).  bn_*[i] are the matching BatchNorm vectors (fp32 [Cout]);
+ *              bn_eps[i] the matching eps (host array).  fc_w fp32 [1000,2048], fc_b [1000].
+ * BatchNorm is folded (eval: running stats) into the packed conv weights at create time.
+ * ------------------------------------------------------------------------------------------ */
+#define ADVB200_NUM_CONVS 53
+int advb200_model_create(const float* const* conv_w, const float* const* bn_gamma,
+                         const float* const* bn_beta, const float* const* bn_mean,
+                         const float* const* bn_var, const float* bn_eps_host, const float* fc_w,
+                         const float* fc_b, int precision, void* stream, advb200_model** out);
+int advb200_model_destroy(advb200_model* m);
+int advb200_model_precision(const advb200_model* m);
+
+/* bytes of caller-owned workspace needed for a batch of n images (forward + input-grad) */
+int64_t advb200_workspace_bytes(const advb200_model* m, int n);
+
+/* logits = model((x-mean)/std).  mean3/std3: fp32 [3] device (normalize_batch, attack.py:10-17).
+ * If score_out != NULL also writes the layer3 detector score per image
+ * (defense_experiments.py:221-257).  If stop_at_layer3 != 0 the forward ends after layer3 and
+ * logits_out may be NULL.  preds_out (int64 [N], may be NULL) = argmax(logits) (first max). */
+int advb200_forward(advb200_model* m, const float* x, const float* mean3, const float* std3, int n,
+                    float* logits_out, int64_t* preds_out, int stop_at_layer3, float* score_out,
+                    void* workspace, int64_t workspace_bytes, void* stream);
+
+/* One forward + input-only backward (no weight gradients; weights are frozen):
+ * grad_x = d loss / d x, fp32 NCHW, through the normalisation (includes the 1/std factor).
+ *   CE_MEAN : loss = mean_n CE(logits_n, y_n); scale = inv_n_global (1/N of the whole batch so a
+ *             sharded batch reproduces the unsharded gradient, attack.py:31)
+ *   CW_*    : loss = sum_n c*f_n (attack.py:119-127; the L2 term is added by advb200_cw_step_f32)
+ * Optional outputs (NULL to skip): logits_out fp32 [N,1000]; preds_out int64 [N];
+ * loss_out fp32 [N] (per-image CE, or f_n for CW); success_out uint8 [N] (CW success flag,
+ * attack.py:121,124; for CE: pred != y). y_cmp is y_true (CE, CW untargeted) or y_target. */
+int advb200_input_grad(advb200_model* m, const float* x, const float* mean3, const float* std3,
+                       const int64_t* y_cmp, int n, int loss_kind, float c, float kappa,
+                       float inv_n_global, float* logits_out, int64_t* preds_out, float* loss_out,
+                       uint8_t* success_out, float* grad_x_out, void* workspace,
+                       int64_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Update kernels (HBM-bound, 128-bit vectorised, bit-exact against the reference arithmetic)
+ * ------------------------------------------------------------------------------------------ */
+
+/* FGSM / PGD step, in place on x_adv (attack.py:33-34 when project==0, attack.py:61-63 when
+ * project!=0):  x1 = x_adv + alpha*sign(g);  [x2 = max(min(x1, x0+eps), x0-eps)];  clamp(.,0,1) */
+int advb200_linf_step_f32(float* x_adv, const float* x_orig, const float* grad, float alpha,
+                          float eps, int64_t n_elems, int project, void* stream);
+
+/* PGD random start (attack.py:50-51): x_adv = clamp(x_orig + noise, 0, 1); noise is supplied by
+ * the caller (torch's generator) so both sides of a parity test draw the same tensor. */
+int advb200_random_start_f32(float* x_adv, const float* x_orig, const float* noise, int64_t n_elems,
+                             void* stream);
+
+/* CW-L2 (attack.py:95-105): x0 = clamp(x,0,1); w = atanh((x0*(1-2e-6)+1e-6)*2-1); m = v = 0;
+ * x_adv = 0.5*(tanh(w)+1); best_adv = x0; best_l2 = +inf; best_success = 0;
+ * l2_partials[N,parts] = per-block partial sums of (x_adv-x0)^2 (fixed-order, deterministic). */
+int advb200_cw_parts(int64_t elems_per_img); /* number of partial sums per image */
+int advb200_cw_init_f32(const float* x, float* x0, float* w, float* m, float* v, float* x_adv,
+                        float* best_adv, float* best_l2, uint8_t* best_success, float* l2_partials,
+                        int n_img, int64_t elems_per_img, void* stream);
+
+/* One CW iteration after advb200_input_grad(CW_*) produced grad_x and success for the current
+ * x_adv (attack.py:126-137 + torch.optim.Adam single-tensor update):
+ *   l2_n = sum(l2_partials_in[n,:])                     (distance of the CURRENT x_adv)
+ *   improved_n = success_n && l2_n < best_l2_n  -> best_l2, best_success, best_adv updated
+ *   g_w = (2*(x_adv-x0) + grad_x) * 0.5 * (1 - tanh(w)^2);  Adam(m, v, w)
+ *   x_adv <- 0.5*(tanh(w)+1) for the NEXT iteration, l2_partials_out <- its distance partials.
+ * step_size = lr/(1-beta1^t) and bc2_sqrt = sqrt(1-beta2^t) are computed in double by the host. */
+int advb200_cw_step_f32(float* w, float* m, float* v, const float* x0, const float* grad_x,
+                        float* x_adv, float* best_adv, float* best_l2, uint8_t* best_success,
+                        const uint8_t* success, const float* l2_partials_in, float* l2_partials_out,
+                        float* l2_out, int n_img, int64_t elems_per_img, float step_size,
+                        float bc2_sqrt, float beta1, float beta2, float adam_eps, void* stream);
+
+/* attack.py:139: out = best_success ? best_adv : x_adv (x_adv already holds 0.5*(tanh(w)+1)
+ * of the post-update w). */
+int advb200_cw_finalize_f32(const float* x_adv, const float* best_adv, const uint8_t* best_success,
+                            float* out, int n_img, int64_t elems_per_img, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Defenses (defense_experiments.py:177-217) — fp32 NCHW planes of h x w
+ * ------------------------------------------------------------------------------------------ */
+/* 3x3 mean, stride 1, zero pad 1, divisor 9 (F.avg_pool2d(x,3,1,1)); bit-exact vs torch CPU */
+int advb200_smooth3x3_f32(const float* x, float* out, int64_t planes, int h, int w, void* stream);
+/* round(clamp(x,0,1)*(levels-1))/(levels-1), round-half-even, true division; bit-exact */
+int advb200_quantize_f32(const float* x, float* out, int64_t n_elems, int levels, void* stream);
+/* defend_input without JPEG: clamp -> smooth -> quantize(16) -> clamp, one pass */
+int advb200_defend_input_f32(const float* x, float* out, int64_t planes, int h, int w, int levels,
+                             void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Evaluation counters (defense_experiments.py:597-637, 809-832)
+ * counters int64 [7] += {clean_correct, attack_success, defense_preproc_success,
+ *                        detector_flags_clean, detector_flags_adv, detector_attack_success, count}
+ * flags_out uint8 [N,6] (optional) receives the per-image booleans in the same order.
+ * ------------------------------------------------------------------------------------------ */
+int advb200_eval_counters(const int64_t* pred_clean, const int64_t* pred_adv, const int64_t* pred_def,
+                          const float* score_clean, const float* score_adv, float threshold,
+                          const int64_t* y_true, int n, int64_t* counters, uint8_t* flags_out,
+                          void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Kernel-level test hooks (used by tests/ and bench.py only)
+ * ------------------------------------------------------------------------------------------ */
+/* NHWC convolution through the same kernels the model uses.
+ *   x     : [N,H,W,Cin]  bf16 (PREC_BF16) or fp32 (PREC_FP32)
+ *   wgt   : fp32 [Cout,Cin,kh,kw];  bias fp32 [Cout] or NULL
+ *   add   : optional residual, same shape/dtype as out;  relu: apply max(.,0)
+ *   dgrad : 0 = forward conv (stride, pad); 1 = data gradient of that conv (x is dY
+ *           [N,Ho,Wo,Cout], out is dX [N,H,W,Cin]); mask (optional, dX-shaped) zeroes out
+ *           where mask<=0.
+ * Supported shapes are the ResNet-50 ones (1x1 s1/s2, 3x3 s1/s2 pad 1; Cin,Cout % 64 == 0). */
+int advb200_test_conv(int precision, const void* x, const float* wgt, const float* bias,
+                      const void* add, const void* mask, void* out, int n, int h, int w, int cin,
+                      int cout, int ksize, int stride, int relu, int dgrad, void* stream);
+
+/* number of kernels launched by this library since load (bench.py's gpu_launches) */
+int64_t advb200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ADVB200_H_ */
