@@ -215,6 +215,7 @@ def native_model(model, precision: Optional[str] = None) -> NativeResNet50:
     per = _CACHE.setdefault(model, {})
     nm = per.get(precision)
     if nm is None:
+        _conv_bn_pairs(model)          # TypeError for anything that is not a ResNet-50
         try:
             dev = next(model.parameters()).device
         except StopIteration:

@@ -44,9 +44,7 @@ struct ConvW {
 
 struct TcOp {
   int bn = 0;
-  int nmaps = 0;
-  CUtensorMap a[4];
-  CUtensorMap b;
+  ConvGemmMaps maps;
   ConvGemmParams p;
 };
 
@@ -70,13 +68,16 @@ inline void tile_shape(int w, int h, int& bw, int& bh, int& bn) {
 }
 inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 
-inline int pick_bn(int gemm_n, long long m_tiles) {
+// n_aux > 0 (residual / mask tiles staged in smem) caps the tile at 128 columns so the ring keeps
+// at least four stages next to the epilogue slots.
+inline int pick_bn(int gemm_n, long long m_tiles, int n_aux) {
   const int cands[3] = {256, 128, 64};
   const double bonus[3] = {1.0, 0.97, 0.80};
   int best = 64;
   double best_score = -1;
   for (int i = 0; i < 3; ++i) {
     if (gemm_n % cands[i]) continue;
+    if (n_aux > 0 && cands[i] > 128) continue;
     const long long tiles = m_tiles * (gemm_n / cands[i]);
     const long long waves = (tiles + kNumSMs - 1) / kNumSMs;
     const double eff = (double)tiles / (double)(waves * kNumSMs) * bonus[i];
@@ -116,10 +117,21 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
   TcOp& t = op.tc;
   ConvGemmParams& p = t.p;
   memset(&p, 0, sizeof p);
+  memset(&t.maps, 0, sizeof t.maps);
   p.kblocks = gemm_k / 64;
-  p.bias = bias; p.add = add; p.mask = mask; p.relu = relu; p.epi = 0;
+  p.bias = bias; p.has_add = add != nullptr; p.has_mask = mask != nullptr; p.relu = relu; p.epi = 0;
   p.cout = gemm_n;
-  p.out = out.p;
+  p.out = nullptr;
+  const int n_aux = p.has_add + p.has_mask;
+  // output-shaped maps (store target, residual, mask): 64-channel boxes over the same pixel box as A
+  auto make_out_maps = [&](TcOp& tt, const Act& o, int sub, int ph, int pw) {
+    Act v = o;
+    const ConvGemmParams& q = tt.p;
+    int rc = make_a(&tt.maps.out, v, sub, ph, pw, q.bw, q.bh, q.bn);
+    if (!rc && add) { v.p = const_cast<bf16*>(add); rc = make_a(&tt.maps.add, v, sub, ph, pw, q.bw, q.bh, q.bn); }
+    if (!rc && mask) { v.p = const_cast<bf16*>(mask); rc = make_a(&tt.maps.mask, v, sub, ph, pw, q.bw, q.bh, q.bn); }
+    return rc;
+  };
 
   if (ksize == 1 && stride == 1) {
     // plain GEMM over all pixels
@@ -128,19 +140,21 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     ADV_CHECK_ARG(m < (1ll << 31), "tc conv: too many pixels");
     p.bw = 128; p.bh = 1; p.bn = 1;
     p.tiles_w = (int)((m + 127) / 128); p.tiles_h = 1; p.tiles_n = 1;
-    t.bn = pick_bn(gemm_n, p.tiles_w);
+    t.bn = pick_bn(gemm_n, p.tiles_w, n_aux);
     p.tiles_c = gemm_n / t.bn;
     p.ntaps = 1;
     p.out_w = (int)m; p.out_h = 1; p.out_n = 1;
-    p.o_sw = gemm_n; p.o_sh = 0; p.o_sn = 0;
-    const uint64_t dims[4] = {(uint64_t)gemm_k, (uint64_t)m, 1, 1};
-    const uint64_t strides[3] = {(uint64_t)gemm_k * 2, (uint64_t)gemm_k * 2 * (uint64_t)m,
-                                 (uint64_t)gemm_k * 2 * (uint64_t)m};
-    const uint32_t box[4] = {64, 128, 1, 1};
-    int rc = make_tmap_bf16(&t.a[0], in.p, 4, dims, strides, box);
-    if (rc) return rc;
-    t.nmaps = 1;
-    rc = make_b(&t.b, t.bn);
+    auto flat_map = [&](CUtensorMap* mp, const void* base, int ch) {
+      const uint64_t dims[4] = {(uint64_t)ch, (uint64_t)m, 1, 1};
+      const uint64_t strides[3] = {(uint64_t)ch * 2, (uint64_t)ch * 2 * (uint64_t)m, (uint64_t)ch * 2 * (uint64_t)m};
+      const uint32_t box[4] = {64, 128, 1, 1};
+      return make_tmap_bf16(mp, base, 4, dims, strides, box);
+    };
+    int rc = flat_map(&t.maps.a[0], in.p, gemm_k);
+    if (!rc) rc = flat_map(&t.maps.out, out.p, gemm_n);
+    if (!rc && add) rc = flat_map(&t.maps.add, add, gemm_n);
+    if (!rc && mask) rc = flat_map(&t.maps.mask, mask, gemm_n);
+    if (!rc) rc = make_b(&t.maps.b, t.bn);
     if (rc) return rc;
     ops.push_back(op);
     return ADVB200_OK;
@@ -152,23 +166,22 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     ADV_CHECK_ARG(stride == 1 || (in.h % 2 == 0 && in.w % 2 == 0), "tc conv fwd: stride 2 needs even sizes");
     tile_shape(out.w, out.h, p.bw, p.bh, p.bn);
     p.tiles_w = cdiv(out.w, p.bw); p.tiles_h = cdiv(out.h, p.bh); p.tiles_n = cdiv(out.n, p.bn);
-    t.bn = pick_bn(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n);
+    t.bn = pick_bn(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, n_aux);
     p.tiles_c = gemm_n / t.bn;
     p.out_w = out.w; p.out_h = out.h; p.out_n = out.n;
-    p.o_sw = gemm_n; p.o_sh = (long long)out.w * gemm_n; p.o_sn = (long long)out.h * out.w * gemm_n;
     int rc;
     if (stride == 1) {
-      rc = make_a(&t.a[0], in, 1, 0, 0, p.bw, p.bh, p.bn);
+      rc = make_a(&t.maps.a[0], in, 1, 0, 0, p.bw, p.bh, p.bn);
       if (rc) return rc;
-      t.nmaps = 1;
     } else {
       for (int ph = 0; ph < 2; ++ph)
         for (int pw = 0; pw < 2; ++pw) {
-          rc = make_a(&t.a[ph * 2 + pw], in, 2, ph, pw, p.bw, p.bh, p.bn);
+          rc = make_a(&t.maps.a[ph * 2 + pw], in, 2, ph, pw, p.bw, p.bh, p.bn);
           if (rc) return rc;
         }
-      t.nmaps = 4;
     }
+    rc = make_out_maps(t, out, 1, 0, 0);
+    if (rc) return rc;
     p.ntaps = 0;
     for (int r = 0; r < ksize; ++r)
       for (int s = 0; s < ksize; ++s) {
@@ -184,7 +197,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
           p.tap_dw[i] = (s == 0) ? -1 : 0;
         }
       }
-    rc = make_b(&t.b, t.bn);
+    rc = make_b(&t.maps.b, t.bn);
     if (rc) return rc;
     ops.push_back(op);
     return ADVB200_OK;
@@ -195,13 +208,12 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     ADV_CHECK_ARG(out.h == in.h && out.w == in.w && in.n == out.n, "tc conv dgrad: shape mismatch");
     tile_shape(out.w, out.h, p.bw, p.bh, p.bn);
     p.tiles_w = cdiv(out.w, p.bw); p.tiles_h = cdiv(out.h, p.bh); p.tiles_n = cdiv(out.n, p.bn);
-    t.bn = pick_bn(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n);
+    t.bn = pick_bn(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, n_aux);
     p.tiles_c = gemm_n / t.bn;
     p.out_w = out.w; p.out_h = out.h; p.out_n = out.n;
-    p.o_sw = gemm_n; p.o_sh = (long long)out.w * gemm_n; p.o_sn = (long long)out.h * out.w * gemm_n;
-    int rc = make_a(&t.a[0], in, 1, 0, 0, p.bw, p.bh, p.bn);
+    int rc = make_a(&t.maps.a[0], in, 1, 0, 0, p.bw, p.bh, p.bn);
+    if (!rc) rc = make_out_maps(t, out, 1, 0, 0);
     if (rc) return rc;
-    t.nmaps = 1;
     p.ntaps = 0;
     for (int r = 0; r < 3; ++r)
       for (int s = 0; s < 3; ++s) {
@@ -209,7 +221,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
         p.tap_map[i] = 0; p.tap_dh[i] = 1 - r; p.tap_dw[i] = 1 - s;   // dX[h,w] += dY[h+1-r, w+1-s] W[r,s]
         p.tap_brow[i] = (r * 3 + s) * gemm_n;
       }
-    rc = make_b(&t.b, t.bn);
+    rc = make_b(&t.maps.b, t.bn);
     if (rc) return rc;
     ops.push_back(op);
     return ADVB200_OK;
@@ -238,18 +250,12 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
       const int sw = out.w / 2, sh = out.h / 2;
       tile_shape(sw, sh, q.bw, q.bh, q.bn);
       q.tiles_w = cdiv(sw, q.bw); q.tiles_h = cdiv(sh, q.bh); q.tiles_n = cdiv(out.n, q.bn);
-      t2.bn = pick_bn(gemm_n, (long long)q.tiles_w * q.tiles_h * q.tiles_n);
+      t2.bn = pick_bn(gemm_n, (long long)q.tiles_w * q.tiles_h * q.tiles_n, n_aux);
       q.tiles_c = gemm_n / t2.bn;
       q.out_w = sw; q.out_h = sh; q.out_n = out.n;
-      q.o_sw = 2ll * gemm_n; q.o_sh = 2ll * out.w * gemm_n; q.o_sn = (long long)out.h * out.w * gemm_n;
-      const long long sub_off = ((long long)ph * out.w + pw) * gemm_n;
-      q.out = reinterpret_cast<bf16*>(out.p) + sub_off;
-      if (add) q.add = add + sub_off;
-      if (mask) q.mask = mask + sub_off;
-      int rc = make_a(&t2.a[0], in, 1, 0, 0, q.bw, q.bh, q.bn);
-      if (rc) return rc;
-      t2.nmaps = 1;
-      rc = make_b(&t2.b, t2.bn);
+      int rc = make_a(&t2.maps.a[0], in, 1, 0, 0, q.bw, q.bh, q.bn);
+      if (!rc) rc = make_out_maps(t2, out, 2, ph, pw);     // (ph, pw) sub-lattice of dX / residual / mask
+      if (!rc) rc = make_b(&t2.maps.b, t2.bn);
       if (rc) return rc;
       ops.push_back(o2);
     }
@@ -270,11 +276,28 @@ int build_simt_op(std::vector<Op>& ops, const float* wm, int ksize, int stride, 
   return ADVB200_OK;
 }
 
-int run_ops(const std::vector<Op>& ops, cudaStream_t st) {
-  for (const Op& op : ops) {
+// optional per-launch timing of the conv kernels (bench.py's roofline leg): CUDA events on the
+// launching stream around every tcgen05 conv launch, summed by advb200_profile_read
+bool g_prof_on = false;
+std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_prof_events;
+
+int run_ops(std::vector<Op>& ops, cudaStream_t st) {
+  for (Op& op : ops) {
     int rc = ADVB200_OK;
     switch (op.kind) {
-      case Op::TC: rc = launch_conv_gemm(op.tc.bn, op.tc.a, op.tc.nmaps, op.tc.b, op.tc.p, st); break;
+      case Op::TC: {
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (g_prof_on) {
+          cudaEventCreate(&e0); cudaEventCreate(&e1);
+          cudaEventRecord(e0, st);
+        }
+        rc = launch_conv_gemm(op.tc.bn, op.tc.maps, op.tc.p, st);
+        if (g_prof_on) {
+          cudaEventRecord(e1, st);
+          g_prof_events.emplace_back(e0, e1);
+        }
+        break;
+      }
       case Op::SIMT: rc = launch_simt_conv(op.simt, st); break;
       case Op::MEMSET: {
         cudaError_t e = cudaMemsetAsync(op.ms_ptr, 0, op.ms_bytes, st);
@@ -398,17 +421,21 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
       p.ntaps = 4; p.kblocks = 1;
       for (int i = 0; i < 4; ++i) { p.tap_map[i] = 0; p.tap_dw[i] = 0; p.tap_dh[i] = i; p.tap_brow[i] = i * 64; }
       p.out_w = 112; p.out_h = 112; p.out_n = n; p.cout = 64;
-      p.o_sw = 64; p.o_sh = 112 * 64; p.o_sn = 112ll * 112 * 64;
-      p.out = m->c1.p; p.bias = w0.shift; p.relu = 1; p.epi = 0;
+      p.bias = w0.shift; p.relu = 1; p.epi = 0;
+      memset(&t.maps, 0, sizeof t.maps);
       const uint64_t dims[4] = {64, 112, 115, (uint64_t)n};
       const uint64_t strides[3] = {128, 128ull * 112, 128ull * 112 * 115};
       const uint32_t box[4] = {64, 16, 8, 1};
-      rc = make_tmap_bf16(&t.a[0], m->t_in.p, 4, dims, strides, box);
-      t.nmaps = 1;
+      rc = make_tmap_bf16(&t.maps.a[0], m->t_in.p, 4, dims, strides, box);
+      {
+        const uint64_t od[4] = {64, 112, 112, (uint64_t)n};
+        const uint64_t os[3] = {128, 128ull * 112, 128ull * 112 * 112};
+        if (!rc) rc = make_tmap_bf16(&t.maps.out, m->c1.p, 4, od, os, box);
+      }
       const uint64_t bd[2] = {64, 256};
       const uint64_t bs[1] = {128};
       const uint32_t bb[2] = {64, 64};
-      if (!rc) rc = make_tmap_bf16(&t.b, w0.b_fwd, 2, bd, bs, bb);
+      if (!rc) rc = make_tmap_bf16(&t.maps.b, w0.b_fwd, 2, bd, bs, bb);
       m->ops_conv1.push_back(op);
     } else {
       rc = build_simt_op(m->ops_conv1, w0.f_fwd, 7, 2, false, m->t_in, m->c1, w0.shift, nullptr, nullptr, 1, 3);
@@ -549,12 +576,13 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
       const uint64_t dims[4] = {64, 112, 112, (uint64_t)n};
       const uint64_t strides[3] = {128, 128ull * 112, 128ull * 112 * 112};
       const uint32_t box[4] = {64, 16, 8, 1};
-      rc = make_tmap_bf16(&t.a[0], m->g_c1, 4, dims, strides, box);
-      t.nmaps = 1;
+      memset(&t.maps, 0, sizeof t.maps);
+      rc = make_tmap_bf16(&t.maps.a[0], m->g_c1, 4, dims, strides, box);
+      t.maps.out = t.maps.a[0];   // unused by the scatter epilogue; keeps the prefetch well-defined
       const uint64_t bd[2] = {64, 256};
       const uint64_t bs[1] = {128};
       const uint32_t bb[2] = {64, 16};
-      if (!rc) rc = make_tmap_bf16(&t.b, m->conv[0].b_dgrad, 2, bd, bs, bb);
+      if (!rc) rc = make_tmap_bf16(&t.maps.b, m->conv[0].b_dgrad, 2, bd, bs, bb);
       m->ops_conv1_bwd.push_back(op);
     } else {
       Act gy = m->c1; gy.p = m->g_c1;
@@ -604,10 +632,7 @@ int forward_impl(advb200_model* m, const float* x, const float* mean3, const flo
   else rc = launch_avgpool_fwd<float>((const float*)m->l4out.p, m->feat, n, 49, kFeat, st);
   if (rc) return rc;
   // fc forward: logits = feat * W^T + b   (fp32 in both modes)
-  SimtConvParams f{};
-  f.in = m->feat; f.wm = m->fc_wt; f.out = m->logits; f.bias = m->fc_b;
-  f.n = n; f.hi = f.wi = f.ho = f.wo = 1; f.ci = kFeat; f.co = kClasses; f.kh = f.kw = 1; f.stride = 1;
-  return launch_simt_conv(f, st);
+  return launch_fc_nt(m->feat, m->fc_w, m->fc_b, m->logits, n, kClasses, kFeat, st);
 }
 
 }  // namespace
@@ -693,6 +718,27 @@ int advb200_model_create(const float* const* conv_w, const float* const* bn_gamm
   return ADVB200_OK;
 }
 
+int advb200_profile_enable(int on) {
+  g_prof_on = on != 0;
+  return ADVB200_OK;
+}
+
+int advb200_profile_read(double* conv_ms, int64_t* conv_launches) {
+  ADV_CHECK_ARG(conv_ms && conv_launches, "profile_read: null argument");
+  double total = 0.0;
+  for (auto& pr : g_prof_events) {
+    ADV_CHECK_CUDA(cudaEventSynchronize(pr.second));
+    float ms = 0.f;
+    ADV_CHECK_CUDA(cudaEventElapsedTime(&ms, pr.first, pr.second));
+    total += ms;
+    cudaEventDestroy(pr.first); cudaEventDestroy(pr.second);
+  }
+  *conv_ms = total;
+  *conv_launches = (int64_t)g_prof_events.size();
+  g_prof_events.clear();
+  return ADVB200_OK;
+}
+
 int advb200_model_destroy(advb200_model* m) {
   if (!m) return ADVB200_OK;
   for (void* p : m->owned) cudaFree(p);
@@ -741,10 +787,7 @@ int advb200_input_grad(advb200_model* m, const float* x, const float* mean3, con
                              loss_out, success_out, st)))
     return rc;
   // fc input gradient: dfeat = dlogits * W
-  SimtConvParams f{};
-  f.in = m->dlogits; f.wm = m->fc_w; f.out = m->dfeat;
-  f.n = n; f.hi = f.wi = f.ho = f.wo = 1; f.ci = kClasses; f.co = kFeat; f.kh = f.kw = 1; f.stride = 1;
-  if ((rc = launch_simt_conv(f, st))) return rc;
+  if ((rc = launch_fc_nt(m->dlogits, m->fc_wt, nullptr, m->dfeat, n, kFeat, kClasses, st))) return rc;
   if (tc) rc = launch_avgpool_bwd<bf16>(m->dfeat, (const bf16*)m->l4out.p, (bf16*)m->g_top, n, 49, kFeat, st);
   else rc = launch_avgpool_bwd<float>(m->dfeat, (const float*)m->l4out.p, (float*)m->g_top, n, 49, kFeat, st);
   if (rc) return rc;

@@ -1,6 +1,8 @@
 // Non-GEMM layers of the ResNet-50 attack path.  See layers.cuh for the contracts.
 #include "layers.cuh"
 
+#include <type_traits>
+
 namespace advb200 {
 
 namespace {
@@ -16,33 +18,44 @@ template <> __device__ __forceinline__ float from_f<float>(float v) { return v; 
 template <> __device__ __forceinline__ bf16 from_f<bf16>(float v) { return __float2bfloat16_rn(v); }
 
 // ---------------------------------------------------------------- input preparation
+// one block per output row (n, hp): the two source image rows (3 channels each) are read
+// coalesced into shared memory, normalised once, then scattered into the 64-channel hcol pixels
 __global__ void __launch_bounds__(kT)
 prep_hcol_kernel(const float* __restrict__ x, const float* __restrict__ mean3, const float* __restrict__ std3,
-                 bf16* __restrict__ out, long long total) {
-  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= total) return;
-  const int j8 = (int)(t & 7);
-  long long r = t >> 3;
-  const int wo = (int)(r % 112); r /= 112;
-  const int hp = (int)(r % 115);
-  const int n = (int)(r / 115);
-  const int u = j8 >> 1, q0 = (j8 & 1) * 8;
-  __align__(16) bf16 v[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int q = q0 + i;
-    float val = 0.f;
-    if (q < 12) {
-      const int c = q % 3, pw = (q / 3) & 1, ph = q / 6;
-      const int row = 2 * (hp - 2) + ph, col = 2 * (wo - 2 + u) + pw;
-      if (row >= 0 && row < 224 && col >= 0 && col < 224) {
-        const float px = __ldg(x + (((long long)n * 3 + c) * 224 + row) * 224 + col);
-        val = __fdiv_rn(__fsub_rn(px, __ldg(mean3 + c)), __ldg(std3 + c));   // attack.py:17
-      }
+                 bf16* __restrict__ out) {
+  __shared__ float src[2][3][224 + 8];     // [ph][c][col + 4]: cols -4..227 so the halo reads stay in range
+  const int hp = blockIdx.x % 115;
+  const int n = blockIdx.x / 115;
+  for (int i = threadIdx.x; i < 2 * 3 * 232; i += kT) {
+    const int col = i % 232 - 4;
+    const int c = (i / 232) % 3;
+    const int ph = i / (232 * 3);
+    const int row = 2 * (hp - 2) + ph;
+    float v = 0.f;
+    if (row >= 0 && row < 224 && col >= 0 && col < 224) {
+      const float px = __ldg(x + (((long long)n * 3 + c) * 224 + row) * 224 + col);
+      v = __fdiv_rn(__fsub_rn(px, __ldg(mean3 + c)), __ldg(std3 + c));   // attack.py:17
     }
-    v[i] = __float2bfloat16_rn(val);
+    src[ph][c][col + 4] = v;
   }
-  *reinterpret_cast<uint4*>(out + t * 8) = *reinterpret_cast<const uint4*>(v);
+  __syncthreads();
+  bf16* orow = out + ((long long)n * 115 + hp) * 112 * 64;
+  for (int t = threadIdx.x; t < 112 * 8; t += kT) {
+    const int j8 = t & 7, wo = t >> 3;
+    const int u = j8 >> 1, q0 = (j8 & 1) * 8;
+    __align__(16) bf16 v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int q = q0 + i;
+      float val = 0.f;
+      if (q < 12) {
+        const int c = q % 3, pw = (q / 3) & 1, ph = q / 6;
+        val = src[ph][c][2 * (wo - 2 + u) + pw + 4];
+      }
+      v[i] = __float2bfloat16_rn(val);
+    }
+    *reinterpret_cast<uint4*>(orow + (long long)t * 8) = *reinterpret_cast<const uint4*>(v);
+  }
 }
 
 __global__ void __launch_bounds__(kT)
@@ -127,6 +140,137 @@ maxpool_bwd_kernel(const T* __restrict__ gout, const uint8_t* __restrict__ idx, 
     }
   }
   gin[t] = from_f<T>(g);
+}
+
+// ---- bf16, 8 channels (16 bytes) per thread ------------------------------------------------
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { f[2 * i] = __uint_as_float(w[i] << 16); f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u); }
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+    w[i] = *reinterpret_cast<uint32_t*>(&h);
+  }
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+__global__ void __launch_bounds__(kT)
+maxpool_fwd_bf16x8_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, uint8_t* __restrict__ idx, int hi,
+                          int wi, int ho, int wo, int c8, long long total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // (n, oh, ow, c8)
+  if (t >= total) return;
+  const int cg = (int)(t % c8);
+  long long r = t / c8;
+  const int ow = (int)(r % wo); r /= wo;
+  const int oh = (int)(r % ho);
+  const long long n = r / ho;
+  float best[8]; int pos[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { best[i] = -INFINITY; pos[i] = 0; }
+#pragma unroll
+  for (int dr = 0; dr < 3; ++dr) {
+    const int ih = 2 * oh - 1 + dr;
+    if (ih < 0 || ih >= hi) continue;
+#pragma unroll
+    for (int ds = 0; ds < 3; ++ds) {
+      const int iw = 2 * ow - 1 + ds;
+      if (iw < 0 || iw >= wi) continue;
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(in + (((n * hi + ih) * wi + iw) * c8 + cg) * 8));
+      float f[8];
+      unpack8(u, f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (f[i] > best[i]) { best[i] = f[i]; pos[i] = dr * 3 + ds; }
+    }
+  }
+  *reinterpret_cast<uint4*>(out + t * 8) = pack8(best);
+  uint32_t lo = 0, hi32 = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    lo |= (uint32_t)(best[i] > 0.f ? pos[i] : 255) << (8 * i);
+    hi32 |= (uint32_t)(best[4 + i] > 0.f ? pos[4 + i] : 255) << (8 * i);
+  }
+  *reinterpret_cast<uint2*>(idx + t * 8) = make_uint2(lo, hi32);
+}
+
+// one thread = a 2x2 input patch (rows 2a,2a+1; cols 2b,2b+1) x 8 channels: the four windows that can
+// route gradient into the patch, (a..a+1, b..b+1), are each loaded once (all loads issued up front)
+__global__ void __launch_bounds__(kT)
+maxpool_bwd_bf16x8_kernel(const bf16* __restrict__ gout, const uint8_t* __restrict__ idx, bf16* __restrict__ gin,
+                          int hi, int wi, int ho, int wo, int c8, long long total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // (n, a, b, c8)
+  if (t >= total) return;
+  const int cg = (int)(t % c8);
+  long long r = t / c8;
+  const int pb = (int)(r % (wi / 2)); r /= (wi / 2);
+  const int pa = (int)(r % (hi / 2));
+  const long long n = r / (hi / 2);
+  uint2 ix[2][2];
+  uint4 gv[2][2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int oh = pa + i, ow = pb + j;
+      if (oh < ho && ow < wo) {
+        const long long o = (((n * ho + oh) * wo + ow) * c8 + cg) * 8;
+        ix[i][j] = __ldg(reinterpret_cast<const uint2*>(idx + o));
+        gv[i][j] = __ldg(reinterpret_cast<const uint4*>(gout + o));
+      } else {
+        ix[i][j] = make_uint2(0xffffffffu, 0xffffffffu);
+        gv[i][j] = make_uint4(0, 0, 0, 0);
+      }
+    }
+  float gf[2][2][8];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 2; ++j) unpack8(gv[i][j], gf[i][j]);
+#pragma unroll
+  for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+    for (int dx = 0; dx < 2; ++dx) {
+      const int ih = 2 * pa + dy, iw = 2 * pb + dx;
+      float g[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = 0.f;
+      // windows containing (ih, iw): oh in {ih>>1 .. (ih+1)>>1}, likewise ow  (same order as the scalar kernel)
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int oh = pa + i, ow = pb + j;
+          if (oh < (ih >> 1) || oh > ((ih + 1) >> 1) || ow < (iw >> 1) || ow > ((iw + 1) >> 1)) continue;
+          const uint32_t want = (uint32_t)((ih - (2 * oh - 1)) * 3 + (iw - (2 * ow - 1)));
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            if (((ix[i][j].x >> (8 * k)) & 0xffu) == want) g[k] += gf[i][j][k];
+            if (((ix[i][j].y >> (8 * k)) & 0xffu) == want) g[4 + k] += gf[i][j][4 + k];
+          }
+        }
+      *reinterpret_cast<uint4*>(gin + (((n * hi + ih) * wi + iw) * c8 + cg) * 8) = pack8(g);
+    }
+}
+
+__global__ void __launch_bounds__(kT)
+avgpool_bwd_bf16x8_kernel(const float* __restrict__ dfeat, const bf16* __restrict__ act, bf16* __restrict__ gact,
+                          int hw, int c8, long long total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // (n, p, c8)
+  if (t >= total) return;
+  const int cg = (int)(t % c8);
+  const long long n = t / ((long long)hw * c8);
+  const float4 d0 = __ldg(reinterpret_cast<const float4*>(dfeat + (n * c8 + cg) * 8));
+  const float4 d1 = __ldg(reinterpret_cast<const float4*>(dfeat + (n * c8 + cg) * 8) + 1);
+  const float d[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+  float a[8], g[8];
+  unpack8(__ldg(reinterpret_cast<const uint4*>(act + t * 8)), a);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) g[i] = a[i] > 0.f ? d[i] / (float)hw : 0.f;
+  *reinterpret_cast<uint4*>(gact + t * 8) = pack8(g);
 }
 
 // ---------------------------------------------------------------- global average pool
@@ -375,9 +519,8 @@ __global__ void f32_to_bf16_kernel(const float* __restrict__ in, bf16* __restric
 }  // namespace
 
 int launch_prep_hcol(const float* x, const float* mean3, const float* std3, bf16* out, int n, cudaStream_t st) {
-  const long long total = (long long)n * 115 * 112 * 8;
-  if (!total) return ADVB200_OK;
-  prep_hcol_kernel<<<nblocks(total), kT, 0, st>>>(x, mean3, std3, out, total);
+  if (!n) return ADVB200_OK;
+  prep_hcol_kernel<<<n * 115, kT, 0, st>>>(x, mean3, std3, out);
   ADV_LAUNCHED();
   return ADVB200_OK;
 }
@@ -403,6 +546,13 @@ int launch_maxpool_fwd(const T* in, T* out, uint8_t* idx, int n, int hi, int wi,
   const int ho = (hi + 2 - 3) / 2 + 1, wo = (wi + 2 - 3) / 2 + 1;
   const long long total = (long long)n * ho * wo * c;
   if (!total) return ADVB200_OK;
+  if constexpr (std::is_same<T, bf16>::value) {
+    if (c % 8 == 0) {
+      maxpool_fwd_bf16x8_kernel<<<nblocks(total / 8), kT, 0, st>>>(in, out, idx, hi, wi, ho, wo, c / 8, total / 8);
+      ADV_LAUNCHED();
+      return ADVB200_OK;
+    }
+  }
   maxpool_fwd_kernel<T><<<nblocks(total), kT, 0, st>>>(in, out, idx, hi, wi, ho, wo, c, total);
   ADV_LAUNCHED();
   return ADVB200_OK;
@@ -413,6 +563,13 @@ int launch_maxpool_bwd(const T* gout, const uint8_t* idx, T* gin, int n, int hi,
   const int ho = (hi + 2 - 3) / 2 + 1, wo = (wi + 2 - 3) / 2 + 1;
   const long long total = (long long)n * hi * wi * c;
   if (!total) return ADVB200_OK;
+  if constexpr (std::is_same<T, bf16>::value) {
+    if (c % 8 == 0 && hi % 2 == 0 && wi % 2 == 0) {
+      maxpool_bwd_bf16x8_kernel<<<nblocks(total / 32), kT, 0, st>>>(gout, idx, gin, hi, wi, ho, wo, c / 8, total / 32);
+      ADV_LAUNCHED();
+      return ADVB200_OK;
+    }
+  }
   maxpool_bwd_kernel<T><<<nblocks(total), kT, 0, st>>>(gout, idx, gin, hi, wi, ho, wo, c, total);
   ADV_LAUNCHED();
   return ADVB200_OK;
@@ -429,6 +586,13 @@ template <typename T>
 int launch_avgpool_bwd(const float* dfeat, const T* act, T* gact, int n, int hw, int c, cudaStream_t st) {
   const long long total = (long long)n * hw * c;
   if (!total) return ADVB200_OK;
+  if constexpr (std::is_same<T, bf16>::value) {
+    if (c % 8 == 0) {
+      avgpool_bwd_bf16x8_kernel<<<nblocks(total / 8), kT, 0, st>>>(dfeat, act, gact, hw, c / 8, total / 8);
+      ADV_LAUNCHED();
+      return ADVB200_OK;
+    }
+  }
   avgpool_bwd_kernel<T><<<nblocks(total), kT, 0, st>>>(dfeat, act, gact, hw, c, total);
   ADV_LAUNCHED();
   return ADVB200_OK;

@@ -99,7 +99,64 @@ simt_conv_kernel(const SimtConvParams p) {
   }
 }
 
+// out[m, n] = sum_k a[m, k] * b[n, k] (+ bias[n]) — both operands K-contiguous (fp32 classifier head)
+__global__ void __launch_bounds__(256)
+fc_nt_kernel(const float* __restrict__ a, const float* __restrict__ b, const float* __restrict__ bias,
+             float* __restrict__ out, int m_total, int n_total, int k_total) {
+  __shared__ float As[32][33];
+  __shared__ float Bs[64][33];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;          // 16 x 16 threads, 2 x 4 outputs each
+  const int m0 = blockIdx.x * 32, n0 = blockIdx.y * 64;
+  float acc[2][4] = {};
+  for (int k0 = 0; k0 < k_total; k0 += 32) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int idx = tid + i * 256, r = idx >> 5, kk = idx & 31;
+      const int m = m0 + r, k = k0 + kk;
+      As[r][kk] = (m < m_total && k < k_total) ? __ldg(a + (long long)m * k_total + k) : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int idx = tid + i * 256, r = idx >> 5, kk = idx & 31;
+      const int n = n0 + r, k = k0 + kk;
+      Bs[r][kk] = (n < n_total && k < k_total) ? __ldg(b + (long long)n * k_total + k) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 32; ++kk) {
+      const float a0 = As[ty * 2][kk], a1 = As[ty * 2 + 1][kk];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float bv = Bs[tx * 4 + j][kk];
+        acc[0][j] = fmaf(a0, bv, acc[0][j]);
+        acc[1][j] = fmaf(a1, bv, acc[1][j]);
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int m = m0 + ty * 2 + i;
+    if (m >= m_total) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n < n_total) out[(long long)m * n_total + n] = acc[i][j] + (bias ? __ldg(bias + n) : 0.f);
+    }
+  }
+}
+
 }  // namespace
+
+int launch_fc_nt(const float* a, const float* b, const float* bias, float* out, int m, int n, int k,
+                 cudaStream_t stream) {
+  if (m == 0) return ADVB200_OK;
+  dim3 grid((unsigned)((m + 31) / 32), (unsigned)((n + 63) / 64));
+  fc_nt_kernel<<<grid, 256, 0, stream>>>(a, b, bias, out, m, n, k);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
 
 int launch_simt_conv(const SimtConvParams& p, cudaStream_t stream) {
   const long long m_total = (long long)p.n * p.ho * p.wo;

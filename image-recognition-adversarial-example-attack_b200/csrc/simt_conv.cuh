@@ -19,4 +19,8 @@ struct SimtConvParams {
 
 int launch_simt_conv(const SimtConvParams& p, cudaStream_t stream);
 
+// out[m, n] = sum_k a[m, k] * b[n, k] (+ bias[n]); fp32, both operands K-contiguous
+int launch_fc_nt(const float* a, const float* b, const float* bias, float* out, int m, int n, int k,
+                 cudaStream_t stream);
+
 }  // namespace advb200

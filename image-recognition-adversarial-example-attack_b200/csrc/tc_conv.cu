@@ -24,17 +24,16 @@ constexpr int kATileBytes = kBlockM * kBlockK * 2;   // 16 KB
 constexpr int kThreads = 192;
 constexpr int kEpiWarp0 = 2;
 
+constexpr int kMaxStages = 8;
+constexpr int kMaxAuxDepth = 8;
+constexpr int kSmemBudget = 232448;            // 227 KB opt-in limit per CTA
+constexpr int kSubTileBytes = kBlockM * 128;   // 128 rows x 64 bf16: one epilogue sub-tile
+constexpr int kBarrierBytes = 512;
+
 template <int BN> struct Cfg {
   static constexpr int kBTileBytes = BN * kBlockK * 2;
   static constexpr int kStageBytes = kATileBytes + kBTileBytes;
-  static constexpr int kStages = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
   static constexpr int kTmemCols = (2 * BN < 32) ? 32 : 2 * BN;  // two accumulators
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
-};
-
-struct TmapPack {
-  CUtensorMap a[4];
-  CUtensorMap b;
 };
 
 // ---------------------------------------------------------------- PTX wrappers
@@ -150,19 +149,58 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 __device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
 
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void* src, int c0, int c1, int c2,
+                                             int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
 // ---------------------------------------------------------------- the kernel
+struct TileCoord { int w0, h0, n0, c0; };
+__device__ __forceinline__ TileCoord tile_coord(const ConvGemmParams& p, int tile, int bn_cols) {
+  TileCoord t;
+  const int tc = tile % p.tiles_c; tile /= p.tiles_c;
+  const int tw = tile % p.tiles_w; tile /= p.tiles_w;
+  const int th = tile % p.tiles_h; tile /= p.tiles_h;
+  t.w0 = tw * p.bw; t.h0 = th * p.bh; t.n0 = tile * p.bn; t.c0 = tc * bn_cols;
+  return t;
+}
+
 template <int BN>
 __global__ void __launch_bounds__(kThreads, 1)
-conv_gemm_kernel(const __grid_constant__ TmapPack maps, const __grid_constant__ ConvGemmParams p) {
+conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constant__ ConvGemmParams p) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  const int n_aux = (p.has_add ? 1 : 0) + (p.has_mask ? 1 : 0);
+  const int aux_depth = p.aux_depth;                        // aux ring slots (sub-tiles of prefetch)
+  const int aux_slot_bytes = kSubTileBytes * n_aux;
+  uint8_t* out_smem = smem + p.stages * C::kStageBytes;     // 2 x 16 KB output staging
+  uint8_t* aux_smem = out_smem + ((BN == 16) ? 0 : 2 * kSubTileBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(aux_smem + aux_depth * aux_slot_bytes);
   uint64_t* full_bar = bars;
-  uint64_t* empty_bar = bars + C::kStages;
-  uint64_t* tfull_bar = bars + 2 * C::kStages;
+  uint64_t* empty_bar = bars + kMaxStages;
+  uint64_t* tfull_bar = bars + 2 * kMaxStages;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* aux_bar = tempty_bar + 2;                       // kMaxAuxDepth entries
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_bar + kMaxAuxDepth);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -170,8 +208,10 @@ conv_gemm_kernel(const __grid_constant__ TmapPack maps, const __grid_constant__ 
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < 4; ++i) prefetch_tmap(&maps.a[i]);
     prefetch_tmap(&maps.b);
-    for (int s = 0; s < C::kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    prefetch_tmap(&maps.out);
+    for (int s = 0; s < kMaxStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], 4); }
+    for (int a = 0; a < kMaxAuxDepth; ++a) mbar_init(&aux_bar[a], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -188,6 +228,7 @@ conv_gemm_kernel(const __grid_constant__ TmapPack maps, const __grid_constant__ 
 
   const int total_tiles = p.tiles_w * p.tiles_h * p.tiles_n * p.tiles_c;
   const int ksteps = p.ntaps * p.kblocks;
+  const int nstages = p.stages;
 
   if (warp == 0) {
     // =========================== TMA producer ===========================
@@ -195,24 +236,19 @@ conv_gemm_kernel(const __grid_constant__ TmapPack maps, const __grid_constant__ 
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        int t = tile;
-        const int tc = t % p.tiles_c; t /= p.tiles_c;
-        const int tw = t % p.tiles_w; t /= p.tiles_w;
-        const int th = t % p.tiles_h; t /= p.tiles_h;
-        const int tn = t;
-        const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn, c0 = tc * BN;
+        const TileCoord tc = tile_coord(p, tile, BN);
         for (int tap = 0; tap < p.ntaps; ++tap) {
           const CUtensorMap* ma = &maps.a[p.tap_map[tap]];
-          const int cw = w0 + p.tap_dw[tap], ch = h0 + p.tap_dh[tap];
-          const int brow = p.tap_brow[tap] + c0;
+          const int cw = tc.w0 + p.tap_dw[tap], ch = tc.h0 + p.tap_dh[tap];
+          const int brow = p.tap_brow[tap] + tc.c0;
           for (int kb = 0; kb < p.kblocks; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1);
             uint8_t* sa = smem + stage * C::kStageBytes;
             uint8_t* sb = sa + kATileBytes;
             mbar_expect_tx(&full_bar[stage], C::kStageBytes);
-            tma_load_4d(ma, &full_bar[stage], sa, kb * kBlockK, cw, ch, n0);
+            tma_load_4d(ma, &full_bar[stage], sa, kb * kBlockK, cw, ch, tc.n0);
             tma_load_2d(&maps.b, &full_bar[stage], sb, kb * kBlockK, brow);
-            if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+            if (++stage == nstages) { stage = 0; phase ^= 1; }
           }
         }
       }
@@ -244,7 +280,7 @@ conv_gemm_kernel(const __grid_constant__ TmapPack maps, const __grid_constant__ 
                       (ks | k) != 0 ? 1u : 0u);
           }
           umma_commit(&empty_bar[stage]);
-          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+          if (++stage == nstages) { stage = 0; phase ^= 1; }
         }
         umma_commit(&tfull_bar[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
@@ -256,27 +292,21 @@ conv_gemm_kernel(const __grid_constant__ TmapPack maps, const __grid_constant__ 
     const int row = quad * 32 + lane;            // accumulator row == pixel within the tile
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      int t = tile;
-      const int tc = t % p.tiles_c; t /= p.tiles_c;
-      const int tw = t % p.tiles_w; t /= p.tiles_w;
-      const int th = t % p.tiles_h; t /= p.tiles_h;
-      const int tn = t;
-      const int wi = row % p.bw, hi = (row / p.bw) % p.bh, ni = row / (p.bw * p.bh);
-      const int w = tw * p.bw + wi, h = th * p.bh + hi, n = tn * p.bn + ni;
-      const bool valid = (w < p.out_w) && (h < p.out_h) && (n < p.out_n);
-      const long long off = (long long)n * p.o_sn + (long long)h * p.o_sh + (long long)w * p.o_sw;
 
-      mbar_wait(&tfull_bar[acc], acc_phase);
-      tc_fence_after();
-      const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN);
-
-      if constexpr (BN == 16) {
-        // conv1 input gradient: columns q = (ph*2+pw)*3 + c of the space-to-depth pixel (h, w)
+    if constexpr (BN == 16) {
+      // conv1 input gradient: columns q = (ph*2+pw)*3 + c of the space-to-depth pixel (h, w);
+      // fp32 scatter into the NCHW image gradient, divided by the normalisation std
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const TileCoord tc = tile_coord(p, tile, BN);
+        const int wi = row % p.bw, hi = (row / p.bw) % p.bh, ni = row / (p.bw * p.bh);
+        const int w = tc.w0 + wi, h = tc.h0 + hi, n = tc.n0 + ni;
+        const bool valid = (w < p.out_w) && (h < p.out_h) && (n < p.out_n);
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
         uint32_t v[32];
-        tmem_ld16(taddr0, v);
+        tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN), v);
         tmem_ld_wait();
-        if (valid && p.epi == 1) {
+        if (valid) {
           float* g = reinterpret_cast<float*>(p.out);
 #pragma unroll
           for (int q = 0; q < 12; ++q) {
@@ -285,30 +315,79 @@ conv_gemm_kernel(const __grid_constant__ TmapPack maps, const __grid_constant__ 
             g[o] = __fdiv_rn(__uint_as_float(v[q]), __ldg(p.std_dev + c));
           }
         }
-      } else {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    } else {
+      // Sub-tiles of 64 channels: TMEM -> registers -> (bias, residual, ReLU, mask) -> swizzled smem
+      // staging -> TMA store.  Residual / mask tiles arrive by TMA into the same slot, issued by the
+      // epilogue leader two sub-tiles ahead.
+      constexpr int kSub = BN / 64;
+      const bool leader = threadIdx.x == kEpiWarp0 * 32;
+      const bool has_aux = n_aux > 0;
+      const uint32_t out0 = smem_u32(out_smem);
+      const uint32_t aux0 = smem_u32(aux_smem);
+      const uint32_t add_off = 0;
+      const uint32_t mask_off = p.has_add ? kSubTileBytes : 0;
+      const uint32_t row_off = (uint32_t)row * 128u;
+      const uint32_t sw = (uint32_t)(row & 7);
+
+      // aux prefetch cursor (leader only): runs aux_depth sub-tiles ahead of the consumer
+      int pf_tile = blockIdx.x, pf_j = 0;
+      auto issue_aux = [&](int slot) {
+        const TileCoord tc = tile_coord(p, pf_tile, BN);
+        uint8_t* base = aux_smem + slot * aux_slot_bytes;
+        mbar_expect_tx(&aux_bar[slot], (uint32_t)aux_slot_bytes);
+        if (p.has_add) tma_load_4d(&maps.add, &aux_bar[slot], base + add_off, tc.c0 + 64 * pf_j, tc.w0, tc.h0, tc.n0);
+        if (p.has_mask) tma_load_4d(&maps.mask, &aux_bar[slot], base + mask_off, tc.c0 + 64 * pf_j, tc.w0, tc.h0, tc.n0);
+        if (++pf_j == kSub) { pf_j = 0; pf_tile += gridDim.x; }
+      };
+      if (leader && has_aux) {
+        if (p.has_add) prefetch_tmap(&maps.add);
+        if (p.has_mask) prefetch_tmap(&maps.mask);
+        for (int s = 0; s < aux_depth; ++s)
+          if (pf_tile < total_tiles) issue_aux(s);
+      }
+      int aslot = 0;            // aux ring position of the sub-tile being consumed
+      uint32_t aphase = 0;
+
+      uint32_t e = 0;   // running sub-tile counter: output staging slot = e & 1
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const TileCoord tc = tile_coord(p, tile, BN);
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN);
 #pragma unroll 1
-        for (int j = 0; j < BN / 32; ++j) {
-          uint32_t v[32];
-          tmem_ld32(taddr0 + (uint32_t)(j * 32), v);
-          tmem_ld_wait();
-          const int col0 = tc * BN + j * 32;
-          if (valid && col0 < p.cout) {
+        for (int j = 0; j < kSub; ++j, ++e) {
+          const int slot = (int)(e & 1u);
+          const uint32_t obase = out0 + (uint32_t)(slot * kSubTileBytes);
+          const uint32_t abase = aux0 + (uint32_t)(aslot * aux_slot_bytes);
+          // the TMA store issued from this staging slot two sub-tiles ago must have finished reading it
+          if (leader) bulk_wait_read<1>();
+          epi_bar();
+          if (has_aux) mbar_wait(&aux_bar[aslot], aphase);
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf) {
+            uint32_t v[32];
+            tmem_ld32(taddr0 + (uint32_t)(j * 64 + hf * 32), v);
+            tmem_ld_wait();
             float f[32];
 #pragma unroll
             for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
             if (p.bias) {
-              const float4* b4 = reinterpret_cast<const float4*>(p.bias + col0);
+              const float4* b4 = reinterpret_cast<const float4*>(p.bias + tc.c0 + j * 64 + hf * 32);
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
                 const float4 b = __ldg(b4 + i);
                 f[4 * i] += b.x; f[4 * i + 1] += b.y; f[4 * i + 2] += b.z; f[4 * i + 3] += b.w;
               }
             }
-            if (p.add) {
-              const uint4* a4 = reinterpret_cast<const uint4*>(p.add + off + col0);
+            if (p.has_add) {
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
-                const uint4 a = __ldg(a4 + i);
+                const uint4 a = lds128(abase + add_off + row_off + ((((uint32_t)(hf * 4 + i)) ^ sw) << 4));
                 f[8 * i] += bf16_lo(a.x); f[8 * i + 1] += bf16_hi(a.x);
                 f[8 * i + 2] += bf16_lo(a.y); f[8 * i + 3] += bf16_hi(a.y);
                 f[8 * i + 4] += bf16_lo(a.z); f[8 * i + 5] += bf16_hi(a.z);
@@ -319,11 +398,10 @@ conv_gemm_kernel(const __grid_constant__ TmapPack maps, const __grid_constant__ 
 #pragma unroll
               for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
             }
-            if (p.mask) {
-              const uint4* m4 = reinterpret_cast<const uint4*>(p.mask + off + col0);
+            if (p.has_mask) {
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
-                const uint4 m = __ldg(m4 + i);
+                const uint4 m = lds128(abase + mask_off + row_off + ((((uint32_t)(hf * 4 + i)) ^ sw) << 4));
                 const uint32_t mm[4] = {m.x, m.y, m.z, m.w};
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
@@ -332,7 +410,6 @@ conv_gemm_kernel(const __grid_constant__ TmapPack maps, const __grid_constant__ 
                 }
               }
             }
-            uint4* o4 = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + off + col0);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               uint4 o;
@@ -340,16 +417,25 @@ conv_gemm_kernel(const __grid_constant__ TmapPack maps, const __grid_constant__ 
               o.y = pack_bf16x2(f[8 * i + 2], f[8 * i + 3]);
               o.z = pack_bf16x2(f[8 * i + 4], f[8 * i + 5]);
               o.w = pack_bf16x2(f[8 * i + 6], f[8 * i + 7]);
-              o4[i] = o;
+              sts128(obase + row_off + ((((uint32_t)(hf * 4 + i)) ^ sw) << 4), o);
             }
           }
+          fence_async_smem();          // generic-proxy smem writes -> visible to the TMA store
+          epi_bar();
+          if (leader) {
+            tma_store_4d(&maps.out, out_smem + slot * kSubTileBytes, tc.c0 + 64 * j, tc.w0, tc.h0, tc.n0);
+            bulk_commit();
+            if (has_aux && pf_tile < total_tiles) issue_aux(aslot);   // this aux slot is free again
+          }
+          if (has_aux && ++aslot == aux_depth) { aslot = 0; aphase ^= 1u; }
         }
+        // accumulator drained: hand the TMEM buffer back to the MMA warp
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
-      // accumulator drained: hand the TMEM buffer back to the MMA warp
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      if (leader) bulk_wait_read<0>();
     }
   }
 
@@ -364,32 +450,41 @@ conv_gemm_kernel(const __grid_constant__ TmapPack maps, const __grid_constant__ 
 }
 
 template <int BN>
-int launch_impl(const TmapPack& maps, const ConvGemmParams& p, cudaStream_t stream) {
+int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream) {
   using C = Cfg<BN>;
   static bool configured = false;
   if (!configured) {
     ADV_CHECK_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        C::kSmemBytes));
+                                        kSmemBudget));
     configured = true;
   }
   const long long total = (long long)p.tiles_w * p.tiles_h * p.tiles_n * p.tiles_c;
   if (total <= 0) return ADVB200_OK;
+  const int n_aux = (p.has_add ? 1 : 0) + (p.has_mask ? 1 : 0);
+  const int out_bytes = (BN == 16) ? 0 : 2 * kSubTileBytes;
+  // aux ring: as deep as possible (HBM latency ~ two tiles of epilogue) while the operand ring keeps
+  // at least three stages
+  int depth = n_aux ? kMaxAuxDepth : 0, stages = 0;
+  for (;; --depth) {
+    stages = (kSmemBudget - 1024 - kBarrierBytes - out_bytes - depth * n_aux * kSubTileBytes) / C::kStageBytes;
+    if (!n_aux || stages >= (n_aux == 1 ? 4 : 3) || depth <= 2) break;
+  }
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2) return fail(ADVB200_ERR_ARG, "conv_gemm: tile configuration does not fit shared memory");
+  p.stages = stages;
+  p.aux_depth = depth;
+  const int smem_bytes = stages * C::kStageBytes + out_bytes + depth * n_aux * kSubTileBytes + 1024 + kBarrierBytes;
   const int grid = (int)(total < kNumSMs ? total : kNumSMs);
-  conv_gemm_kernel<BN><<<grid, kThreads, C::kSmemBytes, stream>>>(maps, p);
+  conv_gemm_kernel<BN><<<grid, kThreads, smem_bytes, stream>>>(maps, p);
   ADV_LAUNCHED();
   return ADVB200_OK;
 }
 
 }  // namespace
 
-int launch_conv_gemm(int bn_cols, const CUtensorMap* tmA, int n_maps, const CUtensorMap& tmB,
-                     const ConvGemmParams& p, cudaStream_t stream) {
-  ADV_CHECK_ARG(n_maps >= 1 && n_maps <= 4, "conv_gemm: 1..4 activation maps");
+int launch_conv_gemm(int bn_cols, const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream) {
   ADV_CHECK_ARG(p.bw * p.bh * p.bn == kBlockM, "conv_gemm: tile must hold 128 pixels");
   ADV_CHECK_ARG(p.ntaps >= 1 && p.ntaps <= kMaxTaps && p.kblocks >= 1, "conv_gemm: bad K loop");
-  TmapPack maps;
-  for (int i = 0; i < 4; ++i) maps.a[i] = tmA[i < n_maps ? i : 0];
-  maps.b = tmB;
   switch (bn_cols) {
     case 16: return launch_impl<16>(maps, p, stream);
     case 64: return launch_impl<64>(maps, p, stream);

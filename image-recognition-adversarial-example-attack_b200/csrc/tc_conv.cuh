@@ -25,22 +25,30 @@ struct ConvGemmParams {
   int tap_dw[kMaxTaps];           // pixel shift of the tap along w / h
   int tap_dh[kMaxTaps];
   int tap_brow[kMaxTaps];         // first row of the tap's weights in the packed B matrix
-  // output addressing (elements): off = n*o_sn + h*o_sh + w*o_sw + channel
+  // output extent in tile coordinates (w, h, n) and channels
   int out_w, out_h, out_n, cout;
-  long long o_sn, o_sh, o_sw;
-  void* out;                      // bf16 (epi 0) or fp32 NCHW image gradient (epi 1)
+  void* out;                      // epi 1 only: fp32 NCHW image gradient (epi 0 stores through maps.out)
   const float* bias;              // [cout] or null
-  const __nv_bfloat16* add;       // residual / other-branch gradient, addressed like out, or null
-  const __nv_bfloat16* mask;      // forward activation whose sign gates the gradient, or null
+  int has_add;                    // residual / other-branch gradient tile read through maps.add
+  int has_mask;                   // forward activation (maps.mask) whose sign gates the gradient
   int relu;
+  int stages;                     // smem ring depth chosen by the host for this launch
+  int aux_depth;                  // residual/mask prefetch ring depth (sub-tiles), host-chosen
   int epi;                        // 0: bf16 NHWC store; 1: conv1 input-gradient scatter (fp32 NCHW)
   const float* std_dev;           // epi 1: device pointer to std[3]; gradient is divided by std[c]
   int img_h, img_w;               // epi 1: full-resolution image size
 };
 
-// Launch on `stream`.  bn_cols in {16, 64, 128, 256}.  tmA: up to 4 maps; tmB: packed weights.
-int launch_conv_gemm(int bn_cols, const CUtensorMap* tmA, int n_maps, const CUtensorMap& tmB,
-                     const ConvGemmParams& p, cudaStream_t stream);
+struct ConvGemmMaps {
+  CUtensorMap a[4];   // activation (or one per stride-2 sub-lattice)
+  CUtensorMap b;      // packed weights
+  CUtensorMap out;    // output tile store (64-channel boxes, same pixel box as a[])
+  CUtensorMap add;    // optional, output-shaped
+  CUtensorMap mask;   // optional, output-shaped
+};
+
+// Launch on `stream`.  bn_cols in {16, 64, 128, 256}.  Fills p.stages.
+int launch_conv_gemm(int bn_cols, const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream);
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda needed).
 // dims/strides innermost-first; strides in BYTES for dims 1..rank-1; bf16 elements; 128B swizzle.

@@ -168,6 +168,12 @@ int advb200_test_conv(int precision, const void* x, const float* wgt, const floa
 /* number of kernels launched by this library since load (bench.py's gpu_launches) */
 int64_t advb200_launch_count(void);
 
+/* Per-launch timing of the conv kernels for bench.py's roofline leg: while enabled, every tcgen05
+ * conv launch is bracketed by CUDA events on its stream; advb200_profile_read synchronises on them,
+ * returns the summed device time (ms) and the number of launches, and clears the list. */
+int advb200_profile_enable(int on);
+int advb200_profile_read(double* conv_ms_host, int64_t* conv_launches_host);
+
 #ifdef __cplusplus
 }
 #endif

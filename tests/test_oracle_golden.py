@@ -1,0 +1,86 @@
+"""Pins the CPU oracle (oracle/) against outputs of the reference itself (tests/golden/, produced
+by oracle/gen_golden.py importing /root/reference).  CPU only."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import attacks_ref, defenses_ref, resnet50_ref, weights
+
+
+def _tiny(golden_dir):
+    g = np.load(golden_dir / "tiny_linear.npz")
+    wt = torch.from_numpy(g["wt"])
+    return g, (lambda z: z.flatten(1) @ wt)
+
+
+def test_fgsm_and_pgd_match_reference_bitwise(golden_dir):
+    g, model = _tiny(golden_dir)
+    mean, std = weights.mean_std()
+    x, y = torch.from_numpy(g["x"]), torch.from_numpy(g["y"])
+    eps, alpha = float(g["eps"]), float(g["alpha"])
+    assert np.array_equal(attacks_ref.fgsm(model, x, y, eps=eps, mean=mean, std=std).numpy(), g["fgsm"])
+    out = attacks_ref.pgd_linf(model, x, y, eps=eps, alpha=alpha, steps=7, mean=mean, std=std)
+    assert np.array_equal(out.numpy(), g["pgd_nostart"])
+    noise = weights.pgd_noise(x.shape, eps, 5)
+    out = attacks_ref.pgd_linf(model, x, y, eps=eps, alpha=alpha, steps=7, mean=mean, std=std, noise=noise)
+    assert np.array_equal(out.numpy(), g["pgd_seed5"])
+
+
+def test_cw_matches_reference(golden_dir):
+    g, model = _tiny(golden_dir)
+    mean, std = weights.mean_std()
+    x, y, yt = torch.from_numpy(g["x"]), torch.from_numpy(g["y"]), torch.from_numpy(g["yt"])
+    xa, s, _ = attacks_ref.cw_l2(model, x, y, mean=mean, std=std, c=2.0, kappa=0.1, steps=25, lr=0.05)
+    assert np.array_equal(s.numpy(), g["cwu_s"])
+    np.testing.assert_allclose(xa.numpy(), g["cwu_x"], rtol=0, atol=2e-6)   # explicit Adam vs torch.optim.Adam
+    xa, s, _ = attacks_ref.cw_l2(model, x, y, mean=mean, std=std, c=2.0, kappa=0.0, steps=25, lr=0.05,
+                                 targeted=True, y_target=yt)
+    assert np.array_equal(s.numpy(), g["cwt_s"])
+    np.testing.assert_allclose(xa.numpy(), g["cwt_x"], rtol=0, atol=2e-6)
+    with pytest.raises(ValueError):
+        attacks_ref.cw_l2(model, x, y, mean=mean, std=std, targeted=True)
+
+
+def test_defenses_match_reference_bitwise(golden_dir):
+    g = np.load(golden_dir / "defense_small.npz")
+    assert np.array_equal(defenses_ref.smooth3x3(g["x"]), g["smooth"])
+    assert np.array_equal(defenses_ref.quantize(g["x"], 16), g["quant16"])
+    assert np.array_equal(defenses_ref.quantize(g["x"], 4), g["quant4"])
+    assert np.array_equal(defenses_ref.defend_input(g["x"]), g["defend"])
+
+
+@pytest.fixture(scope="module")
+def fmodel():
+    return resnet50_ref.FunctionalResNet50(weights.seeded_resnet50(0).state_dict())
+
+
+def test_functional_resnet_matches_reference(golden_dir, fmodel):
+    g = np.load(golden_dir / "resnet_n2.npz")
+    mean, std = weights.mean_std()
+    x = weights.synthetic_images(4)[:2]
+    y = torch.from_numpy(g["y"])
+    grad, logits = attacks_ref.ce_input_grad(fmodel, x, y, mean, std)
+    ref = torch.from_numpy(g["logits"])
+    assert float((logits - ref).norm() / ref.norm()) < 1e-5
+    assert torch.equal(logits.argmax(1), y)
+    gref = torch.from_numpy(g["grad"])
+    # the reference's own fp32 noise floor on this model is ~4e-3 (meta.json: ref_fp32_vs_fp64)
+    assert float((grad - gref).norm() / gref.norm()) < 2e-2
+    mask = gref.abs() > 1e-6 * gref.abs().max()
+    assert float((grad.sign() == gref.sign())[mask].float().mean()) > 0.998
+
+
+def test_detector_and_evaluate_defenses_match_reference(golden_meta, fmodel):
+    mean, std = weights.mean_std()
+    xs = weights.synthetic_images(4)
+    det = golden_meta["detector"]
+    feats = fmodel.layer3_features(attacks_ref.normalize(xs, mean, std))
+    scores = defenses_ref.layer3_score(feats)
+    np.testing.assert_allclose(scores.numpy(), np.array(det["scores"], dtype=np.float32), rtol=2e-5)
+    thr = defenses_ref.calibrate_threshold(torch.tensor(det["scores"]), 0.95)
+    assert abs(thr - det["threshold"]) < 1e-6
+    x = xs[:1]
+    y = fmodel(attacks_ref.normalize(x, mean, std)).argmax(1)
+    out, _ = defenses_ref.evaluate_defenses(fmodel, x, y, mean, std, "fgsm", 4 / 255, 2 / 255, 10, det["threshold"])
+    want = det["evaluate_defenses"]["fgsm_4"][0]
+    assert {k: int(v) for k, v in out.items()} == want
