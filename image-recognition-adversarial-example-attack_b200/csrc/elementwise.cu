@@ -351,9 +351,10 @@ extern "C" {
 
 int advb200_linf_step_f32(float* x_adv, const float* x_orig, const float* grad, float alpha, float eps,
                           int64_t n, int project, void* stream) {
-  ADV_CHECK_ARG(x_adv && grad && n >= 0, "linf_step: null pointer or negative size");
+  ADV_CHECK_ARG(n >= 0, "linf_step: negative size");
+  if (n == 0) return ADVB200_OK;      // empty batch: nothing to do (pointers may be null)
+  ADV_CHECK_ARG(x_adv && grad, "linf_step: null pointer");
   ADV_CHECK_ARG(!project || x_orig, "linf_step: x_orig required when project != 0");
-  if (n == 0) return ADVB200_OK;
   cudaStream_t st = as_stream(stream);
   const bool vec = aligned16(x_adv) && aligned16(grad) && (!project || aligned16(x_orig));
   if (vec) {
@@ -372,17 +373,19 @@ int advb200_linf_step_f32(float* x_adv, const float* x_orig, const float* grad, 
 
 int advb200_random_start_f32(float* x_adv, const float* x_orig, const float* noise, int64_t n,
                              void* stream) {
-  ADV_CHECK_ARG(x_adv && x_orig && noise && n >= 0, "random_start: bad arguments");
+  ADV_CHECK_ARG(n >= 0, "random_start: negative size");
   if (n == 0) return ADVB200_OK;
+  ADV_CHECK_ARG(x_adv && x_orig && noise, "random_start: null pointer");
   random_start_kernel<<<grid_for(n), kThreads, 0, as_stream(stream)>>>(x_adv, x_orig, noise, n);
   ADV_LAUNCHED();
   return ADVB200_OK;
 }
 
 int advb200_quantize_f32(const float* x, float* out, int64_t n, int levels, void* stream) {
-  ADV_CHECK_ARG(x && out && n >= 0, "quantize: bad arguments");
+  ADV_CHECK_ARG(n >= 0, "quantize: negative size");
   ADV_CHECK_ARG(levels >= 2, "quantize: levels must be >= 2");
   if (n == 0) return ADVB200_OK;
+  ADV_CHECK_ARG(x && out, "quantize: null pointer");
   const int vec = aligned16(x) && aligned16(out);
   const int64_t n4 = n / 4;
   quantize_kernel<<<grid_for(vec ? (n4 > 0 ? n4 : 1) : n), kThreads, 0, as_stream(stream)>>>(
@@ -393,9 +396,10 @@ int advb200_quantize_f32(const float* x, float* out, int64_t n, int levels, void
 
 static int smooth_launch(const float* x, float* out, int64_t planes, int h, int w, int levels,
                          bool defend, void* stream) {
-  ADV_CHECK_ARG(x && out && planes >= 0 && h > 0 && w > 0, "smooth3x3: bad arguments");
-  ADV_CHECK_ARG(x != out, "smooth3x3: in-place operation is not supported");
+  ADV_CHECK_ARG(planes >= 0 && h > 0 && w > 0, "smooth3x3: bad sizes");
   if (planes == 0) return ADVB200_OK;
+  ADV_CHECK_ARG(x && out, "smooth3x3: null pointer");
+  ADV_CHECK_ARG(x != out, "smooth3x3: in-place operation is not supported");
   const int groups = (w + 3) / 4, chunks = (h + kSmoothRows - 1) / kSmoothRows;
   const int64_t total = planes * (int64_t)groups * chunks;
   const int grid = grid_for(total);

@@ -39,7 +39,9 @@ def test_argument_errors_do_not_need_a_gpu():
     assert rc == -1 and b"quantize" in lib.advb200_last_error()
     with pytest.raises(ValueError):
         _lib.check(rc, "advb200_quantize_f32")
-    assert lib.advb200_linf_step_f32(None, None, None, 0.1, 0.1, 0, 1, None) == -1
+    assert lib.advb200_linf_step_f32(None, None, None, 0.1, 0.1, -1, 1, None) == -1
+    assert lib.advb200_linf_step_f32(None, None, None, 0.1, 0.1, 4, 1, None) == -1
+    assert lib.advb200_linf_step_f32(None, None, None, 0.1, 0.1, 0, 1, None) == 0      # empty batch is fine
     assert lib.advb200_cw_parts(150528) == 49
 
 
