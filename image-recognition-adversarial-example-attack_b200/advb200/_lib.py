@@ -51,6 +51,7 @@ SIGNATURES = {
     "advb200_launch_count": (c_int64, []),
     "advb200_profile_enable": (c_int, [c_int]),
     "advb200_profile_read": (c_int, [POINTER(ctypes.c_double), POINTER(c_int64)]),
+    "advb200_profile_dump": (c_int64, [c_char_p, c_int64]),
 }
 
 

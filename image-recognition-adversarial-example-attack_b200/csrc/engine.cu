@@ -8,6 +8,7 @@
 // Reference: model(normalize_batch(x)) attack.py:30,57,111; autograd.grad(loss, x) attack.py:32,59;
 // loss.backward() attack.py:130 (without its unused weight gradients); _layer3_features
 // defense_experiments.py:221-257.
+#include <cstdlib>
 #include <vector>
 
 #include "layers.cuh"
@@ -54,7 +55,17 @@ struct Op {
   SimtConvParams simt;
   void* ms_ptr = nullptr;
   size_t ms_bytes = 0;
+  // profiling metadata (advb200_profile_dump): layer label, algorithmic flops and HBM bytes
+  char name[48] = {0};
+  double flops = 0, bytes = 0;
 };
+
+// label given to the ops built next (set by plan(); read by build_tc_ops)
+const char* g_label = "";
+void label_op(Op& op, const char* suffix, double flops, double bytes) {
+  snprintf(op.name, sizeof op.name, "%s%s", g_label, suffix);
+  op.flops = flops; op.bytes = bytes;
+}
 
 inline int pow2_div(int v, int cap) {
   int b = 1;
@@ -77,7 +88,8 @@ inline int pick_bn(int gemm_n, long long m_tiles, int n_aux) {
   double best_score = -1;
   for (int i = 0; i < 3; ++i) {
     if (gemm_n % cands[i]) continue;
-    if (n_aux > 0 && cands[i] > 128) continue;
+    static const bool wide_aux = !getenv("ADVB200_NO_BN256_AUX");   // tuning knob
+    if (n_aux > 0 && cands[i] > 128 && !wide_aux) continue;
     const long long tiles = m_tiles * (gemm_n / cands[i]);
     const long long waves = (tiles + kNumSMs - 1) / kNumSMs;
     const double eff = (double)tiles / (double)(waves * kNumSMs) * bonus[i];
@@ -90,7 +102,7 @@ inline int pick_bn(int gemm_n, long long m_tiles, int n_aux) {
 // in : GEMM K side (activation for fwd, dY for dgrad); out: GEMM N side.  wpack: K-major packed
 // weights with k*k*out.c rows of in.c columns.
 int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride, bool dgrad, Act in, Act out,
-                 const float* bias, const bf16* add, const bf16* mask, int relu) {
+                 const float* bias, const bf16* add, const uint32_t* mask, int relu, uint32_t* mask_out = nullptr) {
   const int gemm_n = out.c, gemm_k = in.c;
   ADV_CHECK_ARG(gemm_k % 64 == 0 && gemm_n % 64 == 0, "tc conv: channels must be multiples of 64");
   ADV_CHECK_ARG((ksize == 1 || ksize == 3) && (stride == 1 || stride == 2), "tc conv: unsupported geometry");
@@ -118,18 +130,26 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
   ConvGemmParams& p = t.p;
   memset(&p, 0, sizeof p);
   memset(&t.maps, 0, sizeof t.maps);
+  // algorithmic cost of one launch: out_pix output pixels, `taps` filter taps, in_share of the input tensor
+  auto annotate = [&](Op& o, const char* sfx, double out_pix, int taps, double in_share) {
+    const double naux = (add ? 1 : 0) + (mask ? 1.0 / 16 : 0) + (mask_out ? 1.0 / 16 : 0);
+    label_op(o, sfx, 2.0 * out_pix * gemm_n * gemm_k * taps,
+             2.0 * (in_share * (double)in.elems() + out_pix * gemm_n * (1.0 + naux) + (double)taps * gemm_n * gemm_k));
+  };
   p.kblocks = gemm_k / 64;
-  p.bias = bias; p.has_add = add != nullptr; p.has_mask = mask != nullptr; p.relu = relu; p.epi = 0;
+  p.bias = bias; p.has_add = add != nullptr; p.relu = relu; p.epi = 0;
+  p.mask_in = mask; p.mask_out = mask_out;
+  p.mask_pixels = (long long)out.n * out.h * out.w;
+  p.pix_sub = 1; p.pix_ph = 0; p.pix_pw = 0; p.full_h = out.h; p.full_w = out.w;
   p.cout = gemm_n;
   p.out = nullptr;
-  const int n_aux = p.has_add + p.has_mask;
+  const int n_aux = p.has_add;
   // output-shaped maps (store target, residual, mask): 64-channel boxes over the same pixel box as A
   auto make_out_maps = [&](TcOp& tt, const Act& o, int sub, int ph, int pw) {
     Act v = o;
     const ConvGemmParams& q = tt.p;
     int rc = make_a(&tt.maps.out, v, sub, ph, pw, q.bw, q.bh, q.bn);
     if (!rc && add) { v.p = const_cast<bf16*>(add); rc = make_a(&tt.maps.add, v, sub, ph, pw, q.bw, q.bh, q.bn); }
-    if (!rc && mask) { v.p = const_cast<bf16*>(mask); rc = make_a(&tt.maps.mask, v, sub, ph, pw, q.bw, q.bh, q.bn); }
     return rc;
   };
 
@@ -144,6 +164,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     p.tiles_c = gemm_n / t.bn;
     p.ntaps = 1;
     p.out_w = (int)m; p.out_h = 1; p.out_n = 1;
+    p.full_h = 1; p.full_w = (int)m;
     auto flat_map = [&](CUtensorMap* mp, const void* base, int ch) {
       const uint64_t dims[4] = {(uint64_t)ch, (uint64_t)m, 1, 1};
       const uint64_t strides[3] = {(uint64_t)ch * 2, (uint64_t)ch * 2 * (uint64_t)m, (uint64_t)ch * 2 * (uint64_t)m};
@@ -153,9 +174,9 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     int rc = flat_map(&t.maps.a[0], in.p, gemm_k);
     if (!rc) rc = flat_map(&t.maps.out, out.p, gemm_n);
     if (!rc && add) rc = flat_map(&t.maps.add, add, gemm_n);
-    if (!rc && mask) rc = flat_map(&t.maps.mask, mask, gemm_n);
     if (!rc) rc = make_b(&t.maps.b, t.bn);
     if (rc) return rc;
+    annotate(op, "", (double)m, 1, 1.0);
     ops.push_back(op);
     return ADVB200_OK;
   }
@@ -199,6 +220,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
       }
     rc = make_b(&t.maps.b, t.bn);
     if (rc) return rc;
+    annotate(op, "", (double)out.n * out.h * out.w, p.ntaps, 1.0);
     ops.push_back(op);
     return ADVB200_OK;
   }
@@ -223,6 +245,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
       }
     rc = make_b(&t.maps.b, t.bn);
     if (rc) return rc;
+    annotate(op, "", (double)out.n * out.h * out.w, p.ntaps, 1.0);
     ops.push_back(op);
     return ADVB200_OK;
   }
@@ -253,10 +276,15 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
       t2.bn = pick_bn(gemm_n, (long long)q.tiles_w * q.tiles_h * q.tiles_n, n_aux);
       q.tiles_c = gemm_n / t2.bn;
       q.out_w = sw; q.out_h = sh; q.out_n = out.n;
+      q.pix_sub = 2; q.pix_ph = ph; q.pix_pw = pw;
       int rc = make_a(&t2.maps.a[0], in, 1, 0, 0, q.bw, q.bh, q.bn);
       if (!rc) rc = make_out_maps(t2, out, 2, ph, pw);     // (ph, pw) sub-lattice of dX / residual / mask
       if (!rc) rc = make_b(&t2.maps.b, t2.bn);
       if (rc) return rc;
+      {
+        const char sfx[4] = {'/', (char)('0' + ph * 2 + pw), 0, 0};
+        annotate(o2, sfx, (double)out.n * sh * sw, q.ntaps, ksize == 1 ? 1.0 : 0.25);
+      }
       ops.push_back(o2);
     }
   return ADVB200_OK;
@@ -279,7 +307,8 @@ int build_simt_op(std::vector<Op>& ops, const float* wm, int ksize, int stride, 
 // optional per-launch timing of the conv kernels (bench.py's roofline leg): CUDA events on the
 // launching stream around every tcgen05 conv launch, summed by advb200_profile_read
 bool g_prof_on = false;
-std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_prof_events;
+struct ProfRec { cudaEvent_t e0, e1; const Op* op; };
+std::vector<ProfRec> g_prof_events;
 
 int run_ops(std::vector<Op>& ops, cudaStream_t st) {
   for (Op& op : ops) {
@@ -294,7 +323,7 @@ int run_ops(std::vector<Op>& ops, cudaStream_t st) {
         rc = launch_conv_gemm(op.tc.bn, op.tc.maps, op.tc.p, st);
         if (g_prof_on) {
           cudaEventRecord(e1, st);
-          g_prof_events.emplace_back(e0, e1);
+          g_prof_events.push_back(ProfRec{e0, e1, &op});
         }
         break;
       }
@@ -383,6 +412,12 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
     a.p = bump.take((size_t)a.elems() * esz);
     return a;
   };
+  static char lbl[48];
+  auto setl = [&](const char* dir, const BlockSpec* s, const char* conv) {
+    if (s) snprintf(lbl, sizeof lbl, "%s l%d.%d.%s", dir, s->layer + 1, s->idx, conv);
+    else snprintf(lbl, sizeof lbl, "%s %s", dir, conv);
+    g_label = lbl;
+  };
   if (build) {
     m->ops_conv1.clear(); m->ops_l123.clear(); m->ops_l4.clear(); m->ops_bwd.clear(); m->ops_conv1_bwd.clear();
   }
@@ -436,6 +471,8 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
       const uint64_t bs[1] = {128};
       const uint32_t bb[2] = {64, 64};
       if (!rc) rc = make_tmap_bf16(&t.maps.b, w0.b_fwd, 2, bd, bs, bb);
+      setl("fwd", nullptr, "conv1");
+      label_op(op, "", 2.0 * n * 112 * 112 * 64 * 147, 2.0 * n * (115.0 * 112 * 64 + 112.0 * 112 * 64));
       m->ops_conv1.push_back(op);
     } else {
       rc = build_simt_op(m->ops_conv1, w0.f_fwd, 7, 2, false, m->t_in, m->c1, w0.shift, nullptr, nullptr, 1, 3);
@@ -443,7 +480,7 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
   }
 
   // ---- residual stages: forward ops, and the tensors the backward pass needs
-  struct BlkT { Act x, a, b, out, idn; };
+  struct BlkT { Act x, a, b, out, idn; uint32_t *ma = nullptr, *mb = nullptr, *mout = nullptr, *mx = nullptr; };
   std::vector<BlkT> bt(m->blocks.size());
   Act x = m->p1;
   for (size_t bi = 0; bi < m->blocks.size() && !rc; ++bi) {
@@ -455,19 +492,29 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
     t.b = act(hout, hout, s.width);
     t.out = act(hout, hout, s.width * 4);
     if (s.down) t.idn = act(hout, hout, s.width * 4);
+    if (tc) {   // ReLU bit masks of the three activations (1 bit per element) for the backward pass
+      t.ma = reinterpret_cast<uint32_t*>(bump.take((size_t)t.a.elems() / 8));
+      t.mb = reinterpret_cast<uint32_t*>(bump.take((size_t)t.b.elems() / 8));
+      t.mout = reinterpret_cast<uint32_t*>(bump.take((size_t)t.out.elems() / 8));
+      t.mx = bi > 0 ? bt[bi - 1].mout : nullptr;   // block input = previous block's output
+    }
     if (build) {
       std::vector<Op>& ops = (s.layer < 3) ? m->ops_l123 : m->ops_l4;
       const ConvW& c1 = m->conv[s.conv_base], &c2 = m->conv[s.conv_base + 1], &c3 = m->conv[s.conv_base + 2];
       if (tc) {
-        rc = build_tc_ops(ops, c1.b_fwd, 1, 1, false, t.x, t.a, c1.shift, nullptr, nullptr, 1);
-        if (!rc) rc = build_tc_ops(ops, c2.b_fwd, 3, s.stride, false, t.a, t.b, c2.shift, nullptr, nullptr, 1);
+        setl("fwd", &s, "c1");
+        rc = build_tc_ops(ops, c1.b_fwd, 1, 1, false, t.x, t.a, c1.shift, nullptr, nullptr, 1, t.ma);
+        setl("fwd", &s, "c2");
+        if (!rc) rc = build_tc_ops(ops, c2.b_fwd, 3, s.stride, false, t.a, t.b, c2.shift, nullptr, nullptr, 1, t.mb);
         const bf16* res = reinterpret_cast<const bf16*>(t.x.p);
         if (!rc && s.down) {
           const ConvW& cd = m->conv[s.conv_base + 3];
+          setl("fwd", &s, "ds");
           rc = build_tc_ops(ops, cd.b_fwd, 1, s.stride, false, t.x, t.idn, cd.shift, nullptr, nullptr, 0);
           res = reinterpret_cast<const bf16*>(t.idn.p);
         }
-        if (!rc) rc = build_tc_ops(ops, c3.b_fwd, 1, 1, false, t.b, t.out, c3.shift, res, nullptr, 1);
+        setl("fwd", &s, "c3");
+        if (!rc) rc = build_tc_ops(ops, c3.b_fwd, 1, 1, false, t.b, t.out, c3.shift, res, nullptr, 1, t.mout);
       } else {
         rc = build_simt_op(ops, c1.f_fwd, 1, 1, false, t.x, t.a, c1.shift, nullptr, nullptr, 1);
         if (!rc) rc = build_simt_op(ops, c2.f_fwd, 3, s.stride, false, t.a, t.b, c2.shift, nullptr, nullptr, 1);
@@ -500,9 +547,10 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
     int nxt;
     if (build) {
       if (tc) {
-        typedef const bf16* B;
-        rc = build_tc_ops(m->ops_bwd, c3.b_dgrad, 1, 1, true, g_sum, g_b, nullptr, nullptr, (B)t.b.p, 0);
-        if (!rc) rc = build_tc_ops(m->ops_bwd, c2.b_dgrad, 3, s.stride, true, g_b, g_a, nullptr, nullptr, (B)t.a.p, 0);
+        setl("bwd", &s, "c3");
+        rc = build_tc_ops(m->ops_bwd, c3.b_dgrad, 1, 1, true, g_sum, g_b, nullptr, nullptr, t.mb, 0);
+        setl("bwd", &s, "c2");
+        if (!rc) rc = build_tc_ops(m->ops_bwd, c2.b_dgrad, 3, s.stride, true, g_b, g_a, nullptr, nullptr, t.ma, 0);
       } else {
         typedef const float* F;
         rc = build_simt_op(m->ops_bwd, c3.f_dgrad, 1, 1, true, g_sum, g_b, nullptr, nullptr, (F)t.b.p, 0);
@@ -520,6 +568,7 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
             Op ms; ms.kind = Op::MEMSET; ms.ms_ptr = g_t.p; ms.ms_bytes = (size_t)g_t.elems() * esz;
             m->ops_bwd.push_back(ms);
           }
+          setl("bwd", &s, "ds");
           rc = build_tc_ops(m->ops_bwd, cd.b_dgrad, 1, s.stride, true, g_sum, g_t, nullptr, nullptr, nullptr, 0);
         } else {
           rc = build_simt_op(m->ops_bwd, cd.f_dgrad, 1, s.stride, true, g_sum, g_t, nullptr, nullptr, nullptr, 0);
@@ -528,8 +577,9 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
       gbusy[cur] = false;                                // g_sum consumed by both branches
       nxt = gacquire(); g_x.p = gbuf[nxt];
       if (build && !rc) {
+        setl("bwd", &s, "c1");
         if (tc) rc = build_tc_ops(m->ops_bwd, c1.b_dgrad, 1, 1, true, g_a, g_x, nullptr, (const bf16*)g_t.p,
-                                  first ? nullptr : (const bf16*)t.x.p, 0);
+                                  first ? nullptr : t.mx, 0);
         else rc = build_simt_op(m->ops_bwd, c1.f_dgrad, 1, 1, true, g_a, g_x, nullptr, (const float*)g_t.p,
                                 first ? nullptr : (const float*)t.x.p, 0);
       }
@@ -537,8 +587,9 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
     } else {
       nxt = gacquire(); g_x.p = gbuf[nxt];
       if (build && !rc) {
+        setl("bwd", &s, "c1");
         if (tc) rc = build_tc_ops(m->ops_bwd, c1.b_dgrad, 1, 1, true, g_a, g_x, nullptr, (const bf16*)g_sum.p,
-                                  (const bf16*)t.x.p, 0);
+                                  first ? nullptr : t.mx, 0);
         else rc = build_simt_op(m->ops_bwd, c1.f_dgrad, 1, 1, true, g_a, g_x, nullptr, (const float*)g_sum.p,
                                 (const float*)t.x.p, 0);
       }
@@ -583,6 +634,8 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
       const uint64_t bs[1] = {128};
       const uint32_t bb[2] = {64, 16};
       if (!rc) rc = make_tmap_bf16(&t.maps.b, m->conv[0].b_dgrad, 2, bd, bs, bb);
+      setl("bwd", nullptr, "conv1");
+      label_op(op, "", 2.0 * n * 112 * 112 * 64 * 147, n * (2.0 * 112 * 112 * 64 + 4.0 * 3 * 224 * 224));
       m->ops_conv1_bwd.push_back(op);
     } else {
       Act gy = m->c1; gy.p = m->g_c1;
@@ -727,16 +780,39 @@ int advb200_profile_read(double* conv_ms, int64_t* conv_launches) {
   ADV_CHECK_ARG(conv_ms && conv_launches, "profile_read: null argument");
   double total = 0.0;
   for (auto& pr : g_prof_events) {
-    ADV_CHECK_CUDA(cudaEventSynchronize(pr.second));
+    ADV_CHECK_CUDA(cudaEventSynchronize(pr.e1));
     float ms = 0.f;
-    ADV_CHECK_CUDA(cudaEventElapsedTime(&ms, pr.first, pr.second));
+    ADV_CHECK_CUDA(cudaEventElapsedTime(&ms, pr.e0, pr.e1));
     total += ms;
-    cudaEventDestroy(pr.first); cudaEventDestroy(pr.second);
+    cudaEventDestroy(pr.e0); cudaEventDestroy(pr.e1);
   }
   *conv_ms = total;
   *conv_launches = (int64_t)g_prof_events.size();
   g_prof_events.clear();
   return ADVB200_OK;
+}
+
+int64_t advb200_profile_dump(char* buf_host, int64_t cap) {
+  // one CSV line per recorded conv launch: name,BN,tiles,ksteps,ms,flops,bytes  (drains the list)
+  std::string out = "name,bn,tiles,ksteps,stages,ms,flops,bytes\n";
+  for (auto& pr : g_prof_events) {
+    float ms = 0.f;
+    if (cudaEventSynchronize(pr.e1) == cudaSuccess) cudaEventElapsedTime(&ms, pr.e0, pr.e1);
+    cudaEventDestroy(pr.e0); cudaEventDestroy(pr.e1);
+    const ConvGemmParams& q = pr.op->tc.p;
+    char line[256];
+    snprintf(line, sizeof line, "%s,%d,%lld,%d,%d,%.6f,%.6g,%.6g\n", pr.op->name, pr.op->tc.bn,
+             (long long)q.tiles_w * q.tiles_h * q.tiles_n * q.tiles_c, q.ntaps * q.kblocks, q.stages, ms,
+             pr.op->flops, pr.op->bytes);
+    out += line;
+  }
+  g_prof_events.clear();
+  if (buf_host && cap > 0) {
+    const size_t ncopy = out.size() < (size_t)cap - 1 ? out.size() : (size_t)cap - 1;
+    memcpy(buf_host, out.data(), ncopy);
+    buf_host[ncopy] = 0;
+  }
+  return (int64_t)out.size() + 1;
 }
 
 int advb200_model_destroy(advb200_model* m) {
@@ -825,12 +901,18 @@ int advb200_test_conv(int precision, const void* x, const float* wgt, const floa
   const size_t esz = precision == ADVB200_PREC_BF16 ? 2 : 4;
   ADV_CHECK_CUDA(cudaMalloc(&pk_f, wn * esz));
   ADV_CHECK_CUDA(cudaMalloc(&pk_d, wn * esz));
+  void* mbits = nullptr;
   if (precision == ADVB200_PREC_BF16) {
     rc = launch_pack_bf16(wgt, nullptr, (bf16*)pk_f, (bf16*)pk_d, cout, cin, ksize, st);
+    if (!rc && mask) {
+      const long long px = (long long)a_out.n * a_out.h * a_out.w;
+      ADV_CHECK_CUDA(cudaMalloc(&mbits, (size_t)px * a_out.c / 8));
+      rc = launch_pack_mask_bits((const bf16*)mask, (uint32_t*)mbits, px, a_out.c, st);
+    }
     if (!rc && dgrad && stride == 2 && ksize == 1)
       ADV_CHECK_CUDA(cudaMemsetAsync(out, 0, (size_t)a_out.elems() * 2, st));
     if (!rc) rc = build_tc_ops(ops, dgrad ? (const bf16*)pk_d : (const bf16*)pk_f, ksize, stride, dgrad != 0, a_in, a_out,
-                               bias, (const bf16*)add, (const bf16*)mask, relu);
+                               bias, (const bf16*)add, (const uint32_t*)mbits, relu);
   } else {
     rc = launch_pack_f32(wgt, nullptr, (float*)pk_f, (float*)pk_d, cout, cin, ksize, st);
     if (!rc) rc = build_simt_op(ops, dgrad ? (const float*)pk_d : (const float*)pk_f, ksize, stride, dgrad != 0, a_in,
@@ -838,7 +920,7 @@ int advb200_test_conv(int precision, const void* x, const float* wgt, const floa
   }
   if (!rc) rc = run_ops(ops, st);
   cudaError_t e = cudaStreamSynchronize(st);
-  cudaFree(pk_f); cudaFree(pk_d);
+  cudaFree(pk_f); cudaFree(pk_d); cudaFree(mbits);
   if (!rc && e != cudaSuccess) rc = fail(ADVB200_ERR_CUDA, std::string("test_conv: ") + cudaGetErrorString(e));
   return rc;
 }

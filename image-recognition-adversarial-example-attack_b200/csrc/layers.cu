@@ -516,7 +516,30 @@ __global__ void f32_to_bf16_kernel(const float* __restrict__ in, bf16* __restric
   if (t < n) out[t] = __float2bfloat16_rn(in[t]);
 }
 
+// bf16 tensor [pixels, c] -> ReLU bit mask (bit set <=> value > 0); word ((c/64)*pixels + pixel)*2 + (c/32)%2
+__global__ void __launch_bounds__(kT)
+pack_mask_bits_kernel(const bf16* __restrict__ act, uint32_t* __restrict__ bits, long long pixels, int c) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // (pixel, c32)
+  const int c32n = c / 32;
+  if (t >= pixels * c32n) return;
+  const int c32 = (int)(t % c32n);
+  const long long px = t / c32n;
+  const bf16* a = act + px * c + c32 * 32;
+  uint32_t w = 0;
+#pragma unroll
+  for (int i = 0; i < 32; ++i) w |= (__bfloat162float(a[i]) > 0.f ? 1u : 0u) << i;
+  bits[((long long)(c32 >> 1) * pixels + px) * 2 + (c32 & 1)] = w;
+}
+
 }  // namespace
+
+int launch_pack_mask_bits(const bf16* act, uint32_t* bits, long long pixels, int c, cudaStream_t st) {
+  const long long total = pixels * (c / 32);
+  if (!total) return ADVB200_OK;
+  pack_mask_bits_kernel<<<nblocks(total), kT, 0, st>>>(act, bits, pixels, c);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
 
 int launch_prep_hcol(const float* x, const float* mean3, const float* std3, bf16* out, int n, cudaStream_t st) {
   if (!n) return ADVB200_OK;

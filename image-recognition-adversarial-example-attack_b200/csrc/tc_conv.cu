@@ -21,14 +21,17 @@ namespace {
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;                 // 64 bf16 = 128 bytes = one swizzle row
 constexpr int kATileBytes = kBlockM * kBlockK * 2;   // 16 KB
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;                // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
 constexpr int kEpiWarp0 = 2;
+constexpr int kEpiThreads = 256;
 
 constexpr int kMaxStages = 8;
 constexpr int kMaxAuxDepth = 8;
 constexpr int kSmemBudget = 232448;            // 227 KB opt-in limit per CTA
 constexpr int kSubTileBytes = kBlockM * 128;   // 128 rows x 64 bf16: one epilogue sub-tile
 constexpr int kBarrierBytes = 512;
+constexpr int kIdentBytes = 64 * 128;          // 64x64 bf16 identity operand of the residual k-steps
+constexpr int kBiasBytes = 2 * 256 * 4;        // per-accumulator copy of the tile's folded-BN shift
 
 template <int BN> struct Cfg {
   static constexpr int kBTileBytes = BN * kBlockK * 2;
@@ -146,6 +149,31 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
 }
+// relu fused into the conversion: max(x, 0) then round-to-nearest-even to bf16 (NaN -> canonical NaN)
+__device__ __forceinline__ uint32_t pack_bf16x2_relu(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+// packed fp32x2 add (sm_100): {a0, a1} += {b0, b1}
+__device__ __forceinline__ void add2(float& a0, float& a1, float b0, float b1) {
+  asm("{\n.reg .b64 ra, rb;\nmov.b64 ra, {%0, %1};\nmov.b64 rb, {%2, %3};\nadd.rn.f32x2 ra, ra, rb;\n"
+      "mov.b64 {%0, %1}, ra;\n}"
+      : "+f"(a0), "+f"(a1)
+      : "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void tmem_ld32f(uint32_t taddr, float (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]),
+        "=f"(v[8]), "=f"(v[9]), "=f"(v[10]), "=f"(v[11]), "=f"(v[12]), "=f"(v[13]), "=f"(v[14]),
+        "=f"(v[15]), "=f"(v[16]), "=f"(v[17]), "=f"(v[18]), "=f"(v[19]), "=f"(v[20]), "=f"(v[21]),
+        "=f"(v[22]), "=f"(v[23]), "=f"(v[24]), "=f"(v[25]), "=f"(v[26]), "=f"(v[27]), "=f"(v[28]),
+        "=f"(v[29]), "=f"(v[30]), "=f"(v[31])
+      : "r"(taddr));
+}
 __device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
 
@@ -161,7 +189,12 @@ template <int N> __device__ __forceinline__ void bulk_wait_read() {
   asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
 }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 v;
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
@@ -183,35 +216,42 @@ __device__ __forceinline__ TileCoord tile_coord(const ConvGemmParams& p, int til
   return t;
 }
 
+// smem carve-up (host and device agree through these helpers)
+template <int BN> struct Smem {
+  using C = Cfg<BN>;
+  __host__ __device__ static constexpr int out_slots() { return BN == 16 ? 0 : 4; }
+  __host__ __device__ static constexpr int fixed_bytes() {
+    return out_slots() * kSubTileBytes + kIdentBytes + kBiasBytes + kBarrierBytes;
+  }
+};
+
 template <int BN>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constant__ ConvGemmParams p) {
   using C = Cfg<BN>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int n_aux = (p.has_add ? 1 : 0) + (p.has_mask ? 1 : 0);
-  const int aux_depth = p.aux_depth;                        // aux ring slots (sub-tiles of prefetch)
-  const int aux_slot_bytes = kSubTileBytes * n_aux;
-  uint8_t* out_smem = smem + p.stages * C::kStageBytes;     // 2 x 16 KB output staging
-  uint8_t* aux_smem = out_smem + ((BN == 16) ? 0 : 2 * kSubTileBytes);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(aux_smem + aux_depth * aux_slot_bytes);
+  extern __shared__ __align__(1024) uint8_t smem[];
+  constexpr int n_out_slots = Smem<BN>::out_slots();
+  uint8_t* out_smem = smem + p.stages * C::kStageBytes;     // n_out_slots x 16 KB output staging
+  uint8_t* ident_smem = out_smem + n_out_slots * kSubTileBytes;   // 64x64 bf16 identity (K-major, swizzled)
+  float* bias_smem = reinterpret_cast<float*>(ident_smem + kIdentBytes);   // [2][256]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(bias_smem) + kBiasBytes);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kMaxStages;
   uint64_t* tfull_bar = bars + 2 * kMaxStages;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint64_t* aux_bar = tempty_bar + 2;                       // kMaxAuxDepth entries
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_bar + kMaxAuxDepth);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
+    if (smem_u32(smem) & 1023u) __trap();                   // swizzled tiles need 1024-byte alignment
     for (int i = 0; i < 4; ++i) prefetch_tmap(&maps.a[i]);
     prefetch_tmap(&maps.b);
     prefetch_tmap(&maps.out);
+    if (p.has_add) prefetch_tmap(&maps.add);
     for (int s = 0; s < kMaxStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], 4); }
-    for (int a = 0; a < kMaxAuxDepth; ++a) mbar_init(&aux_bar[a], 1);
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -221,12 +261,35 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
+  const int total_tiles = p.tiles_w * p.tiles_h * p.tiles_n * p.tiles_c;
+  if (warp >= kEpiWarp0 && p.bias && BN != 16) {
+    // folded-BN shift of the first tile's column block (accumulator 0's copy)
+    const int i = threadIdx.x - kEpiWarp0 * 32;
+    if (i < BN && (int)blockIdx.x < total_tiles) bias_smem[i] = __ldg(p.bias + tile_coord(p, blockIdx.x, BN).c0 + i);
+  }
+  if (warp >= kEpiWarp0 && p.has_add) {
+    // identity operand for the residual k-steps: I[n][k] = (n == k), rows of 128 B, 16-byte chunks
+    // XOR-swizzled by (row & 7) exactly as TMA would have written them
+    const int i = threadIdx.x - kEpiWarp0 * 32;          // 256 threads x 32 B = 8 KB
+    const int r = i >> 2, cpair = (i & 3) * 2;           // row, first of two logical chunks
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+      const int c = cpair + cc;                          // logical chunk: columns 8c..8c+7
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if ((r >> 3) == c) {
+        const uint32_t one = 0x3F80u << (16 * (r & 1));  // bf16 1.0 in the right half-word
+        const int wsel = (r & 7) >> 1;
+        v.x = wsel == 0 ? one : 0; v.y = wsel == 1 ? one : 0; v.z = wsel == 2 ? one : 0; v.w = wsel == 3 ? one : 0;
+      }
+      *reinterpret_cast<uint4*>(ident_smem + r * 128 + ((c ^ (r & 7)) << 4)) = v;
+    }
+    fence_async_smem();
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int total_tiles = p.tiles_w * p.tiles_h * p.tiles_n * p.tiles_c;
   const int ksteps = p.ntaps * p.kblocks;
   const int nstages = p.stages;
 
@@ -248,6 +311,16 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
             mbar_expect_tx(&full_bar[stage], C::kStageBytes);
             tma_load_4d(ma, &full_bar[stage], sa, kb * kBlockK, cw, ch, tc.n0);
             tma_load_2d(&maps.b, &full_bar[stage], sb, kb * kBlockK, brow);
+            if (++stage == nstages) { stage = 0; phase ^= 1; }
+          }
+        }
+        if (p.has_add) {
+          // residual / skip-gradient tile, one 64-channel block per stage (added by an identity MMA)
+          for (int j = 0; j < BN / 64; ++j) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            mbar_expect_tx(&full_bar[stage], kATileBytes);
+            tma_load_4d(&maps.add, &full_bar[stage], smem + stage * C::kStageBytes, tc.c0 + 64 * j, tc.w0, tc.h0,
+                        tc.n0);
             if (++stage == nstages) { stage = 0; phase ^= 1; }
           }
         }
@@ -282,14 +355,35 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           umma_commit(&empty_bar[stage]);
           if (++stage == nstages) { stage = 0; phase ^= 1; }
         }
+        if (p.has_add) {
+          // D[:, 64j..64j+63] += R_j * I  (bf16 x 1.0 accumulated in fp32: exact)
+          constexpr uint32_t idesc64 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(64 >> 3) << 17) |
+                                       ((uint32_t)(kBlockM >> 4) << 24);
+          const uint64_t idesc_b = make_smem_desc(smem_u32(ident_smem));
+          for (int j = 0; j < BN / 64; ++j) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            const uint64_t adesc = make_smem_desc(smem_u32(smem + stage * C::kStageBytes));
+#pragma unroll
+            for (int k = 0; k < kBlockK / 16; ++k)
+              umma_bf16(d_tmem + (uint32_t)(64 * j), adesc + (uint64_t)(2 * k), idesc_b + (uint64_t)(2 * k), idesc64, 1u);
+            umma_commit(&empty_bar[stage]);
+            if (++stage == nstages) { stage = 0; phase ^= 1; }
+          }
+        }
         umma_commit(&tfull_bar[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
   } else {
-    // =========================== epilogue ===========================
-    const int quad = warp & 3;                   // TMEM lane group this warp may access
+    // =========================== epilogue (8 warps) ===========================
+    // warp w may only touch TMEM lanes 32*(w%4)..+31; the two warps of a lane group split every
+    // 64-column sub-tile into its two 32-column halves.
+    const int ew = warp - kEpiWarp0;
+    const int quad = warp & 3;
+    const int half = ew >> 2;
     const int row = quad * 32 + lane;            // accumulator row == pixel within the tile
+    const int etid = threadIdx.x - kEpiWarp0 * 32;
     int acc = 0;
     uint32_t acc_phase = 0;
 
@@ -303,16 +397,18 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
         const bool valid = (w < p.out_w) && (h < p.out_h) && (n < p.out_n);
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
-        uint32_t v[32];
-        tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN), v);
-        tmem_ld_wait();
-        if (valid) {
-          float* g = reinterpret_cast<float*>(p.out);
+        if (half == 0) {
+          uint32_t v[32];
+          tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN), v);
+          tmem_ld_wait();
+          if (valid) {
+            float* g = reinterpret_cast<float*>(p.out);
 #pragma unroll
-          for (int q = 0; q < 12; ++q) {
-            const int c = q % 3, pw = (q / 3) & 1, ph = q / 6;
-            const long long o = (((long long)n * 3 + c) * p.img_h + (2 * h + ph)) * p.img_w + (2 * w + pw);
-            g[o] = __fdiv_rn(__uint_as_float(v[q]), __ldg(p.std_dev + c));
+            for (int q = 0; q < 12; ++q) {
+              const int c = q % 3, pw = (q / 3) & 1, ph = q / 6;
+              const long long o = (((long long)n * 3 + c) * p.img_h + (2 * h + ph)) * p.img_w + (2 * w + pw);
+              g[o] = __fdiv_rn(__uint_as_float(v[q]), __ldg(p.std_dev + c));
+            }
           }
         }
         tc_fence_before();
@@ -321,118 +417,96 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     } else {
-      // Sub-tiles of 64 channels: TMEM -> registers -> (bias, residual, ReLU, mask) -> swizzled smem
-      // staging -> TMA store.  Residual / mask tiles arrive by TMA into the same slot, issued by the
-      // epilogue leader two sub-tiles ahead.
+      // Sub-tiles of 64 channels: TMEM -> registers -> (+shift, ReLU, bit masks) -> bf16 -> swizzled smem
+      // staging -> TMA store.  The residual / skip gradient was already accumulated by the MMA warp.
+      // One named barrier per sub-tile; four staging slots.
       constexpr int kSub = BN / 64;
-      const bool leader = threadIdx.x == kEpiWarp0 * 32;
-      const bool has_aux = n_aux > 0;
+      const bool leader = etid == 0;
       const uint32_t out0 = smem_u32(out_smem);
-      const uint32_t aux0 = smem_u32(aux_smem);
-      const uint32_t add_off = 0;
-      const uint32_t mask_off = p.has_add ? kSubTileBytes : 0;
+      const uint32_t bias0 = smem_u32(bias_smem);
       const uint32_t row_off = (uint32_t)row * 128u;
       const uint32_t sw = (uint32_t)(row & 7);
+      const int tile_px = p.bw * p.bh;
+      const bool has_bias = p.bias != nullptr;
+      const bool relu = p.relu != 0;
+      const bool has_mask_in = p.mask_in != nullptr;
+      const bool has_mask_out = relu && p.mask_out != nullptr;
+      int oslot = 0;            // output staging slot of the sub-tile being produced
 
-      // aux prefetch cursor (leader only): runs aux_depth sub-tiles ahead of the consumer
-      int pf_tile = blockIdx.x, pf_j = 0;
-      auto issue_aux = [&](int slot) {
-        const TileCoord tc = tile_coord(p, pf_tile, BN);
-        uint8_t* base = aux_smem + slot * aux_slot_bytes;
-        mbar_expect_tx(&aux_bar[slot], (uint32_t)aux_slot_bytes);
-        if (p.has_add) tma_load_4d(&maps.add, &aux_bar[slot], base + add_off, tc.c0 + 64 * pf_j, tc.w0, tc.h0, tc.n0);
-        if (p.has_mask) tma_load_4d(&maps.mask, &aux_bar[slot], base + mask_off, tc.c0 + 64 * pf_j, tc.w0, tc.h0, tc.n0);
-        if (++pf_j == kSub) { pf_j = 0; pf_tile += gridDim.x; }
-      };
-      if (leader && has_aux) {
-        if (p.has_add) prefetch_tmap(&maps.add);
-        if (p.has_mask) prefetch_tmap(&maps.mask);
-        for (int s = 0; s < aux_depth; ++s)
-          if (pf_tile < total_tiles) issue_aux(s);
-      }
-      int aslot = 0;            // aux ring position of the sub-tile being consumed
-      uint32_t aphase = 0;
-
-      uint32_t e = 0;   // running sub-tile counter: output staging slot = e & 1
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const TileCoord tc = tile_coord(p, tile, BN);
+        // output pixel of this thread's row (bit-mask addressing) and whether it exists
+        const int wi = row % p.bw, hi = (row / p.bw) % p.bh, ni = row / tile_px;
+        const int tw = tc.w0 + wi, th = tc.h0 + hi, tn = tc.n0 + ni;
+        const bool valid = (tw < p.out_w) && (th < p.out_h) && (tn < p.out_n);
+        const long long pixel = ((long long)tn * p.full_h + (th * p.pix_sub + p.pix_ph)) * p.full_w +
+                                (tw * p.pix_sub + p.pix_pw);
+        const long long mword0 = ((long long)(tc.c0 >> 6) * p.mask_pixels + pixel) * 2 + half;
+        // folded-BN shift of the NEXT tile goes to the other accumulator's copy
+        if (has_bias && etid < BN && tile + (int)gridDim.x < total_tiles)
+          bias_smem[(acc ^ 1) * 256 + etid] = __ldg(p.bias + tile_coord(p, tile + gridDim.x, BN).c0 + etid);
+        uint32_t mword[kSub];
+#pragma unroll
+        for (int j = 0; j < kSub; ++j)
+          mword[j] = (has_mask_in && valid) ? __ldg(p.mask_in + mword0 + (long long)j * p.mask_pixels * 2) : 0xffffffffu;
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
-        const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN);
-#pragma unroll 1
-        for (int j = 0; j < kSub; ++j, ++e) {
-          const int slot = (int)(e & 1u);
-          const uint32_t obase = out0 + (uint32_t)(slot * kSubTileBytes);
-          const uint32_t abase = aux0 + (uint32_t)(aslot * aux_slot_bytes);
-          // the TMA store issued from this staging slot two sub-tiles ago must have finished reading it
-          if (leader) bulk_wait_read<1>();
-          epi_bar();
-          if (has_aux) mbar_wait(&aux_bar[aslot], aphase);
+        const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + half * 32);
 #pragma unroll
-          for (int hf = 0; hf < 2; ++hf) {
-            uint32_t v[32];
-            tmem_ld32(taddr0 + (uint32_t)(j * 64 + hf * 32), v);
-            tmem_ld_wait();
-            float f[32];
+        for (int j = 0; j < kSub; ++j) {
+          float f[32];
+          tmem_ld32f(taddr0 + (uint32_t)(j * 64), f);
+          const uint32_t obase = out0 + (uint32_t)(oslot * kSubTileBytes);
+          tmem_ld_wait();
+          if (j == kSub - 1) {
+            // every TMEM read of this accumulator has completed: hand it back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+          }
+          if (has_bias) {
+            const uint32_t bb = bias0 + (uint32_t)((acc * 256 + j * 64 + half * 32) * 4);
 #pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
-            if (p.bias) {
-              const float4* b4 = reinterpret_cast<const float4*>(p.bias + tc.c0 + j * 64 + hf * 32);
-#pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                const float4 b = __ldg(b4 + i);
-                f[4 * i] += b.x; f[4 * i + 1] += b.y; f[4 * i + 2] += b.z; f[4 * i + 3] += b.w;
-              }
+            for (int i = 0; i < 8; ++i) {
+              const float4 b = lds_f4(bb + 16u * i);
+              add2(f[4 * i], f[4 * i + 1], b.x, b.y);
+              add2(f[4 * i + 2], f[4 * i + 3], b.z, b.w);
             }
-            if (p.has_add) {
+          }
+          if (has_mask_out) {
+            uint32_t bits = 0;
 #pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const uint4 a = lds128(abase + add_off + row_off + ((((uint32_t)(hf * 4 + i)) ^ sw) << 4));
-                f[8 * i] += bf16_lo(a.x); f[8 * i + 1] += bf16_hi(a.x);
-                f[8 * i + 2] += bf16_lo(a.y); f[8 * i + 3] += bf16_hi(a.y);
-                f[8 * i + 4] += bf16_lo(a.z); f[8 * i + 5] += bf16_hi(a.z);
-                f[8 * i + 6] += bf16_lo(a.w); f[8 * i + 7] += bf16_hi(a.w);
-              }
+            for (int i = 0; i < 32; ++i) bits |= (f[i] > 0.f ? 1u : 0u) << i;
+            if (valid) p.mask_out[mword0 + (long long)j * p.mask_pixels * 2] = bits;
+          }
+          if (has_mask_in) {
+            const uint32_t mw = mword[j];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = ((mw >> i) & 1u) ? f[i] : 0.f;
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            uint4 o;
+            if (relu) {
+              o.x = pack_bf16x2_relu(f[8 * i], f[8 * i + 1]); o.y = pack_bf16x2_relu(f[8 * i + 2], f[8 * i + 3]);
+              o.z = pack_bf16x2_relu(f[8 * i + 4], f[8 * i + 5]); o.w = pack_bf16x2_relu(f[8 * i + 6], f[8 * i + 7]);
+            } else {
+              o.x = pack_bf16x2(f[8 * i], f[8 * i + 1]); o.y = pack_bf16x2(f[8 * i + 2], f[8 * i + 3]);
+              o.z = pack_bf16x2(f[8 * i + 4], f[8 * i + 5]); o.w = pack_bf16x2(f[8 * i + 6], f[8 * i + 7]);
             }
-            if (p.relu) {
-#pragma unroll
-              for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
-            }
-            if (p.has_mask) {
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const uint4 m = lds128(abase + mask_off + row_off + ((((uint32_t)(hf * 4 + i)) ^ sw) << 4));
-                const uint32_t mm[4] = {m.x, m.y, m.z, m.w};
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                  if (!(bf16_lo(mm[k]) > 0.f)) f[8 * i + 2 * k] = 0.f;
-                  if (!(bf16_hi(mm[k]) > 0.f)) f[8 * i + 2 * k + 1] = 0.f;
-                }
-              }
-            }
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              uint4 o;
-              o.x = pack_bf16x2(f[8 * i], f[8 * i + 1]);
-              o.y = pack_bf16x2(f[8 * i + 2], f[8 * i + 3]);
-              o.z = pack_bf16x2(f[8 * i + 4], f[8 * i + 5]);
-              o.w = pack_bf16x2(f[8 * i + 6], f[8 * i + 7]);
-              sts128(obase + row_off + ((((uint32_t)(hf * 4 + i)) ^ sw) << 4), o);
-            }
+            sts128(obase + row_off + ((((uint32_t)(half * 4 + i)) ^ sw) << 4), o);
           }
           fence_async_smem();          // generic-proxy smem writes -> visible to the TMA store
           epi_bar();
           if (leader) {
-            tma_store_4d(&maps.out, out_smem + slot * kSubTileBytes, tc.c0 + 64 * j, tc.w0, tc.h0, tc.n0);
+            tma_store_4d(&maps.out, out_smem + oslot * kSubTileBytes, tc.c0 + 64 * j, tc.w0, tc.h0, tc.n0);
             bulk_commit();
-            if (has_aux && pf_tile < total_tiles) issue_aux(aslot);   // this aux slot is free again
+            // four staging slots: before the next barrier all but the two newest stores must have
+            // finished reading their slot
+            bulk_wait_read<2>();
           }
-          if (has_aux && ++aslot == aux_depth) { aslot = 0; aphase ^= 1u; }
+          oslot = (oslot + 1) & 3;
         }
-        // accumulator drained: hand the TMEM buffer back to the MMA warp
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty_bar[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
       if (leader) bulk_wait_read<0>();
@@ -460,20 +534,12 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
   }
   const long long total = (long long)p.tiles_w * p.tiles_h * p.tiles_n * p.tiles_c;
   if (total <= 0) return ADVB200_OK;
-  const int n_aux = (p.has_add ? 1 : 0) + (p.has_mask ? 1 : 0);
-  const int out_bytes = (BN == 16) ? 0 : 2 * kSubTileBytes;
-  // aux ring: as deep as possible (HBM latency ~ two tiles of epilogue) while the operand ring keeps
-  // at least three stages
-  int depth = n_aux ? kMaxAuxDepth : 0, stages = 0;
-  for (;; --depth) {
-    stages = (kSmemBudget - 1024 - kBarrierBytes - out_bytes - depth * n_aux * kSubTileBytes) / C::kStageBytes;
-    if (!n_aux || stages >= (n_aux == 1 ? 4 : 3) || depth <= 2) break;
-  }
+  int stages = (kSmemBudget - Smem<BN>::fixed_bytes()) / C::kStageBytes;
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return fail(ADVB200_ERR_ARG, "conv_gemm: tile configuration does not fit shared memory");
   p.stages = stages;
-  p.aux_depth = depth;
-  const int smem_bytes = stages * C::kStageBytes + out_bytes + depth * n_aux * kSubTileBytes + 1024 + kBarrierBytes;
+  p.aux_depth = 0;
+  const int smem_bytes = stages * C::kStageBytes + Smem<BN>::fixed_bytes();
   const int grid = (int)(total < kNumSMs ? total : kNumSMs);
   conv_gemm_kernel<BN><<<grid, kThreads, smem_bytes, stream>>>(maps, p);
   ADV_LAUNCHED();

@@ -30,8 +30,15 @@ struct ConvGemmParams {
   void* out;                      // epi 1 only: fp32 NCHW image gradient (epi 0 stores through maps.out)
   const float* bias;              // [cout] or null
   int has_add;                    // residual / other-branch gradient tile read through maps.add
-  int has_mask;                   // forward activation (maps.mask) whose sign gates the gradient
   int relu;
+  // ReLU bit masks, one bit per (pixel, channel): word (c/64, pixel, (c/32)&1), bit c%32.
+  //   mask_in : gates the gradient written by a dgrad launch (bit set <=> forward output > 0)
+  //   mask_out: written by a forward launch with relu (bit set <=> output > 0)
+  const uint32_t* mask_in;
+  uint32_t* mask_out;
+  long long mask_pixels;          // pixels of the output tensor (plane stride of the mask)
+  int pix_sub, pix_ph, pix_pw;    // output pixel (h, w) of tile coords (th, tw): (th*sub+ph, tw*sub+pw)
+  int full_h, full_w;             // full-resolution output height / width
   int stages;                     // smem ring depth chosen by the host for this launch
   int aux_depth;                  // residual/mask prefetch ring depth (sub-tiles), host-chosen
   int epi;                        // 0: bf16 NHWC store; 1: conv1 input-gradient scatter (fp32 NCHW)
@@ -44,7 +51,6 @@ struct ConvGemmMaps {
   CUtensorMap b;      // packed weights
   CUtensorMap out;    // output tile store (64-channel boxes, same pixel box as a[])
   CUtensorMap add;    // optional, output-shaped
-  CUtensorMap mask;   // optional, output-shaped
 };
 
 // Launch on `stream`.  bn_cols in {16, 64, 128, 256}.  Fills p.stages.

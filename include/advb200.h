@@ -173,6 +173,10 @@ int64_t advb200_launch_count(void);
  * returns the summed device time (ms) and the number of launches, and clears the list. */
 int advb200_profile_enable(int on);
 int advb200_profile_read(double* conv_ms_host, int64_t* conv_launches_host);
+/* Same list as CSV text, one line per launch: name,bn,tiles,ksteps,stages,ms,flops,bytes (algorithmic
+ * flops / HBM bytes of that launch).  Writes at most cap bytes (NUL-terminated) into buf_host, returns
+ * the size needed, and clears the list. */
+int64_t advb200_profile_dump(char* buf_host, int64_t cap);
 
 #ifdef __cplusplus
 }
