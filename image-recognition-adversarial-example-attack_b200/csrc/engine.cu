@@ -181,6 +181,33 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     return ADVB200_OK;
   }
 
+  if (ksize == 3 && stride == 1 && gemm_k == 64 && gemm_n == 64 && out.w % 8 == 0 && !add &&
+      !getenv("ADVB200_NO_HALO")) {
+    // halo mode: tile = 8 x 16 pixels of one image; one (10 x 18)-pixel box feeds all nine taps and the
+    // 9 x 64 x 64 weights stay resident in shared memory
+    ADV_CHECK_ARG(out.h == in.h && out.w == in.w && in.n == out.n, "tc conv halo: shape mismatch");
+    p.bw = 8; p.bh = 16; p.bn = 1;
+    p.tiles_w = out.w / 8; p.tiles_h = cdiv(out.h, 16); p.tiles_n = out.n; p.tiles_c = 1;
+    t.bn = 64;
+    p.out_w = out.w; p.out_h = out.h; p.out_n = out.n;
+    p.halo = 1; p.halo_w0 = -1; p.halo_h0 = -1; p.halo_rows = 10 * 18; p.sbo_rows = 10;
+    p.ntaps = 0;
+    for (int r = 0; r < 3; ++r)
+      for (int s = 0; s < 3; ++s) {
+        const int i = p.ntaps++;
+        const int dh = dgrad ? 1 - r : r - 1, dw = dgrad ? 1 - s : s - 1;
+        p.tap_row[i] = (1 + dh) * 10 + (1 + dw);
+        p.tap_brow[i] = (r * 3 + s) * gemm_n;
+      }
+    int rc = make_a(&t.maps.a[0], in, 1, 0, 0, 10, 18, 1);
+    if (!rc) rc = make_out_maps(t, out, 1, 0, 0);
+    if (!rc) rc = make_b(&t.maps.b, 64);
+    if (rc) return rc;
+    annotate(op, "", (double)out.n * out.h * out.w, 9, 1.0);
+    ops.push_back(op);
+    return ADVB200_OK;
+  }
+
   if (!dgrad) {
     // forward conv: tiles over the OUTPUT pixel grid
     ADV_CHECK_ARG(out.h == in.h / stride && out.w == in.w / stride && in.n == out.n, "tc conv fwd: shape mismatch");
@@ -450,22 +477,27 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
       Op op; op.kind = Op::TC;
       TcOp& t = op.tc; ConvGemmParams& p = t.p;
       memset(&p, 0, sizeof p);
-      p.bw = 16; p.bh = 8; p.bn = 1;
-      p.tiles_w = 7; p.tiles_h = 14; p.tiles_n = n; p.tiles_c = 1;
+      // tile = 8 x 16 output pixels; halo mode: one (8 x 19)-row box of the hcol operand feeds the four
+      // vertical taps, the 4 x 64 x 64 weights stay resident
+      p.bw = 8; p.bh = 16; p.bn = 1;
+      p.tiles_w = 14; p.tiles_h = 7; p.tiles_n = n; p.tiles_c = 1;
       t.bn = 64;
       p.ntaps = 4; p.kblocks = 1;
-      for (int i = 0; i < 4; ++i) { p.tap_map[i] = 0; p.tap_dw[i] = 0; p.tap_dh[i] = i; p.tap_brow[i] = i * 64; }
+      p.halo = 1; p.halo_w0 = 0; p.halo_h0 = 0; p.halo_rows = 8 * 19; p.sbo_rows = 8;
+      for (int i = 0; i < 4; ++i) { p.tap_row[i] = i * 8; p.tap_brow[i] = i * 64; }
       p.out_w = 112; p.out_h = 112; p.out_n = n; p.cout = 64;
+      p.pix_sub = 1; p.full_h = 112; p.full_w = 112; p.mask_pixels = (long long)n * 112 * 112;
       p.bias = w0.shift; p.relu = 1; p.epi = 0;
       memset(&t.maps, 0, sizeof t.maps);
       const uint64_t dims[4] = {64, 112, 115, (uint64_t)n};
       const uint64_t strides[3] = {128, 128ull * 112, 128ull * 112 * 115};
-      const uint32_t box[4] = {64, 16, 8, 1};
+      const uint32_t box[4] = {64, 8, 19, 1};
       rc = make_tmap_bf16(&t.maps.a[0], m->t_in.p, 4, dims, strides, box);
       {
         const uint64_t od[4] = {64, 112, 112, (uint64_t)n};
         const uint64_t os[3] = {128, 128ull * 112, 128ull * 112 * 112};
-        if (!rc) rc = make_tmap_bf16(&t.maps.out, m->c1.p, 4, od, os, box);
+        const uint32_t obox[4] = {64, 8, 16, 1};
+        if (!rc) rc = make_tmap_bf16(&t.maps.out, m->c1.p, 4, od, os, obox);
       }
       const uint64_t bd[2] = {64, 256};
       const uint64_t bs[1] = {128};
@@ -612,21 +644,23 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
       Op op; op.kind = Op::TC;
       TcOp& t = op.tc; ConvGemmParams& p = t.p;
       memset(&p, 0, sizeof p);
-      p.bw = 16; p.bh = 8; p.bn = 1;
-      p.tiles_w = 7; p.tiles_h = 14; p.tiles_n = n; p.tiles_c = 1;
+      // halo mode: one (11 x 19)-pixel box of the conv1-output gradient feeds all 4 x 4 taps
+      p.bw = 8; p.bh = 16; p.bn = 1;
+      p.tiles_w = 14; p.tiles_h = 7; p.tiles_n = n; p.tiles_c = 1;
       t.bn = 16;
       p.ntaps = 16; p.kblocks = 1;
+      p.halo = 1; p.halo_w0 = -1; p.halo_h0 = -1; p.halo_rows = 11 * 19; p.sbo_rows = 11;
       for (int tt = 0; tt < 4; ++tt)
         for (int u = 0; u < 4; ++u) {
           const int i = tt * 4 + u;
-          p.tap_map[i] = 0; p.tap_dh[i] = 2 - tt; p.tap_dw[i] = 2 - u; p.tap_brow[i] = i * 16;
+          p.tap_row[i] = (2 - tt + 1) * 11 + (2 - u + 1); p.tap_brow[i] = i * 16;
         }
       p.out_w = 112; p.out_h = 112; p.out_n = n; p.cout = 16;
       p.epi = 1; p.img_h = kImg; p.img_w = kImg;
       p.out = nullptr;   // patched per call (grad_x_out)
       const uint64_t dims[4] = {64, 112, 112, (uint64_t)n};
       const uint64_t strides[3] = {128, 128ull * 112, 128ull * 112 * 112};
-      const uint32_t box[4] = {64, 16, 8, 1};
+      const uint32_t box[4] = {64, 11, 19, 1};
       memset(&t.maps, 0, sizeof t.maps);
       rc = make_tmap_bf16(&t.maps.a[0], m->g_c1, 4, dims, strides, box);
       t.maps.out = t.maps.a[0];   // unused by the scatter epilogue; keeps the prefetch well-defined

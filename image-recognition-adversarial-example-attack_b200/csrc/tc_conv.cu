@@ -135,11 +135,13 @@ __device__ __forceinline__ void tmem_ld_wait() {
 }
 
 // K-major, 128B-swizzled operand tile: rows of 128 bytes, 8-row atoms of 1024 bytes.
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+// sbo_bytes: distance between consecutive 8-row groups (1024 for a dense tile; the halo-mode A
+// operand uses the halo box width * 128, and start addresses shifted by whole rows).
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t sbo_bytes = 1024) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);   // start address, 16-byte units
   d |= (uint64_t)1 << 16;                        // leading byte offset (unused for swizzled K-major)
-  d |= (uint64_t)(1024 >> 4) << 32;              // stride byte offset: 8 rows * 128 B
+  d |= (uint64_t)(sbo_bytes >> 4) << 32;         // stride byte offset between 8-row groups
   d |= (uint64_t)1 << 46;                        // descriptor version (Blackwell)
   d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
   return d;
@@ -231,7 +233,10 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
   using C = Cfg<BN>;
   extern __shared__ __align__(1024) uint8_t smem[];
   constexpr int n_out_slots = Smem<BN>::out_slots();
-  uint8_t* out_smem = smem + p.stages * C::kStageBytes;     // n_out_slots x 16 KB output staging
+  // [resident weights (halo mode)] [operand ring] [output staging] [identity] [shift] [barriers]
+  uint8_t* ring = smem + p.ring_off;
+  const int stage_bytes = p.stage_bytes;
+  uint8_t* out_smem = ring + p.stages * stage_bytes;        // n_out_slots x 16 KB output staging
   uint8_t* ident_smem = out_smem + n_out_slots * kSubTileBytes;   // 64x64 bf16 identity (K-major, swizzled)
   float* bias_smem = reinterpret_cast<float*>(ident_smem + kIdentBytes);   // [2][256]
   uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(bias_smem) + kBiasBytes);
@@ -239,7 +244,8 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
   uint64_t* empty_bar = bars + kMaxStages;
   uint64_t* tfull_bar = bars + 2 * kMaxStages;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* bres_bar = tempty_bar + 2;                      // resident weights landed (halo mode)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bres_bar + 1);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -252,6 +258,7 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
     if (p.has_add) prefetch_tmap(&maps.add);
     for (int s = 0; s < kMaxStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], 8); }
+    mbar_init(bres_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -298,6 +305,19 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      if (p.halo) {
+        // all taps' weights once, then one halo box of input pixels per tile
+        mbar_expect_tx(bres_bar, (uint32_t)(p.ntaps * BN * 128));
+        for (int tap = 0; tap < p.ntaps; ++tap) tma_load_2d(&maps.b, bres_bar, smem + tap * BN * 128, 0, p.tap_brow[tap]);
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+          const TileCoord tc = tile_coord(p, tile, BN);
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_expect_tx(&full_bar[stage], (uint32_t)(p.halo_rows * 128));
+          tma_load_4d(&maps.a[0], &full_bar[stage], ring + stage * stage_bytes, 0, tc.w0 + p.halo_w0,
+                      tc.h0 + p.halo_h0, tc.n0);
+          if (++stage == nstages) { stage = 0; phase ^= 1; }
+        }
+      } else
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const TileCoord tc = tile_coord(p, tile, BN);
         for (int tap = 0; tap < p.ntaps; ++tap) {
@@ -306,7 +326,7 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           const int brow = p.tap_brow[tap] + tc.c0;
           for (int kb = 0; kb < p.kblocks; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1);
-            uint8_t* sa = smem + stage * C::kStageBytes;
+            uint8_t* sa = ring + stage * stage_bytes;
             uint8_t* sb = sa + kATileBytes;
             mbar_expect_tx(&full_bar[stage], C::kStageBytes);
             tma_load_4d(ma, &full_bar[stage], sa, kb * kBlockK, cw, ch, tc.n0);
@@ -319,7 +339,7 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           for (int j = 0; j < BN / 64; ++j) {
             mbar_wait(&empty_bar[stage], phase ^ 1);
             mbar_expect_tx(&full_bar[stage], kATileBytes);
-            tma_load_4d(&maps.add, &full_bar[stage], smem + stage * C::kStageBytes, tc.c0 + 64 * j, tc.w0, tc.h0,
+            tma_load_4d(&maps.add, &full_bar[stage], ring + stage * stage_bytes, tc.c0 + 64 * j, tc.w0, tc.h0,
                         tc.n0);
             if (++stage == nstages) { stage = 0; phase ^= 1; }
           }
@@ -340,10 +360,25 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        if (p.halo) {
+          if (tile == (int)blockIdx.x) { mbar_wait(bres_bar, 0); }
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(ring + stage * stage_bytes);
+          for (int tap = 0; tap < p.ntaps; ++tap) {
+            const uint64_t adesc = make_smem_desc(sa + (uint32_t)(p.tap_row[tap] * 128), (uint32_t)(p.sbo_rows * 128));
+            const uint64_t bdesc = make_smem_desc(smem_u32(smem + tap * BN * 128));
+#pragma unroll
+            for (int k = 0; k < kBlockK / 16; ++k)
+              umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (tap | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == nstages) { stage = 0; phase ^= 1; }
+        } else
         for (int ks = 0; ks < ksteps; ++ks) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
+          const uint32_t sa = smem_u32(ring + stage * stage_bytes);
           const uint64_t adesc = make_smem_desc(sa);
           const uint64_t bdesc = make_smem_desc(sa + kATileBytes);
 #pragma unroll
@@ -363,7 +398,7 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           for (int j = 0; j < BN / 64; ++j) {
             mbar_wait(&full_bar[stage], phase);
             tc_fence_after();
-            const uint64_t adesc = make_smem_desc(smem_u32(smem + stage * C::kStageBytes));
+            const uint64_t adesc = make_smem_desc(smem_u32(ring + stage * stage_bytes));
 #pragma unroll
             for (int k = 0; k < kBlockK / 16; ++k)
               umma_bf16(d_tmem + (uint32_t)(64 * j), adesc + (uint64_t)(2 * k), idesc_b + (uint64_t)(2 * k), idesc64, 1u);
@@ -402,13 +437,21 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN), v);
           tmem_ld_wait();
           if (valid) {
+            // two horizontally adjacent image pixels (pw = 0, 1) per 8-byte store
             float* g = reinterpret_cast<float*>(p.out);
+            float inv[3];
 #pragma unroll
-            for (int q = 0; q < 12; ++q) {
-              const int c = q % 3, pw = (q / 3) & 1, ph = q / 6;
-              const long long o = (((long long)n * 3 + c) * p.img_h + (2 * h + ph)) * p.img_w + (2 * w + pw);
-              g[o] = __fdiv_rn(__uint_as_float(v[q]), __ldg(p.std_dev + c));
-            }
+            for (int c = 0; c < 3; ++c) inv[c] = __ldg(p.std_dev + c);
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+#pragma unroll
+              for (int ph = 0; ph < 2; ++ph) {
+                const long long o = (((long long)n * 3 + c) * p.img_h + (2 * h + ph)) * p.img_w + 2 * w;
+                float2 v2;
+                v2.x = __fdiv_rn(__uint_as_float(v[(ph * 2 + 0) * 3 + c]), inv[c]);
+                v2.y = __fdiv_rn(__uint_as_float(v[(ph * 2 + 1) * 3 + c]), inv[c]);
+                *reinterpret_cast<float2*>(g + o) = v2;
+              }
           }
         }
         tc_fence_before();
@@ -534,12 +577,19 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
   }
   const long long total = (long long)p.tiles_w * p.tiles_h * p.tiles_n * p.tiles_c;
   if (total <= 0) return ADVB200_OK;
-  int stages = (kSmemBudget - Smem<BN>::fixed_bytes()) / C::kStageBytes;
+  p.ring_off = 0;
+  p.stage_bytes = C::kStageBytes;
+  if (p.halo) {
+    ADV_CHECK_ARG(p.kblocks == 1 && p.tiles_c == 1 && !p.has_add, "conv_gemm: halo mode needs K = 64, one column block");
+    p.ring_off = (p.ntaps * BN * 128 + 1023) & ~1023;
+    p.stage_bytes = (p.halo_rows * 128 + 1023) & ~1023;
+  }
+  int stages = (kSmemBudget - Smem<BN>::fixed_bytes() - p.ring_off) / p.stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return fail(ADVB200_ERR_ARG, "conv_gemm: tile configuration does not fit shared memory");
   p.stages = stages;
   p.aux_depth = 0;
-  const int smem_bytes = stages * C::kStageBytes + Smem<BN>::fixed_bytes();
+  const int smem_bytes = p.ring_off + stages * p.stage_bytes + Smem<BN>::fixed_bytes();
   const int grid = (int)(total < kNumSMs ? total : kNumSMs);
   conv_gemm_kernel<BN><<<grid, kThreads, smem_bytes, stream>>>(maps, p);
   ADV_LAUNCHED();

@@ -25,6 +25,15 @@ struct ConvGemmParams {
   int tap_dw[kMaxTaps];           // pixel shift of the tap along w / h
   int tap_dh[kMaxTaps];
   int tap_brow[kMaxTaps];         // first row of the tap's weights in the packed B matrix
+  // halo mode (kblocks == 1, tiles_c == 1): ONE TMA box of (bw+halo) x (bh+halo) input pixels per tile
+  // serves every tap — tap t reads the rows starting at tap_row[t], 8-row groups sbo_rows rows apart
+  // (tcgen05 applies the 128B swizzle to absolute smem addresses, so row-shifted descriptors are legal;
+  // verified by tools/umma_probe.cu) — and the whole weight matrix stays resident in shared memory.
+  int halo;                       // 0 = one TMA box per tap (generic), 1 = halo mode
+  int halo_w0, halo_h0;           // halo box origin relative to the tile origin (<= 0)
+  int halo_rows;                  // pixels in the halo box
+  int sbo_rows;                   // rows between consecutive 8-row groups (= halo box width)
+  int tap_row[kMaxTaps];
   // output extent in tile coordinates (w, h, n) and channels
   int out_w, out_h, out_n, cout;
   void* out;                      // epi 1 only: fp32 NCHW image gradient (epi 0 stores through maps.out)
@@ -40,6 +49,7 @@ struct ConvGemmParams {
   int pix_sub, pix_ph, pix_pw;    // output pixel (h, w) of tile coords (th, tw): (th*sub+ph, tw*sub+pw)
   int full_h, full_w;             // full-resolution output height / width
   int stages;                     // smem ring depth chosen by the host for this launch
+  int stage_bytes, ring_off;      // ring slot size and offset of the ring (after resident weights)
   int aux_depth;                  // residual/mask prefetch ring depth (sub-tiles), host-chosen
   int epi;                        // 0: bf16 NHWC store; 1: conv1 input-gradient scatter (fp32 NCHW)
   const float* std_dev;           // epi 1: device pointer to std[3]; gradient is divided by std[c]
