@@ -8,6 +8,7 @@
 // Reference: model(normalize_batch(x)) attack.py:30,57,111; autograd.grad(loss, x) attack.py:32,59;
 // loss.backward() attack.py:130 (without its unused weight gradients); _layer3_features
 // defense_experiments.py:221-257.
+#include <cmath>
 #include <cstdlib>
 #include <vector>
 
@@ -37,6 +38,7 @@ struct ConvW {
   int cin = 0, cout = 0, k = 0, stride = 1;
   float* scale = nullptr;
   float* shift = nullptr;
+  float* shift_fused = nullptr;   // conv3 of a downsample block: shift(conv3) + shift(downsample)
   float* f_fwd = nullptr;   // fp32 [(rs*cin+ci), co]
   float* f_dgrad = nullptr; // fp32 [(rs*cout+co), ci]
   bf16* b_fwd = nullptr;    // bf16 [(rs*cout+co)][ci]
@@ -45,6 +47,7 @@ struct ConvW {
 
 struct TcOp {
   int bn = 0;
+  int pair = 0;     // 1: CTA pairs (tcgen05 cta_group::2) on 256-pixel tiles
   ConvGemmMaps maps;
   ConvGemmParams p;
 };
@@ -79,23 +82,95 @@ inline void tile_shape(int w, int h, int& bw, int& bh, int& bn) {
 }
 inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 
-// n_aux > 0 (residual / mask tiles staged in smem) caps the tile at 128 columns so the ring keeps
-// at least four stages next to the epilogue slots.
-inline int pick_bn(int gemm_n, long long m_tiles, int n_aux) {
+// Tile choice for one conv GEMM: BN columns, and whether CTA pairs (cta_group::2, 256-pixel tiles, weight
+// rows split across the pair) are used.  Score = wave efficiency x sqrt(MACs per operand element staged
+// per CTA): the L2<->SM fabric, not the tensor pipe, bounds the wide layers.
+struct TileChoice { int bn, pair; };
+inline TileChoice pick_tile(int gemm_n, long long m_tiles, int ksteps) {
+  static const char* force_pair = getenv("ADVB200_PAIR");      // tuning knobs: "0" / "1"
+  static const char* force_bn = getenv("ADVB200_BN");
   const int cands[3] = {256, 128, 64};
-  const double bonus[3] = {1.0, 0.97, 0.80};
-  int best = 64;
+  TileChoice best{64, 0};
   double best_score = -1;
-  for (int i = 0; i < 3; ++i) {
-    if (gemm_n % cands[i]) continue;
-    static const bool wide_aux = !getenv("ADVB200_NO_BN256_AUX");   // tuning knob
-    if (n_aux > 0 && cands[i] > 128 && !wide_aux) continue;
-    const long long tiles = m_tiles * (gemm_n / cands[i]);
-    const long long waves = (tiles + kNumSMs - 1) / kNumSMs;
-    const double eff = (double)tiles / (double)(waves * kNumSMs) * bonus[i];
-    if (eff > best_score) { best_score = eff; best = cands[i]; }
+  for (int pair = 0; pair < 2; ++pair) {
+    if (force_pair ? atoi(force_pair) != pair : (pair != (ksteps >= 8 ? 1 : 0))) continue;   // measured: pairs pay off
+                                                                                              // only on MMA-heavy tiles
+    for (int i = 0; i < 3; ++i) {
+      const int bn = cands[i];
+      if (gemm_n % bn) continue;
+      if (force_bn && atoi(force_bn) != bn && gemm_n % atoi(force_bn) == 0) continue;
+      const int units = pair ? kNumSMs / 2 : kNumSMs;
+      const long long tiles = (pair ? (m_tiles + 1) / 2 : m_tiles) * (gemm_n / bn);
+      const long long waves = (tiles + units - 1) / units;
+      const double eff = (double)tiles / (double)(waves * units);
+      const double intensity = 128.0 * bn / (128.0 + (pair ? bn / 2 : bn));
+      const double score = eff * sqrt(intensity);
+      if (score > best_score) { best_score = score; best = TileChoice{bn, pair}; }
+    }
   }
   return best;
+}
+
+// ---- fused pointwise (1x1) launches -------------------------------------------------------------
+// out[lattice pixel, :] = sum_i  W_i . src_i[pixel of src_i's own lattice, :]   (+ bias, ReLU, masks)
+// Each source reads its tensor at (h*sub+ph, w*sub+pw); the output is written at (h*osub+oph, w*osub+opw).
+// Used for conv3 + downsample (forward) and conv1-dgrad + downsample-dgrad (backward): the two GEMMs
+// accumulate in the same TMEM tile, so the branch tensor never goes through HBM.
+struct PwSrc { Act in; int sub, ph, pw; const bf16* wpack; };
+
+int tmap_act(CUtensorMap* m, const Act& t, int sub, int ph, int pw, int bw, int bh, int bnimg) {
+  const bf16* base = reinterpret_cast<const bf16*>(t.p) + ((long long)ph * t.w + pw) * t.c;
+  const uint64_t dims[4] = {(uint64_t)t.c, (uint64_t)(t.w / sub), (uint64_t)(t.h / sub), (uint64_t)t.n};
+  const uint64_t strides[3] = {(uint64_t)t.c * 2 * sub, (uint64_t)t.w * t.c * 2 * sub, (uint64_t)t.h * t.w * t.c * 2};
+  const uint32_t box[4] = {64, (uint32_t)bw, (uint32_t)bh, (uint32_t)bnimg};
+  return make_tmap_bf16(m, base, 4, dims, strides, box);
+}
+
+int build_pw_ops(std::vector<Op>& ops, const PwSrc* src, int nsrc, Act out, int osub, int oph, int opw,
+                 const float* bias, const uint32_t* mask, int relu, uint32_t* mask_out) {
+  ADV_CHECK_ARG(nsrc >= 1 && nsrc <= 2, "pw conv: one or two sources");
+  const int gemm_n = out.c;
+  const int lw = out.w / osub, lh = out.h / osub;
+  Op op;
+  op.kind = Op::TC;
+  TcOp& t = op.tc;
+  ConvGemmParams& p = t.p;
+  memset(&p, 0, sizeof p);
+  memset(&t.maps, 0, sizeof t.maps);
+  tile_shape(lw, lh, p.bw, p.bh, p.bn);
+  p.tiles_w = cdiv(lw, p.bw); p.tiles_h = cdiv(lh, p.bh); p.tiles_n = cdiv(out.n, p.bn);
+  int ksteps = 0;
+  double kin = 0, in_bytes = 0;
+  for (int i = 0; i < nsrc; ++i) {
+    ADV_CHECK_ARG(src[i].in.c % 64 == 0 && src[i].in.w / src[i].sub == lw && src[i].in.h / src[i].sub == lh &&
+                      src[i].in.n == out.n, "pw conv: source lattice mismatch");
+    ksteps += src[i].in.c / 64;
+    kin += src[i].in.c;
+    in_bytes += 2.0 * out.n * lw * lh * src[i].in.c;
+  }
+  { const TileChoice tcz = pick_tile(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, ksteps); t.bn = tcz.bn; t.pair = tcz.pair; }
+  p.tiles_c = gemm_n / t.bn;
+  p.out_w = lw; p.out_h = lh; p.out_n = out.n; p.cout = gemm_n;
+  p.bias = bias; p.relu = relu; p.mask_in = mask; p.mask_out = mask_out;
+  p.mask_pixels = (long long)out.n * out.h * out.w;
+  p.pix_sub = osub; p.pix_ph = oph; p.pix_pw = opw; p.full_h = out.h; p.full_w = out.w;
+  p.ntaps = nsrc; p.ksteps = ksteps; p.has_b2 = nsrc > 1; p.kblocks = 0;
+  int rc = tmap_act(&t.maps.out, out, osub, oph, opw, p.bw, p.bh, p.bn);
+  for (int i = 0; i < nsrc && !rc; ++i) {
+    p.tap_map[i] = i; p.tap_dw[i] = 0; p.tap_dh[i] = 0; p.tap_brow[i] = 0;
+    p.tap_kb[i] = src[i].in.c / 64; p.tap_bmap[i] = i;
+    rc = tmap_act(&t.maps.a[i], src[i].in, src[i].sub, src[i].ph, src[i].pw, p.bw, p.bh, p.bn);
+    const uint64_t dims[2] = {(uint64_t)src[i].in.c, (uint64_t)gemm_n};
+    const uint64_t strides[1] = {(uint64_t)src[i].in.c * 2};
+    const uint32_t box[2] = {64, (uint32_t)(t.pair ? t.bn / 2 : t.bn)};
+    if (!rc) rc = make_tmap_bf16(i ? &t.maps.b2 : &t.maps.b, src[i].wpack, 2, dims, strides, box);
+  }
+  if (rc) return rc;
+  const double pix = (double)out.n * lw * lh;
+  label_op(op, "", 2.0 * pix * gemm_n * kin,
+           in_bytes + 2.0 * pix * gemm_n * (1.0 + (mask ? 1.0 / 16 : 0) + (mask_out ? 1.0 / 16 : 0)) + 2.0 * gemm_n * kin);
+  ops.push_back(op);
+  return ADVB200_OK;
 }
 
 // ---- tcgen05 op construction ------------------------------------------------------------------
@@ -108,10 +183,10 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
   ADV_CHECK_ARG((ksize == 1 || ksize == 3) && (stride == 1 || stride == 2), "tc conv: unsupported geometry");
   const int kk = ksize * ksize;
 
-  auto make_b = [&](CUtensorMap* m, int bn) {
+  auto make_b = [&](CUtensorMap* m, int bn, int pair = 0) {
     const uint64_t dims[2] = {(uint64_t)gemm_k, (uint64_t)kk * gemm_n};
     const uint64_t strides[1] = {(uint64_t)gemm_k * 2};
-    const uint32_t box[2] = {64, (uint32_t)bn};
+    const uint32_t box[2] = {64, (uint32_t)(pair ? bn / 2 : bn)};
     return make_tmap_bf16(m, wpack, 2, dims, strides, box);
   };
   // 4-D map over an NHWC tensor or one of its stride-2 sub-lattices
@@ -160,7 +235,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     ADV_CHECK_ARG(m < (1ll << 31), "tc conv: too many pixels");
     p.bw = 128; p.bh = 1; p.bn = 1;
     p.tiles_w = (int)((m + 127) / 128); p.tiles_h = 1; p.tiles_n = 1;
-    t.bn = pick_bn(gemm_n, p.tiles_w, n_aux);
+    { const TileChoice tcz = pick_tile(gemm_n, p.tiles_w, p.kblocks); t.bn = tcz.bn; t.pair = tcz.pair; }
     p.tiles_c = gemm_n / t.bn;
     p.ntaps = 1;
     p.out_w = (int)m; p.out_h = 1; p.out_n = 1;
@@ -174,7 +249,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     int rc = flat_map(&t.maps.a[0], in.p, gemm_k);
     if (!rc) rc = flat_map(&t.maps.out, out.p, gemm_n);
     if (!rc && add) rc = flat_map(&t.maps.add, add, gemm_n);
-    if (!rc) rc = make_b(&t.maps.b, t.bn);
+    if (!rc) rc = make_b(&t.maps.b, t.bn, t.pair);
     if (rc) return rc;
     annotate(op, "", (double)m, 1, 1.0);
     ops.push_back(op);
@@ -214,7 +289,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     ADV_CHECK_ARG(stride == 1 || (in.h % 2 == 0 && in.w % 2 == 0), "tc conv fwd: stride 2 needs even sizes");
     tile_shape(out.w, out.h, p.bw, p.bh, p.bn);
     p.tiles_w = cdiv(out.w, p.bw); p.tiles_h = cdiv(out.h, p.bh); p.tiles_n = cdiv(out.n, p.bn);
-    t.bn = pick_bn(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, n_aux);
+    { const TileChoice tcz = pick_tile(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, kk * p.kblocks); t.bn = tcz.bn; t.pair = tcz.pair; }
     p.tiles_c = gemm_n / t.bn;
     p.out_w = out.w; p.out_h = out.h; p.out_n = out.n;
     int rc;
@@ -245,7 +320,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
           p.tap_dw[i] = (s == 0) ? -1 : 0;
         }
       }
-    rc = make_b(&t.maps.b, t.bn);
+    rc = make_b(&t.maps.b, t.bn, t.pair);
     if (rc) return rc;
     annotate(op, "", (double)out.n * out.h * out.w, p.ntaps, 1.0);
     ops.push_back(op);
@@ -257,7 +332,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     ADV_CHECK_ARG(out.h == in.h && out.w == in.w && in.n == out.n, "tc conv dgrad: shape mismatch");
     tile_shape(out.w, out.h, p.bw, p.bh, p.bn);
     p.tiles_w = cdiv(out.w, p.bw); p.tiles_h = cdiv(out.h, p.bh); p.tiles_n = cdiv(out.n, p.bn);
-    t.bn = pick_bn(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, n_aux);
+    { const TileChoice tcz = pick_tile(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, kk * p.kblocks); t.bn = tcz.bn; t.pair = tcz.pair; }
     p.tiles_c = gemm_n / t.bn;
     p.out_w = out.w; p.out_h = out.h; p.out_n = out.n;
     int rc = make_a(&t.maps.a[0], in, 1, 0, 0, p.bw, p.bh, p.bn);
@@ -270,7 +345,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
         p.tap_map[i] = 0; p.tap_dh[i] = 1 - r; p.tap_dw[i] = 1 - s;   // dX[h,w] += dY[h+1-r, w+1-s] W[r,s]
         p.tap_brow[i] = (r * 3 + s) * gemm_n;
       }
-    rc = make_b(&t.maps.b, t.bn);
+    rc = make_b(&t.maps.b, t.bn, t.pair);
     if (rc) return rc;
     annotate(op, "", (double)out.n * out.h * out.w, p.ntaps, 1.0);
     ops.push_back(op);
@@ -300,13 +375,13 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
       const int sw = out.w / 2, sh = out.h / 2;
       tile_shape(sw, sh, q.bw, q.bh, q.bn);
       q.tiles_w = cdiv(sw, q.bw); q.tiles_h = cdiv(sh, q.bh); q.tiles_n = cdiv(out.n, q.bn);
-      t2.bn = pick_bn(gemm_n, (long long)q.tiles_w * q.tiles_h * q.tiles_n, n_aux);
+      { const TileChoice tcz = pick_tile(gemm_n, (long long)q.tiles_w * q.tiles_h * q.tiles_n, q.ntaps * q.kblocks); t2.bn = tcz.bn; t2.pair = tcz.pair; }
       q.tiles_c = gemm_n / t2.bn;
       q.out_w = sw; q.out_h = sh; q.out_n = out.n;
       q.pix_sub = 2; q.pix_ph = ph; q.pix_pw = pw;
       int rc = make_a(&t2.maps.a[0], in, 1, 0, 0, q.bw, q.bh, q.bn);
       if (!rc) rc = make_out_maps(t2, out, 2, ph, pw);     // (ph, pw) sub-lattice of dX / residual / mask
-      if (!rc) rc = make_b(&t2.maps.b, t2.bn);
+      if (!rc) rc = make_b(&t2.maps.b, t2.bn, t2.pair);
       if (rc) return rc;
       {
         const char sfx[4] = {'/', (char)('0' + ph * 2 + pw), 0, 0};
@@ -347,7 +422,7 @@ int run_ops(std::vector<Op>& ops, cudaStream_t st) {
           cudaEventCreate(&e0); cudaEventCreate(&e1);
           cudaEventRecord(e0, st);
         }
-        rc = launch_conv_gemm(op.tc.bn, op.tc.maps, op.tc.p, st);
+        rc = launch_conv_gemm(op.tc.bn, op.tc.pair, op.tc.maps, op.tc.p, st);
         if (g_prof_on) {
           cudaEventRecord(e1, st);
           g_prof_events.push_back(ProfRec{e0, e1, &op});
@@ -439,6 +514,7 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
     a.p = bump.take((size_t)a.elems() * esz);
     return a;
   };
+  static const bool fuse = !getenv("ADVB200_NO_FUSE");   // conv3+downsample / conv1-dgrad+downsample-dgrad fusion
   static char lbl[48];
   auto setl = [&](const char* dir, const BlockSpec* s, const char* conv) {
     if (s) snprintf(lbl, sizeof lbl, "%s l%d.%d.%s", dir, s->layer + 1, s->idx, conv);
@@ -523,7 +599,7 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
     t.a = act(s.hin, s.hin, s.width);
     t.b = act(hout, hout, s.width);
     t.out = act(hout, hout, s.width * 4);
-    if (s.down) t.idn = act(hout, hout, s.width * 4);
+    if (s.down && !(tc && fuse)) t.idn = act(hout, hout, s.width * 4);
     if (tc) {   // ReLU bit masks of the three activations (1 bit per element) for the backward pass
       t.ma = reinterpret_cast<uint32_t*>(bump.take((size_t)t.a.elems() / 8));
       t.mb = reinterpret_cast<uint32_t*>(bump.take((size_t)t.b.elems() / 8));
@@ -539,14 +615,22 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
         setl("fwd", &s, "c2");
         if (!rc) rc = build_tc_ops(ops, c2.b_fwd, 3, s.stride, false, t.a, t.b, c2.shift, nullptr, nullptr, 1, t.mb);
         const bf16* res = reinterpret_cast<const bf16*>(t.x.p);
-        if (!rc && s.down) {
+        if (!rc && s.down && fuse) {
+          // conv3 + downsample in one launch: both GEMMs accumulate into the same TMEM tile
           const ConvW& cd = m->conv[s.conv_base + 3];
-          setl("fwd", &s, "ds");
-          rc = build_tc_ops(ops, cd.b_fwd, 1, s.stride, false, t.x, t.idn, cd.shift, nullptr, nullptr, 0);
-          res = reinterpret_cast<const bf16*>(t.idn.p);
+          setl("fwd", &s, "c3+ds");
+          const PwSrc src[2] = {{t.b, 1, 0, 0, c3.b_fwd}, {t.x, s.stride, 0, 0, cd.b_fwd}};
+          rc = build_pw_ops(ops, src, 2, t.out, 1, 0, 0, c3.shift_fused, nullptr, 1, t.mout);
+        } else {
+          if (!rc && s.down) {
+            const ConvW& cd = m->conv[s.conv_base + 3];
+            setl("fwd", &s, "ds");
+            rc = build_tc_ops(ops, cd.b_fwd, 1, s.stride, false, t.x, t.idn, cd.shift, nullptr, nullptr, 0);
+            res = reinterpret_cast<const bf16*>(t.idn.p);
+          }
+          setl("fwd", &s, "c3");
+          if (!rc) rc = build_tc_ops(ops, c3.b_fwd, 1, 1, false, t.b, t.out, c3.shift, res, nullptr, 1, t.mout);
         }
-        setl("fwd", &s, "c3");
-        if (!rc) rc = build_tc_ops(ops, c3.b_fwd, 1, 1, false, t.b, t.out, c3.shift, res, nullptr, 1, t.mout);
       } else {
         rc = build_simt_op(ops, c1.f_fwd, 1, 1, false, t.x, t.a, c1.shift, nullptr, nullptr, 1);
         if (!rc) rc = build_simt_op(ops, c2.f_fwd, 3, s.stride, false, t.a, t.b, c2.shift, nullptr, nullptr, 1);
@@ -591,7 +675,30 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
     }
     gbusy[ib] = false;                                   // g_b is dead after conv2's dgrad
     Act g_x = t.x;
-    if (s.down) {
+    if (s.down && tc && fuse) {
+      // conv1-dgrad + downsample-dgrad accumulate in TMEM: g_x = mask(x) * (W1^T g_a + Wds^T g_sum).
+      // Stride 2: one launch per parity class of x; only class (0,0) receives the downsample gradient.
+      const ConvW& cd = m->conv[s.conv_base + 3];
+      nxt = gacquire(); g_x.p = gbuf[nxt];
+      if (build && !rc) {
+        const uint32_t* mk = first ? nullptr : t.mx;
+        if (s.stride == 1) {
+          setl("bwd", &s, "c1+ds");
+          const PwSrc src[2] = {{g_a, 1, 0, 0, c1.b_dgrad}, {g_sum, 1, 0, 0, cd.b_dgrad}};
+          rc = build_pw_ops(m->ops_bwd, src, 2, g_x, 1, 0, 0, nullptr, mk, 0, nullptr);
+        } else {
+          for (int ph = 0; ph < 2 && !rc; ++ph)
+            for (int pw = 0; pw < 2 && !rc; ++pw) {
+              static char l2[16];
+              snprintf(l2, sizeof l2, (ph | pw) ? "c1/%d" : "c1+ds/%d", ph * 2 + pw);
+              setl("bwd", &s, l2);
+              const PwSrc src[2] = {{g_a, 2, ph, pw, c1.b_dgrad}, {g_sum, 1, 0, 0, cd.b_dgrad}};
+              rc = build_pw_ops(m->ops_bwd, src, (ph | pw) ? 1 : 2, g_x, 2, ph, pw, nullptr, mk, 0, nullptr);
+            }
+        }
+      }
+      gbusy[cur] = false;
+    } else if (s.down) {
       const ConvW& cd = m->conv[s.conv_base + 3];
       const int it = gacquire(); Act g_t = t.x; g_t.p = gbuf[it];      // downsample-branch gradient
       if (build && !rc) {
@@ -784,6 +891,14 @@ int advb200_model_create(const float* const* conv_w, const float* const* bn_gamm
       rc = launch_pack_bf16(conv_w[i], c.scale, c.b_fwd, c.b_dgrad, c.cout, c.cin, c.k, st);
     }
   }
+  for (const BlockSpec& bs : m->blocks) {
+    if (rc || !bs.down) continue;
+    ConvW& c3 = m->conv[bs.conv_base + 2];
+    const ConvW& cd = m->conv[bs.conv_base + 3];
+    c3.shift_fused = (float*)dalloc(c3.cout * 4);
+    if (!c3.shift_fused) { rc = fail(ADVB200_ERR_CUDA, "model_create: cudaMalloc failed"); break; }
+    rc = launch_vec_add(c3.shift, cd.shift, c3.shift_fused, c3.cout, st);
+  }
   if (!rc) {
     m->fc_w = (float*)dalloc((size_t)kClasses * kFeat * 4);
     m->fc_wt = (float*)dalloc((size_t)kClasses * kFeat * 4);
@@ -835,8 +950,8 @@ int64_t advb200_profile_dump(char* buf_host, int64_t cap) {
     cudaEventDestroy(pr.e0); cudaEventDestroy(pr.e1);
     const ConvGemmParams& q = pr.op->tc.p;
     char line[256];
-    snprintf(line, sizeof line, "%s,%d,%lld,%d,%d,%.6f,%.6g,%.6g\n", pr.op->name, pr.op->tc.bn,
-             (long long)q.tiles_w * q.tiles_h * q.tiles_n * q.tiles_c, q.ntaps * q.kblocks, q.stages, ms,
+    snprintf(line, sizeof line, "%s,%d%s,%lld,%d,%d,%.6f,%.6g,%.6g\n", pr.op->name, pr.op->tc.bn, pr.op->tc.pair ? "p" : "",
+             (long long)q.tiles_w * q.tiles_h * q.tiles_n * q.tiles_c, q.ksteps, q.stages, ms,
              pr.op->flops, pr.op->bytes);
     out += line;
   }

@@ -533,6 +533,16 @@ pack_mask_bits_kernel(const bf16* __restrict__ act, uint32_t* __restrict__ bits,
 
 }  // namespace
 
+__global__ void vec_add_kernel(const float* a, const float* b, float* out, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = a[i] + b[i];
+}
+int launch_vec_add(const float* a, const float* b, float* out, int n, cudaStream_t st) {
+  vec_add_kernel<<<(n + 255) / 256, 256, 0, st>>>(a, b, out, n);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+
 int launch_pack_mask_bits(const bf16* act, uint32_t* bits, long long pixels, int c, cudaStream_t st) {
   const long long total = pixels * (c / 32);
   if (!total) return ADVB200_OK;

@@ -63,6 +63,9 @@ int launch_pack_conv1_bf16(const float* w, const float* scale, bf16* fwd, bf16* 
 // fc: transpose [classes, feat] -> [feat, classes]
 int launch_transpose_f32(const float* in, float* out, int rows, int cols, cudaStream_t st);
 
+// out = a + b (fused folded-BN shifts)
+int launch_vec_add(const float* a, const float* b, float* out, int n, cudaStream_t st);
+
 // test hook: bf16 [pixels, c] (c % 64 == 0) -> ReLU bit mask in the layout the conv epilogue reads
 int launch_pack_mask_bits(const bf16* act, uint32_t* bits, long long pixels, int c, cudaStream_t st);
 

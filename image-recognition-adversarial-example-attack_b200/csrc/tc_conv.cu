@@ -33,8 +33,11 @@ constexpr int kBarrierBytes = 512;
 constexpr int kIdentBytes = 64 * 128;          // 64x64 bf16 identity operand of the residual k-steps
 constexpr int kBiasBytes = 2 * 256 * 4;        // per-accumulator copy of the tile's folded-BN shift
 
-template <int BN> struct Cfg {
-  static constexpr int kBTileBytes = BN * kBlockK * 2;
+// kPair: two CTAs of a cluster (one SM pair) run tcgen05.mma.cta_group::2 on a 256-pixel x BN tile; each CTA
+// stages its own 128 pixels of A and HALF of the BN weight rows, halving the weight traffic per CTA.
+template <int BN, bool kPair> struct Cfg {
+  static constexpr int kBRows = kPair ? BN / 2 : BN;
+  static constexpr int kBTileBytes = kBRows * kBlockK * 2;
   static constexpr int kStageBytes = kATileBytes + kBTileBytes;
   static constexpr int kTmemCols = (2 * BN < 32) ? 32 : 2 * BN;  // two accumulators
 };
@@ -108,6 +111,60 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
                    smem_u32(bar))
                : "memory");
+}
+// ---- CTA-pair (cta_group::2) variants -----------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `p` (a shared::cta pointer) in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_u32(const void* p, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA loads whose completion is signalled on the LEADER CTA's mbarrier (bar_cluster_addr)
+__device__ __forceinline__ void tma_load_4d_pair(const CUtensorMap* map, uint32_t bar_cluster_addr, void* dst, int c0,
+                                                 int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(const CUtensorMap* map, uint32_t bar_cluster_addr, void* dst, int c0,
+                                                 int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                               uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on the same-offset mbarrier of BOTH CTAs of the pair once all prior MMAs have completed
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"((uint16_t)3)
+      : "memory");
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile(
@@ -209,9 +266,14 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint4 v) {
 
 // ---------------------------------------------------------------- the kernel
 struct TileCoord { int w0, h0, n0, c0; };
-__device__ __forceinline__ TileCoord tile_coord(const ConvGemmParams& p, int tile, int bn_cols) {
+// pair mode: `tile` indexes (pair of consecutive pixel tiles, column block); CTA `rank` takes pixel tile
+// 2*pair + rank (an odd tile count leaves the last rank-1 tile out of bounds in n: loads zero-fill,
+// stores clip)
+template <bool kPair>
+__device__ __forceinline__ TileCoord tile_coord(const ConvGemmParams& p, int tile, int bn_cols, int rank) {
   TileCoord t;
   const int tc = tile % p.tiles_c; tile /= p.tiles_c;
+  if (kPair) tile = 2 * tile + rank;
   const int tw = tile % p.tiles_w; tile /= p.tiles_w;
   const int th = tile % p.tiles_h; tile /= p.tiles_h;
   t.w0 = tw * p.bw; t.h0 = th * p.bh; t.n0 = tile * p.bn; t.c0 = tc * bn_cols;
@@ -220,19 +282,22 @@ __device__ __forceinline__ TileCoord tile_coord(const ConvGemmParams& p, int til
 
 // smem carve-up (host and device agree through these helpers)
 template <int BN> struct Smem {
-  using C = Cfg<BN>;
-  __host__ __device__ static constexpr int out_slots() { return BN == 16 ? 0 : 4; }
-  __host__ __device__ static constexpr int fixed_bytes() {
-    return out_slots() * kSubTileBytes + kIdentBytes + kBiasBytes + kBarrierBytes;
+  // output staging slots: 4 when the epilogue is the busy part (few k-steps), 2 when the operand ring
+  // needs the room (many k-steps)
+  __host__ __device__ static constexpr int fixed_bytes(int out_slots) {
+    return (BN == 16 ? 0 : out_slots) * kSubTileBytes + kIdentBytes + kBiasBytes + kBarrierBytes;
   }
 };
 
-template <int BN>
+template <int BN, bool kPair>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constant__ ConvGemmParams p) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, kPair>;
+  const int rank = kPair ? (int)cluster_ctarank() : 0;       // CTA within the pair; rank 0 issues the MMAs
+  const int tile0 = kPair ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int tile_step = kPair ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   extern __shared__ __align__(1024) uint8_t smem[];
-  constexpr int n_out_slots = Smem<BN>::out_slots();
+  const int n_out_slots = BN == 16 ? 0 : p.out_slots;
   // [resident weights (halo mode)] [operand ring] [output staging] [identity] [shift] [barriers]
   uint8_t* ring = smem + p.ring_off;
   const int stage_bytes = p.stage_bytes;
@@ -254,38 +319,50 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
     if (smem_u32(smem) & 1023u) __trap();                   // swizzled tiles need 1024-byte alignment
     for (int i = 0; i < 4; ++i) prefetch_tmap(&maps.a[i]);
     prefetch_tmap(&maps.b);
+    if (p.has_b2) prefetch_tmap(&maps.b2);
     prefetch_tmap(&maps.out);
     if (p.has_add) prefetch_tmap(&maps.add);
     for (int s = 0; s < kMaxStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], 8); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], kPair ? 16 : 8); }
     mbar_init(bres_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                     smem_u32(tmem_slot)),
-                 "n"(C::kTmemCols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if constexpr (kPair) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                       smem_u32(tmem_slot)),
+                   "n"(C::kTmemCols)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                       smem_u32(tmem_slot)),
+                   "n"(C::kTmemCols)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
-  const int total_tiles = p.tiles_w * p.tiles_h * p.tiles_n * p.tiles_c;
+  const int pixel_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
+  const int total_tiles = (kPair ? (pixel_tiles + 1) / 2 : pixel_tiles) * p.tiles_c;
   if (warp >= kEpiWarp0 && p.bias && BN != 16) {
     // folded-BN shift of the first tile's column block (accumulator 0's copy)
     const int i = threadIdx.x - kEpiWarp0 * 32;
-    if (i < BN && (int)blockIdx.x < total_tiles) bias_smem[i] = __ldg(p.bias + tile_coord(p, blockIdx.x, BN).c0 + i);
+    if (i < BN && tile0 < total_tiles) bias_smem[i] = __ldg(p.bias + tile_coord<kPair>(p, tile0, BN, rank).c0 + i);
   }
   if (warp >= kEpiWarp0 && p.has_add) {
     // identity operand for the residual k-steps: I[n][k] = (n == k), rows of 128 B, 16-byte chunks
     // XOR-swizzled by (row & 7) exactly as TMA would have written them
     const int i = threadIdx.x - kEpiWarp0 * 32;          // 256 threads x 32 B = 8 KB
-    const int r = i >> 2, cpair = (i & 3) * 2;           // row, first of two logical chunks
+    // pair mode: this CTA holds rows 32*rank .. 32*rank+31 of I (its half of the N = 64 operand)
+    const int r = i >> 2, cpair = (i & 3) * 2;           // local row, first of two logical chunks
+    const int nrow = r + (kPair ? 32 * rank : 0);        // row of I
 #pragma unroll
     for (int cc = 0; cc < 2; ++cc) {
       const int c = cpair + cc;                          // logical chunk: columns 8c..8c+7
       uint4 v = make_uint4(0, 0, 0, 0);
-      if ((r >> 3) == c) {
-        const uint32_t one = 0x3F80u << (16 * (r & 1));  // bf16 1.0 in the right half-word
-        const int wsel = (r & 7) >> 1;
+      if ((nrow >> 3) == c) {
+        const uint32_t one = 0x3F80u << (16 * (nrow & 1));  // bf16 1.0 in the right half-word
+        const int wsel = (nrow & 7) >> 1;
         v.x = wsel == 0 ? one : 0; v.y = wsel == 1 ? one : 0; v.z = wsel == 2 ? one : 0; v.w = wsel == 3 ? one : 0;
       }
       *reinterpret_cast<uint4*>(ident_smem + r * 128 + ((c ^ (r & 7)) << 4)) = v;
@@ -293,11 +370,11 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
     fence_async_smem();
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kPair) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int ksteps = p.ntaps * p.kblocks;
+  const int ksteps = p.ksteps;                              // sum of tap_kb[] (generic mode)
   const int nstages = p.stages;
 
   if (warp == 0) {
@@ -309,8 +386,8 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
         // all taps' weights once, then one halo box of input pixels per tile
         mbar_expect_tx(bres_bar, (uint32_t)(p.ntaps * BN * 128));
         for (int tap = 0; tap < p.ntaps; ++tap) tma_load_2d(&maps.b, bres_bar, smem + tap * BN * 128, 0, p.tap_brow[tap]);
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-          const TileCoord tc = tile_coord(p, tile, BN);
+        for (int tile = tile0; tile < total_tiles; tile += tile_step) {
+          const TileCoord tc = tile_coord<kPair>(p, tile, BN, rank);
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_expect_tx(&full_bar[stage], (uint32_t)(p.halo_rows * 128));
           tma_load_4d(&maps.a[0], &full_bar[stage], ring + stage * stage_bytes, 0, tc.w0 + p.halo_w0,
@@ -318,19 +395,28 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           if (++stage == nstages) { stage = 0; phase ^= 1; }
         }
       } else
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const TileCoord tc = tile_coord(p, tile, BN);
+      for (int tile = tile0; tile < total_tiles; tile += tile_step) {
+        const TileCoord tc = tile_coord<kPair>(p, tile, BN, rank);
         for (int tap = 0; tap < p.ntaps; ++tap) {
           const CUtensorMap* ma = &maps.a[p.tap_map[tap]];
+          const CUtensorMap* mb = p.tap_bmap[tap] ? &maps.b2 : &maps.b;
           const int cw = tc.w0 + p.tap_dw[tap], ch = tc.h0 + p.tap_dh[tap];
           const int brow = p.tap_brow[tap] + tc.c0;
-          for (int kb = 0; kb < p.kblocks; ++kb) {
+          for (int kb = 0; kb < p.tap_kb[tap]; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1);
             uint8_t* sa = ring + stage * stage_bytes;
             uint8_t* sb = sa + kATileBytes;
-            mbar_expect_tx(&full_bar[stage], C::kStageBytes);
-            tma_load_4d(ma, &full_bar[stage], sa, kb * kBlockK, cw, ch, tc.n0);
-            tma_load_2d(&maps.b, &full_bar[stage], sb, kb * kBlockK, brow);
+            if constexpr (kPair) {
+              // both CTAs' boxes complete on the leader's barrier; this CTA stages its half of the weight rows
+              const uint32_t fb = mapa_u32(&full_bar[stage], 0);
+              if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * C::kStageBytes);
+              tma_load_4d_pair(ma, fb, sa, kb * kBlockK, cw, ch, tc.n0);
+              tma_load_2d_pair(mb, fb, sb, kb * kBlockK, brow + rank * C::kBRows);
+            } else {
+              mbar_expect_tx(&full_bar[stage], C::kStageBytes);
+              tma_load_4d(ma, &full_bar[stage], sa, kb * kBlockK, cw, ch, tc.n0);
+              tma_load_2d(mb, &full_bar[stage], sb, kb * kBlockK, brow);
+            }
             if (++stage == nstages) { stage = 0; phase ^= 1; }
           }
         }
@@ -338,9 +424,15 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           // residual / skip-gradient tile, one 64-channel block per stage (added by an identity MMA)
           for (int j = 0; j < BN / 64; ++j) {
             mbar_wait(&empty_bar[stage], phase ^ 1);
-            mbar_expect_tx(&full_bar[stage], kATileBytes);
-            tma_load_4d(&maps.add, &full_bar[stage], ring + stage * stage_bytes, tc.c0 + 64 * j, tc.w0, tc.h0,
-                        tc.n0);
+            if constexpr (kPair) {
+              const uint32_t fb = mapa_u32(&full_bar[stage], 0);
+              if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * kATileBytes);
+              tma_load_4d_pair(&maps.add, fb, ring + stage * stage_bytes, tc.c0 + 64 * j, tc.w0, tc.h0, tc.n0);
+            } else {
+              mbar_expect_tx(&full_bar[stage], kATileBytes);
+              tma_load_4d(&maps.add, &full_bar[stage], ring + stage * stage_bytes, tc.c0 + 64 * j, tc.w0, tc.h0,
+                          tc.n0);
+            }
             if (++stage == nstages) { stage = 0; phase ^= 1; }
           }
         }
@@ -348,20 +440,21 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
     }
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
-    if (lane == 0) {
-      // instruction descriptor: D=f32, A=B=bf16, both K-major, N=BN, M=128
+    if (lane == 0 && rank == 0) {
+      // instruction descriptor: D=f32, A=B=bf16, both K-major, N=BN, M=128 (256 across the CTA pair)
+      constexpr uint32_t kMmaM = kPair ? 2 * kBlockM : kBlockM;
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
-                                 ((uint32_t)(kBlockM >> 4) << 24);
+                                 ((uint32_t)(kMmaM >> 4) << 24);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = tile0; tile < total_tiles; tile += tile_step) {
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
         if (p.halo) {
-          if (tile == (int)blockIdx.x) { mbar_wait(bres_bar, 0); }
+          if (tile == tile0) { mbar_wait(bres_bar, 0); }
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(ring + stage * stage_bytes);
@@ -384,16 +477,18 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k) {
             // advance 32 bytes (16 bf16) inside the 128B swizzle row: +2 in 16-byte units
-            umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
-                      (ks | k) != 0 ? 1u : 0u);
+            if constexpr (kPair)
+              umma_bf16_pair(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (ks | k) != 0 ? 1u : 0u);
+            else
+              umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (ks | k) != 0 ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);
+          if constexpr (kPair) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
           if (++stage == nstages) { stage = 0; phase ^= 1; }
         }
         if (p.has_add) {
           // D[:, 64j..64j+63] += R_j * I  (bf16 x 1.0 accumulated in fp32: exact)
           constexpr uint32_t idesc64 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(64 >> 3) << 17) |
-                                       ((uint32_t)(kBlockM >> 4) << 24);
+                                       ((uint32_t)(kMmaM >> 4) << 24);
           const uint64_t idesc_b = make_smem_desc(smem_u32(ident_smem));
           for (int j = 0; j < BN / 64; ++j) {
             mbar_wait(&full_bar[stage], phase);
@@ -401,12 +496,15 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
             const uint64_t adesc = make_smem_desc(smem_u32(ring + stage * stage_bytes));
 #pragma unroll
             for (int k = 0; k < kBlockK / 16; ++k)
-              umma_bf16(d_tmem + (uint32_t)(64 * j), adesc + (uint64_t)(2 * k), idesc_b + (uint64_t)(2 * k), idesc64, 1u);
-            umma_commit(&empty_bar[stage]);
+              if constexpr (kPair)
+                umma_bf16_pair(d_tmem + (uint32_t)(64 * j), adesc + (uint64_t)(2 * k), idesc_b + (uint64_t)(2 * k), idesc64, 1u);
+              else
+                umma_bf16(d_tmem + (uint32_t)(64 * j), adesc + (uint64_t)(2 * k), idesc_b + (uint64_t)(2 * k), idesc64, 1u);
+            if constexpr (kPair) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
             if (++stage == nstages) { stage = 0; phase ^= 1; }
           }
         }
-        umma_commit(&tfull_bar[acc]);
+        if constexpr (kPair) umma_commit_pair(&tfull_bar[acc]); else umma_commit(&tfull_bar[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -425,8 +523,8 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
     if constexpr (BN == 16) {
       // conv1 input gradient: columns q = (ph*2+pw)*3 + c of the space-to-depth pixel (h, w);
       // fp32 scatter into the NCHW image gradient, divided by the normalisation std
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const TileCoord tc = tile_coord(p, tile, BN);
+      for (int tile = tile0; tile < total_tiles; tile += tile_step) {
+        const TileCoord tc = tile_coord<kPair>(p, tile, BN, rank);
         const int wi = row % p.bw, hi = (row / p.bw) % p.bh, ni = row / (p.bw * p.bh);
         const int w = tc.w0 + wi, h = tc.h0 + hi, n = tc.n0 + ni;
         const bool valid = (w < p.out_w) && (h < p.out_h) && (n < p.out_n);
@@ -456,7 +554,9 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+        if (lane == 0) {
+              if constexpr (kPair) mbar_arrive_cluster(mapa_u32(&tempty_bar[acc], 0)); else mbar_arrive(&tempty_bar[acc]);
+            }
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     } else {
@@ -476,8 +576,8 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
       const bool has_mask_out = relu && p.mask_out != nullptr;
       int oslot = 0;            // output staging slot of the sub-tile being produced
 
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const TileCoord tc = tile_coord(p, tile, BN);
+      for (int tile = tile0; tile < total_tiles; tile += tile_step) {
+        const TileCoord tc = tile_coord<kPair>(p, tile, BN, rank);
         // output pixel of this thread's row (bit-mask addressing) and whether it exists
         const int wi = row % p.bw, hi = (row / p.bw) % p.bh, ni = row / tile_px;
         const int tw = tc.w0 + wi, th = tc.h0 + hi, tn = tc.n0 + ni;
@@ -486,8 +586,8 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
                                 (tw * p.pix_sub + p.pix_pw);
         const long long mword0 = ((long long)(tc.c0 >> 6) * p.mask_pixels + pixel) * 2 + half;
         // folded-BN shift of the NEXT tile goes to the other accumulator's copy
-        if (has_bias && etid < BN && tile + (int)gridDim.x < total_tiles)
-          bias_smem[(acc ^ 1) * 256 + etid] = __ldg(p.bias + tile_coord(p, tile + gridDim.x, BN).c0 + etid);
+        if (has_bias && etid < BN && tile + tile_step < total_tiles)
+          bias_smem[(acc ^ 1) * 256 + etid] = __ldg(p.bias + tile_coord<kPair>(p, tile + tile_step, BN, rank).c0 + etid);
         uint32_t mword[kSub];
 #pragma unroll
         for (int j = 0; j < kSub; ++j)
@@ -505,7 +605,9 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
             // every TMEM read of this accumulator has completed: hand it back to the MMA warp
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+            if (lane == 0) {
+              if constexpr (kPair) mbar_arrive_cluster(mapa_u32(&tempty_bar[acc], 0)); else mbar_arrive(&tempty_bar[acc]);
+            }
           }
           if (has_bias) {
             const uint32_t bb = bias0 + (uint32_t)((acc * 256 + j * 64 + half * 32) * 4);
@@ -544,11 +646,11 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           if (leader) {
             tma_store_4d(&maps.out, out_smem + oslot * kSubTileBytes, tc.c0 + 64 * j, tc.w0, tc.h0, tc.n0);
             bulk_commit();
-            // four staging slots: before the next barrier all but the two newest stores must have
+            // n staging slots: before the next barrier all but the newest (n - 2) stores must have
             // finished reading their slot
-            bulk_wait_read<2>();
+            if (n_out_slots == 4) bulk_wait_read<2>(); else bulk_wait_read<0>();
           }
-          oslot = (oslot + 1) & 3;
+          oslot = (oslot + 1) & (n_out_slots - 1);
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
@@ -557,55 +659,71 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kPair) cluster_sync_all(); else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
-                 "n"(C::kTmemCols)
-                 : "memory");
+    if constexpr (kPair)
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::kTmemCols) : "memory");
+    else
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::kTmemCols) : "memory");
   }
 }
 
-template <int BN>
+template <int BN, bool kPair>
 int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, kPair>;
   static bool configured = false;
   if (!configured) {
-    ADV_CHECK_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    ADV_CHECK_CUDA(cudaFuncSetAttribute(conv_gemm_kernel<BN, kPair>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         kSmemBudget));
     configured = true;
   }
-  const long long total = (long long)p.tiles_w * p.tiles_h * p.tiles_n * p.tiles_c;
+  const long long pixel_tiles = (long long)p.tiles_w * p.tiles_h * p.tiles_n;
+  const long long total = (kPair ? (pixel_tiles + 1) / 2 : pixel_tiles) * p.tiles_c;
   if (total <= 0) return ADVB200_OK;
   p.ring_off = 0;
   p.stage_bytes = C::kStageBytes;
+  if (p.ksteps == 0) {                       // plain conv: every tap spans all kblocks of one weight matrix
+    for (int t = 0; t < p.ntaps; ++t) { p.tap_kb[t] = p.kblocks; p.tap_bmap[t] = 0; }
+    p.ksteps = p.ntaps * p.kblocks;
+  }
   if (p.halo) {
-    ADV_CHECK_ARG(p.kblocks == 1 && p.tiles_c == 1 && !p.has_add, "conv_gemm: halo mode needs K = 64, one column block");
+    ADV_CHECK_ARG(p.kblocks == 1 && p.tiles_c == 1 && !p.has_add && !kPair,
+                  "conv_gemm: halo mode needs K = 64, one column block, one CTA per tile");
     p.ring_off = (p.ntaps * BN * 128 + 1023) & ~1023;
     p.stage_bytes = (p.halo_rows * 128 + 1023) & ~1023;
   }
-  int stages = (kSmemBudget - Smem<BN>::fixed_bytes() - p.ring_off) / p.stage_bytes;
+  static const char* force_slots = getenv("ADVB200_OUT_SLOTS");   // tuning knob
+  p.out_slots = force_slots ? atoi(force_slots) : (p.ksteps >= 8 ? 2 : 4);
+  int stages = (kSmemBudget - Smem<BN>::fixed_bytes(p.out_slots) - p.ring_off) / p.stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return fail(ADVB200_ERR_ARG, "conv_gemm: tile configuration does not fit shared memory");
   p.stages = stages;
   p.aux_depth = 0;
-  const int smem_bytes = p.ring_off + stages * p.stage_bytes + Smem<BN>::fixed_bytes();
-  const int grid = (int)(total < kNumSMs ? total : kNumSMs);
-  conv_gemm_kernel<BN><<<grid, kThreads, smem_bytes, stream>>>(maps, p);
+  const int smem_bytes = p.ring_off + stages * p.stage_bytes + Smem<BN>::fixed_bytes(p.out_slots);
+  const int units = kPair ? kNumSMs / 2 : kNumSMs;            // CTAs or CTA pairs
+  const int grid = (int)(total < units ? total : units) * (kPair ? 2 : 1);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = smem_bytes; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kPair ? 2 : 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  ADV_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<BN, kPair>, maps, p));
   ADV_LAUNCHED();
   return ADVB200_OK;
 }
 
 }  // namespace
 
-int launch_conv_gemm(int bn_cols, const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream) {
+int launch_conv_gemm(int bn_cols, int pair, const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream) {
   ADV_CHECK_ARG(p.bw * p.bh * p.bn == kBlockM, "conv_gemm: tile must hold 128 pixels");
-  ADV_CHECK_ARG(p.ntaps >= 1 && p.ntaps <= kMaxTaps && p.kblocks >= 1, "conv_gemm: bad K loop");
+  ADV_CHECK_ARG(p.ntaps >= 1 && p.ntaps <= kMaxTaps && (p.kblocks >= 1 || p.ksteps >= 1), "conv_gemm: bad K loop");
   switch (bn_cols) {
-    case 16: return launch_impl<16>(maps, p, stream);
-    case 64: return launch_impl<64>(maps, p, stream);
-    case 128: return launch_impl<128>(maps, p, stream);
-    case 256: return launch_impl<256>(maps, p, stream);
+    case 16: return launch_impl<16, false>(maps, p, stream);
+    case 64: return pair ? launch_impl<64, true>(maps, p, stream) : launch_impl<64, false>(maps, p, stream);
+    case 128: return pair ? launch_impl<128, true>(maps, p, stream) : launch_impl<128, false>(maps, p, stream);
+    case 256: return pair ? launch_impl<256, true>(maps, p, stream) : launch_impl<256, false>(maps, p, stream);
     default: return fail(ADVB200_ERR_ARG, "conv_gemm: BN must be 16, 64, 128 or 256");
   }
 }

@@ -25,6 +25,13 @@ struct ConvGemmParams {
   int tap_dw[kMaxTaps];           // pixel shift of the tap along w / h
   int tap_dh[kMaxTaps];
   int tap_brow[kMaxTaps];         // first row of the tap's weights in the packed B matrix
+  // fused launches (two 1x1 convs accumulating into one output, e.g. conv3 + downsample): taps may read
+  // different weight matrices (tap_bmap: 0 -> maps.b, 1 -> maps.b2) with different depths (tap_kb).
+  // ksteps = sum of tap_kb; leave 0 for a plain conv (filled from ntaps * kblocks).
+  int tap_kb[kMaxTaps];
+  int tap_bmap[kMaxTaps];
+  int ksteps;
+  int has_b2;
   // halo mode (kblocks == 1, tiles_c == 1): ONE TMA box of (bw+halo) x (bh+halo) input pixels per tile
   // serves every tap — tap t reads the rows starting at tap_row[t], 8-row groups sbo_rows rows apart
   // (tcgen05 applies the 128B swizzle to absolute smem addresses, so row-shifted descriptors are legal;
@@ -49,6 +56,7 @@ struct ConvGemmParams {
   int pix_sub, pix_ph, pix_pw;    // output pixel (h, w) of tile coords (th, tw): (th*sub+ph, tw*sub+pw)
   int full_h, full_w;             // full-resolution output height / width
   int stages;                     // smem ring depth chosen by the host for this launch
+  int out_slots;                  // output staging slots (2 or 4), host-chosen
   int stage_bytes, ring_off;      // ring slot size and offset of the ring (after resident weights)
   int aux_depth;                  // residual/mask prefetch ring depth (sub-tiles), host-chosen
   int epi;                        // 0: bf16 NHWC store; 1: conv1 input-gradient scatter (fp32 NCHW)
@@ -59,12 +67,14 @@ struct ConvGemmParams {
 struct ConvGemmMaps {
   CUtensorMap a[4];   // activation (or one per stride-2 sub-lattice)
   CUtensorMap b;      // packed weights
+  CUtensorMap b2;     // second weight matrix of a fused launch
   CUtensorMap out;    // output tile store (64-channel boxes, same pixel box as a[])
   CUtensorMap add;    // optional, output-shaped
 };
 
-// Launch on `stream`.  bn_cols in {16, 64, 128, 256}.  Fills p.stages.
-int launch_conv_gemm(int bn_cols, const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream);
+// Launch on `stream`.  bn_cols in {16, 64, 128, 256}.  pair != 0: CTA pairs (cta_group::2) on 256-pixel tiles;
+// the weight tensor map must then have a box of bn_cols/2 rows.  Fills p.stages.
+int launch_conv_gemm(int bn_cols, int pair, const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream);
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda needed).
 // dims/strides innermost-first; strides in BYTES for dims 1..rank-1; bf16 elements; 128B swizzle.

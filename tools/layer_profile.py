@@ -51,7 +51,7 @@ for _ in range(reps):
     for line in buf.value.decode().strip().split("\n")[1:]:
         name, bn, tiles, ksteps, stages, ms, fl, by = line.split(",")
         if name not in acc:
-            acc[name] = [int(bn), int(tiles), int(ksteps), int(stages), [], float(fl), float(by)]
+            acc[name] = [bn, int(tiles), int(ksteps), int(stages), [], float(fl), float(by)]
             order.append(name)
         acc[name][4].append(float(ms))
 
