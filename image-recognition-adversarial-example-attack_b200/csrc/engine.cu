@@ -93,7 +93,7 @@ inline TileChoice pick_tile(int gemm_n, long long m_tiles, int ksteps) {
   TileChoice best{64, 0};
   double best_score = -1;
   for (int pair = 0; pair < 2; ++pair) {
-    if (force_pair ? atoi(force_pair) != pair : (pair != (ksteps >= 8 ? 1 : 0))) continue;   // measured: pairs pay off
+    if (force_pair ? atoi(force_pair) != pair : (pair != (ksteps >= 16 ? 1 : 0))) continue;   // measured: pairs pay off
                                                                                               // only on MMA-heavy tiles
     for (int i = 0; i < 3; ++i) {
       const int bn = cands[i];
@@ -412,8 +412,13 @@ bool g_prof_on = false;
 struct ProfRec { cudaEvent_t e0, e1; const Op* op; };
 std::vector<ProfRec> g_prof_events;
 
+// consecutive conv launches alternate their tile traversal direction, so a launch starts on the part of
+// its input that the previous launch wrote last (still in the 126 MB L2)
+int g_snake = 0;
 int run_ops(std::vector<Op>& ops, cudaStream_t st) {
+  static const bool snake = !getenv("ADVB200_NO_SNAKE");
   for (Op& op : ops) {
+    if (op.kind == Op::TC) { op.tc.p.reverse = snake ? (g_snake & 1) : 0; ++g_snake; }
     int rc = ADVB200_OK;
     switch (op.kind) {
       case Op::TC: {

@@ -272,6 +272,7 @@ struct TileCoord { int w0, h0, n0, c0; };
 template <bool kPair>
 __device__ __forceinline__ TileCoord tile_coord(const ConvGemmParams& p, int tile, int bn_cols, int rank) {
   TileCoord t;
+  if (p.reverse) tile = p.total_tiles - 1 - tile;   // snake order: start where the previous launch ended (L2 reuse)
   const int tc = tile % p.tiles_c; tile /= p.tiles_c;
   if (kPair) tile = 2 * tile + rank;
   const int tw = tile % p.tiles_w; tile /= p.tiles_w;
@@ -681,6 +682,7 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
   const long long pixel_tiles = (long long)p.tiles_w * p.tiles_h * p.tiles_n;
   const long long total = (kPair ? (pixel_tiles + 1) / 2 : pixel_tiles) * p.tiles_c;
   if (total <= 0) return ADVB200_OK;
+  p.total_tiles = (int)total;
   p.ring_off = 0;
   p.stage_bytes = C::kStageBytes;
   if (p.ksteps == 0) {                       // plain conv: every tap spans all kblocks of one weight matrix

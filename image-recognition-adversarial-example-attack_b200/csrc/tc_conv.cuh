@@ -57,6 +57,7 @@ struct ConvGemmParams {
   int full_h, full_w;             // full-resolution output height / width
   int stages;                     // smem ring depth chosen by the host for this launch
   int out_slots;                  // output staging slots (2 or 4), host-chosen
+  int reverse, total_tiles;       // traverse tiles last-to-first (alternating launches reuse the L2 tail)
   int stage_bytes, ring_off;      // ring slot size and offset of the ring (after resident weights)
   int aux_depth;                  // residual/mask prefetch ring depth (sub-tiles), host-chosen
   int epi;                        // 0: bf16 NHWC store; 1: conv1 input-gradient scatter (fp32 NCHW)
