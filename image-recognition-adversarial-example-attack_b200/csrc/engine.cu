@@ -756,29 +756,26 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
       Op op; op.kind = Op::TC;
       TcOp& t = op.tc; ConvGemmParams& p = t.p;
       memset(&p, 0, sizeof p);
-      // halo mode: one (11 x 19)-pixel box of the conv1-output gradient feeds all 4 x 4 taps
-      p.bw = 8; p.bh = 16; p.bn = 1;
-      p.tiles_w = 14; p.tiles_h = 7; p.tiles_n = n; p.tiles_c = 1;
-      t.bn = 16;
-      p.ntaps = 16; p.kblocks = 1;
-      p.halo = 1; p.halo_w0 = -1; p.halo_h0 = -1; p.halo_rows = 11 * 19; p.sbo_rows = 11;
-      for (int tt = 0; tt < 4; ++tt)
-        for (int u = 0; u < 4; ++u) {
-          const int i = tt * 4 + u;
-          p.tap_row[i] = (2 - tt + 1) * 11 + (2 - u + 1); p.tap_brow[i] = i * 16;
-        }
-      p.out_w = 112; p.out_h = 112; p.out_n = n; p.cout = 16;
-      p.epi = 1; p.img_h = kImg; p.img_w = kImg;
+      // halo mode, vertical taps in the K loop and horizontal taps in the N dimension: a 16 x 11 box of the
+      // conv1-output gradient (columns w0-1 .. w0+14, rows h0-1 .. h0+9) yields 13 x 8 gradient pixels
+      p.bw = 16; p.bh = 8; p.bn = 1; p.step_w = 13; p.org_w = -1;
+      p.tiles_w = 9; p.tiles_h = 14; p.tiles_n = n; p.tiles_c = 1;
+      t.bn = 64;
+      p.ntaps = 4; p.kblocks = 1;
+      p.halo = 1; p.halo_w0 = 0; p.halo_h0 = -1; p.halo_rows = 16 * 11; p.sbo_rows = 8;   // 16-wide raster: 8-row groups are contiguous
+      for (int tt = 0; tt < 4; ++tt) { p.tap_row[tt] = (2 - tt + 1) * 16; p.tap_brow[tt] = tt * 64; }
+      p.out_w = 112; p.out_h = 112; p.out_n = n; p.cout = 64;
+      p.epi = 2; p.img_h = kImg; p.img_w = kImg;
       p.out = nullptr;   // patched per call (grad_x_out)
       const uint64_t dims[4] = {64, 112, 112, (uint64_t)n};
       const uint64_t strides[3] = {128, 128ull * 112, 128ull * 112 * 112};
-      const uint32_t box[4] = {64, 11, 19, 1};
+      const uint32_t box[4] = {64, 16, 11, 1};
       memset(&t.maps, 0, sizeof t.maps);
       rc = make_tmap_bf16(&t.maps.a[0], m->g_c1, 4, dims, strides, box);
       t.maps.out = t.maps.a[0];   // unused by the scatter epilogue; keeps the prefetch well-defined
       const uint64_t bd[2] = {64, 256};
       const uint64_t bs[1] = {128};
-      const uint32_t bb[2] = {64, 16};
+      const uint32_t bb[2] = {64, 64};
       if (!rc) rc = make_tmap_bf16(&t.maps.b, m->conv[0].b_dgrad, 2, bd, bs, bb);
       setl("bwd", nullptr, "conv1");
       label_op(op, "", 2.0 * n * 112 * 112 * 64 * 147, n * (2.0 * 112 * 112 * 64 + 4.0 * 3 * 224 * 224));

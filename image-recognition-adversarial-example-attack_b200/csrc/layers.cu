@@ -501,7 +501,11 @@ __global__ void pack_conv1_kernel(const float* __restrict__ w, const float* __re
   }
   const bf16 b = __float2bfloat16_rn(v);
   fwd[(tt * 64 + co) * 64 + u * 16 + q] = b;
-  dgrad[((tt * 4 + u) * 16 + q) * 64 + co] = b;
+  // input gradient: vertical taps (tt) stay in the K loop, horizontal taps (u) go to the N dimension:
+  // row tt*64 + qi*4 + u, qi = slot of q in the store-friendly order {0,3,1,4,2,5,6,9 | 7,10,8,11}
+  // (pairs (pw=0, pw=1) of the same (c, ph) adjacent, so the epilogue writes 8-byte pixel pairs)
+  const int slot_of_q[16] = {0, 2, 4, 1, 3, 5, 6, 8, 10, 7, 9, 11, 12, 13, 14, 15};
+  dgrad[(tt * 64 + slot_of_q[q] * 4 + u) * 64 + co] = b;
 }
 
 __global__ void transpose_kernel(const float* __restrict__ in, float* __restrict__ out, int rows, int cols) {

@@ -58,7 +58,7 @@ int launch_pack_f32(const float* w, const float* scale, float* fwd, float* dgrad
 int launch_pack_bf16(const float* w, const float* scale, bf16* fwd, bf16* dgrad, int cout, int cin, int k,
                      cudaStream_t st);
 // conv1 (7x7/2, 3->64) in its space-to-depth form:
-//   fwd  [t*64 + co][u*16+q]      dgrad [(t*4+u)*16 + q][co]    (t,u in 0..3; see launch_prep_hcol)
+//   fwd  [t*64 + co][u*16+q]      dgrad [t*64 + slot(q)*4 + u][co]    (t,u in 0..3; see launch_prep_hcol)
 int launch_pack_conv1_bf16(const float* w, const float* scale, bf16* fwd, bf16* dgrad, cudaStream_t st);
 // fc: transpose [classes, feat] -> [feat, classes]
 int launch_transpose_f32(const float* in, float* out, int rows, int cols, cudaStream_t st);

@@ -273,11 +273,15 @@ template <bool kPair>
 __device__ __forceinline__ TileCoord tile_coord(const ConvGemmParams& p, int tile, int bn_cols, int rank) {
   TileCoord t;
   if (p.reverse) tile = p.total_tiles - 1 - tile;   // snake order: start where the previous launch ended (L2 reuse)
-  const int tc = tile % p.tiles_c; tile /= p.tiles_c;
+  // divisions by launch constants through host-made reciprocals: q = (n * ceil(2^40 / d)) >> 40 (n < 2^20)
+  int q = (int)(((unsigned long long)(unsigned)tile * p.magic_c) >> 40);
+  const int tc = tile - q * p.tiles_c; tile = q;
   if (kPair) tile = 2 * tile + rank;
-  const int tw = tile % p.tiles_w; tile /= p.tiles_w;
-  const int th = tile % p.tiles_h; tile /= p.tiles_h;
-  t.w0 = tw * p.bw; t.h0 = th * p.bh; t.n0 = tile * p.bn; t.c0 = tc * bn_cols;
+  q = (int)(((unsigned long long)(unsigned)tile * p.magic_w) >> 40);
+  const int tw = tile - q * p.tiles_w; tile = q;
+  q = (int)(((unsigned long long)(unsigned)tile * p.magic_h) >> 40);
+  const int th = tile - q * p.tiles_h; tile = q;
+  t.w0 = tw * p.step_w + p.org_w; t.h0 = th * p.bh; t.n0 = tile * p.bn; t.c0 = tc * bn_cols;
   return t;
 }
 
@@ -521,7 +525,56 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
     int acc = 0;
     uint32_t acc_phase = 0;
 
-    if constexpr (BN == 16) {
+    if (BN == 64 && p.epi == 2) {
+      // Stem input gradient.  Accumulator row = pixel (y, x) of a 16-wide box of the 112 x 112 gradient grid
+      // (x = 0 and x = 14, 15 are halo columns); column = slot(q)*4 + u holds the partial sum over the four
+      // vertical taps for horizontal tap u.  dX[y, x, q] = sum_u Z[(y, x+2-u), u, q]: the four addends sit
+      // in neighbouring lanes of the same 16-lane row group -> warp shuffles.  Each lane then owns output
+      // pixel (y, x) for x in 1..13 and writes fp32 NCHW pixel pairs, divided by the normalisation std.
+      float inv_std[3];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) inv_std[c] = __fdiv_rn(1.0f, __ldg(p.std_dev + c));
+      for (int tile = tile0; tile < total_tiles; tile += tile_step) {
+        const TileCoord tc = tile_coord<kPair>(p, tile, BN, rank);
+        const int xi = row & 15, yi = row >> 4;
+        const int w = tc.w0 + xi, h = tc.h0 + yi, n = tc.n0;
+        const bool valid = xi >= 1 && xi <= 13 && w < p.out_w && h < p.out_h && n < p.out_n;
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+        float f[32];
+        tmem_ld32f(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + half * 32), f);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+        float o[8];
+#pragma unroll
+        for (int s = 0; s < 8; ++s) {
+          const float a0 = __shfl_down_sync(0xffffffffu, f[4 * s + 0], 2);
+          const float a1 = __shfl_down_sync(0xffffffffu, f[4 * s + 1], 1);
+          const float a3 = __shfl_up_sync(0xffffffffu, f[4 * s + 3], 1);
+          o[s] = (a0 + a1) + (f[4 * s + 2] + a3);
+        }
+        if (valid) {
+          float* g = reinterpret_cast<float*>(p.out);
+          // slots held by this half: half 0 -> (c,ph) = (0,0),(1,0),(2,0),(0,1); half 1 -> (1,1),(2,1)
+          const int npairs = half == 0 ? 4 : 2;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            if (k < npairs) {
+              const int pi = half * 4 + k;                 // pair index 0..5 = ph*3 + c
+              const int c = pi % 3, ph = pi / 3;
+              const long long off = (((long long)n * 3 + c) * p.img_h + (2 * h + ph)) * p.img_w + 2 * w;
+              float2 v2;               // bf16 path: x (1/std) instead of the true division (fp32 mode keeps it)
+              v2.x = o[2 * k] * inv_std[c];
+              v2.y = o[2 * k + 1] * inv_std[c];
+              *reinterpret_cast<float2*>(g + off) = v2;
+            }
+          }
+        }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    } else if constexpr (BN == 16) {
       // conv1 input gradient: columns q = (ph*2+pw)*3 + c of the space-to-depth pixel (h, w);
       // fp32 scatter into the NCHW image gradient, divided by the normalisation std
       for (int tile = tile0; tile < total_tiles; tile += tile_step) {
@@ -570,7 +623,8 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
       const uint32_t bias0 = smem_u32(bias_smem);
       const uint32_t row_off = (uint32_t)row * 128u;
       const uint32_t sw = (uint32_t)(row & 7);
-      const int tile_px = p.bw * p.bh;
+      // bw, bh are powers of two: pixel (wi, hi, ni) of this thread's row inside the tile box
+      const int wi = row & (p.bw - 1), hi = (row >> p.bw_shift) & (p.bh - 1), ni = row >> (p.bw_shift + p.bh_shift);
       const bool has_bias = p.bias != nullptr;
       const bool relu = p.relu != 0;
       const bool has_mask_in = p.mask_in != nullptr;
@@ -580,7 +634,6 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
       for (int tile = tile0; tile < total_tiles; tile += tile_step) {
         const TileCoord tc = tile_coord<kPair>(p, tile, BN, rank);
         // output pixel of this thread's row (bit-mask addressing) and whether it exists
-        const int wi = row % p.bw, hi = (row / p.bw) % p.bh, ni = row / tile_px;
         const int tw = tc.w0 + wi, th = tc.h0 + hi, tn = tc.n0 + ni;
         const bool valid = (tw < p.out_w) && (th < p.out_h) && (tn < p.out_n);
         const long long pixel = ((long long)tn * p.full_h + (th * p.pix_sub + p.pix_ph)) * p.full_w +
@@ -683,6 +736,13 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
   const long long total = (kPair ? (pixel_tiles + 1) / 2 : pixel_tiles) * p.tiles_c;
   if (total <= 0) return ADVB200_OK;
   p.total_tiles = (int)total;
+  if (p.step_w == 0) p.step_w = p.bw;
+  auto magic = [](int d) { return (unsigned long long)(((1ull << 40) + (unsigned long long)d - 1) / (unsigned long long)d); };
+  auto ilog2 = [](int v) { int s = 0; while ((1 << s) < v) ++s; return s; };
+  ADV_CHECK_ARG(total < (1ll << 20) && pixel_tiles * 2 < (1ll << 20), "conv_gemm: too many tiles for the fast division");
+  ADV_CHECK_ARG((p.bw & (p.bw - 1)) == 0 && (p.bh & (p.bh - 1)) == 0, "conv_gemm: tile box must be a power of two");
+  p.magic_c = magic(p.tiles_c); p.magic_w = magic(p.tiles_w); p.magic_h = magic(p.tiles_h);
+  p.bw_shift = ilog2(p.bw); p.bh_shift = ilog2(p.bh);
   p.ring_off = 0;
   p.stage_bytes = C::kStageBytes;
   if (p.ksteps == 0) {                       // plain conv: every tap spans all kblocks of one weight matrix

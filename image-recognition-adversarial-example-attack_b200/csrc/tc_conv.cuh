@@ -20,6 +20,8 @@ struct ConvGemmParams {
   // tiling: a tile is bw x bh x bn pixels (product 128) by BN output channels
   int tiles_w, tiles_h, tiles_n, tiles_c;
   int bw, bh, bn;
+  int step_w, org_w;              // tile origin along w = tile_w * step_w + org_w (0 -> step_w = bw): tiles whose
+                                  // boxes overlap (stem input gradient keeps its horizontal halo in the tile)
   int ntaps, kblocks;             // K loop: ntaps * kblocks blocks of 64 input channels
   int tap_map[kMaxTaps];          // which A tensor map the tap reads
   int tap_dw[kMaxTaps];           // pixel shift of the tap along w / h
@@ -57,10 +59,13 @@ struct ConvGemmParams {
   int full_h, full_w;             // full-resolution output height / width
   int stages;                     // smem ring depth chosen by the host for this launch
   int out_slots;                  // output staging slots (2 or 4), host-chosen
+  unsigned long long magic_c, magic_w, magic_h;   // ceil(2^40 / tiles_c|w|h): fast division in tile_coord
+  int bw_shift, bh_shift;         // log2(bw), log2(bh)
   int reverse, total_tiles;       // traverse tiles last-to-first (alternating launches reuse the L2 tail)
   int stage_bytes, ring_off;      // ring slot size and offset of the ring (after resident weights)
   int aux_depth;                  // residual/mask prefetch ring depth (sub-tiles), host-chosen
-  int epi;                        // 0: bf16 NHWC store; 1: conv1 input-gradient scatter (fp32 NCHW)
+  int epi;                        // 0: bf16 NHWC store; 1/2: stem input gradient (fp32 NCHW); 2 = horizontal
+                                  // taps in the N dimension, reduced by warp shuffles (BN = 64)
   const float* std_dev;           // epi 1: device pointer to std[3]; gradient is divided by std[c]
   int img_h, img_w;               // epi 1: full-resolution image size
 };
