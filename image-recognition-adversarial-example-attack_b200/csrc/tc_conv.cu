@@ -88,6 +88,13 @@ __device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* ba
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
 }
+// one lane of a converged warp (the rest of the warp keeps running the same uniform control flow)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 }
@@ -445,71 +452,96 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
     }
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
-    if (lane == 0 && rank == 0) {
+    // The whole warp runs the (warp-uniform) control flow, one elected lane issues the MMAs and commits:
+    // loop state then lives in uniform registers and the single-thread issue path — which paces every
+    // launch with N <= 128 — stays short (measured: ~110 clk per MMA when all of this ran divergently
+    // under `if (lane == 0)`).
+    if (rank == 0) {
       // instruction descriptor: D=f32, A=B=bf16, both K-major, N=BN, M=128 (256 across the CTA pair)
       constexpr uint32_t kMmaM = kPair ? 2 * kBlockM : kBlockM;
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
                                  ((uint32_t)(kMmaM >> 4) << 24);
+      constexpr uint32_t idesc64 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(64 >> 3) << 17) |
+                                   ((uint32_t)(kMmaM >> 4) << 24);
+      const uint32_t desc_hi = (uint32_t)(make_smem_desc(0) >> 32);
+      const uint32_t a_hi_halo = (uint32_t)(make_smem_desc(0, (uint32_t)(p.sbo_rows * 128)) >> 32);
+      const uint32_t ring_lo = ((smem_u32(ring) & 0x3FFFFu) >> 4) | (1u << 16);
+      const uint32_t bres_lo = ((smem_u32(smem) & 0x3FFFFu) >> 4) | (1u << 16);
+      const uint32_t ident_lo = ((smem_u32(ident_smem) & 0x3FFFFu) >> 4) | (1u << 16);
+      const uint32_t stage_units = (uint32_t)(stage_bytes >> 4);
+      const bool halo = p.halo != 0, has_add = p.has_add != 0;
+      const int ntaps = p.ntaps;
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      if (halo) mbar_wait(bres_bar, 0);
       for (int tile = tile0; tile < total_tiles; tile += tile_step) {
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
-        if (p.halo) {
-          if (tile == tile0) { mbar_wait(bres_bar, 0); }
+        if (halo) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(ring + stage * stage_bytes);
-          for (int tap = 0; tap < p.ntaps; ++tap) {
-            const uint64_t adesc = make_smem_desc(sa + (uint32_t)(p.tap_row[tap] * 128), (uint32_t)(p.sbo_rows * 128));
-            const uint64_t bdesc = make_smem_desc(smem_u32(smem + tap * BN * 128));
+          if (elect_one()) {
+            const uint32_t a_lo0 = ring_lo + (uint32_t)stage * stage_units;
+            for (int tap = 0; tap < ntaps; ++tap) {
+              const uint32_t a_lo = a_lo0 + (uint32_t)(p.tap_row[tap] * 8);
+              const uint32_t b_lo = bres_lo + (uint32_t)(tap * BN * 8);
 #pragma unroll
-            for (int k = 0; k < kBlockK / 16; ++k)
-              umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (tap | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < kBlockK / 16; ++k)
+                umma_bf16(d_tmem, ((uint64_t)a_hi_halo << 32) | (a_lo + 2u * k), ((uint64_t)desc_hi << 32) | (b_lo + 2u * k),
+                          idesc, (tap | k) != 0 ? 1u : 0u);
+            }
+            umma_commit(&empty_bar[stage]);
           }
-          umma_commit(&empty_bar[stage]);
+          __syncwarp();
           if (++stage == nstages) { stage = 0; phase ^= 1; }
-        } else
-        for (int ks = 0; ks < ksteps; ++ks) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint32_t sa = smem_u32(ring + stage * stage_bytes);
-          const uint64_t adesc = make_smem_desc(sa);
-          const uint64_t bdesc = make_smem_desc(sa + kATileBytes);
-#pragma unroll
-          for (int k = 0; k < kBlockK / 16; ++k) {
-            // advance 32 bytes (16 bf16) inside the 128B swizzle row: +2 in 16-byte units
-            if constexpr (kPair)
-              umma_bf16_pair(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (ks | k) != 0 ? 1u : 0u);
-            else
-              umma_bf16(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (ks | k) != 0 ? 1u : 0u);
-          }
-          if constexpr (kPair) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
-          if (++stage == nstages) { stage = 0; phase ^= 1; }
-        }
-        if (p.has_add) {
-          // D[:, 64j..64j+63] += R_j * I  (bf16 x 1.0 accumulated in fp32: exact)
-          constexpr uint32_t idesc64 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(64 >> 3) << 17) |
-                                       ((uint32_t)(kMmaM >> 4) << 24);
-          const uint64_t idesc_b = make_smem_desc(smem_u32(ident_smem));
-          for (int j = 0; j < BN / 64; ++j) {
+        } else {
+          for (int ks = 0; ks < ksteps; ++ks) {
             mbar_wait(&full_bar[stage], phase);
             tc_fence_after();
-            const uint64_t adesc = make_smem_desc(smem_u32(ring + stage * stage_bytes));
+            if (elect_one()) {
+              const uint32_t a_lo = ring_lo + (uint32_t)stage * stage_units;
+              const uint32_t b_lo = a_lo + (uint32_t)(kATileBytes >> 4);
 #pragma unroll
-            for (int k = 0; k < kBlockK / 16; ++k)
-              if constexpr (kPair)
-                umma_bf16_pair(d_tmem + (uint32_t)(64 * j), adesc + (uint64_t)(2 * k), idesc_b + (uint64_t)(2 * k), idesc64, 1u);
-              else
-                umma_bf16(d_tmem + (uint32_t)(64 * j), adesc + (uint64_t)(2 * k), idesc_b + (uint64_t)(2 * k), idesc64, 1u);
-            if constexpr (kPair) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
+              for (int k = 0; k < kBlockK / 16; ++k) {
+                // advance 32 bytes (16 bf16) inside the 128B swizzle row: +2 in 16-byte units
+                const uint64_t adesc = ((uint64_t)desc_hi << 32) | (a_lo + 2u * k);
+                const uint64_t bdesc = ((uint64_t)desc_hi << 32) | (b_lo + 2u * k);
+                if constexpr (kPair) umma_bf16_pair(d_tmem, adesc, bdesc, idesc, (ks | k) != 0 ? 1u : 0u);
+                else umma_bf16(d_tmem, adesc, bdesc, idesc, (ks | k) != 0 ? 1u : 0u);
+              }
+              if constexpr (kPair) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
+            }
+            __syncwarp();
             if (++stage == nstages) { stage = 0; phase ^= 1; }
           }
+          if (has_add) {
+            // D[:, 64j..64j+63] += R_j * I  (bf16 x 1.0 accumulated in fp32: exact)
+            for (int j = 0; j < BN / 64; ++j) {
+              mbar_wait(&full_bar[stage], phase);
+              tc_fence_after();
+              if (elect_one()) {
+                const uint32_t a_lo = ring_lo + (uint32_t)stage * stage_units;
+#pragma unroll
+                for (int k = 0; k < kBlockK / 16; ++k) {
+                  const uint64_t adesc = ((uint64_t)desc_hi << 32) | (a_lo + 2u * k);
+                  const uint64_t bdesc = ((uint64_t)desc_hi << 32) | (ident_lo + 2u * k);
+                  if constexpr (kPair) umma_bf16_pair(d_tmem + (uint32_t)(64 * j), adesc, bdesc, idesc64, 1u);
+                  else umma_bf16(d_tmem + (uint32_t)(64 * j), adesc, bdesc, idesc64, 1u);
+                }
+                if constexpr (kPair) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
+              }
+              __syncwarp();
+              if (++stage == nstages) { stage = 0; phase ^= 1; }
+            }
+          }
         }
-        if constexpr (kPair) umma_commit_pair(&tfull_bar[acc]); else umma_commit(&tfull_bar[acc]);
+        if (elect_one()) {
+          if constexpr (kPair) umma_commit_pair(&tfull_bar[acc]); else umma_commit(&tfull_bar[acc]);
+        }
+        __syncwarp();
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
