@@ -198,6 +198,11 @@ __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// programmatic dependent launch: the next conv launch may start its prologue (and constant weight loads) while
+// this grid drains; everything that touches activations waits for the previous grid to complete
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // K-major, 128B-swizzled operand tile: rows of 128 bytes, 8-row atoms of 1024 bytes.
 // sbo_bytes: distance between consecutive 8-row groups (1024 for a dense tile; the halo-mode A
 // operand uses the halo box width * 128, and start addresses shifted by whole rows).
@@ -394,10 +399,12 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      pdl_launch_dependents();
       if (p.halo) {
         // all taps' weights once, then one halo box of input pixels per tile
         mbar_expect_tx(bres_bar, (uint32_t)(p.ntaps * BN * 128));
         for (int tap = 0; tap < p.ntaps; ++tap) tma_load_2d(&maps.b, bres_bar, smem + tap * BN * 128, 0, p.tap_brow[tap]);
+        pdl_wait();
         for (int tile = tile0; tile < total_tiles; tile += tile_step) {
           const TileCoord tc = tile_coord<kPair>(p, tile, BN, rank);
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -406,7 +413,24 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
                       tc.h0 + p.halo_h0, tc.n0);
           if (++stage == nstages) { stage = 0; phase ^= 1; }
         }
-      } else
+      } else {
+      const bool bres = p.bres != 0;
+      if (bres && tile0 < total_tiles) {
+        // resident weights: every tile of this CTA has the same column block (the host makes the tile
+        // stride a multiple of tiles_c), so all of its k-blocks are staged once, ahead of the ring
+        const int c0 = tile_coord<kPair>(p, tile0, BN, rank).c0;
+        uint8_t* sb = smem;
+        if constexpr (kPair) { if (rank == 0) mbar_expect_tx(bres_bar, (uint32_t)(2 * ksteps * C::kBTileBytes)); }
+        else mbar_expect_tx(bres_bar, (uint32_t)(ksteps * C::kBTileBytes));
+        for (int tap = 0; tap < p.ntaps; ++tap) {
+          const CUtensorMap* mb = p.tap_bmap[tap] ? &maps.b2 : &maps.b;
+          for (int kb = 0; kb < p.tap_kb[tap]; ++kb, sb += C::kBTileBytes) {
+            if constexpr (kPair) tma_load_2d_pair(mb, mapa_u32(bres_bar, 0), sb, kb * kBlockK, p.tap_brow[tap] + c0 + rank * C::kBRows);
+            else tma_load_2d(mb, bres_bar, sb, kb * kBlockK, p.tap_brow[tap] + c0);
+          }
+        }
+      }
+      pdl_wait();
       for (int tile = tile0; tile < total_tiles; tile += tile_step) {
         const TileCoord tc = tile_coord<kPair>(p, tile, BN, rank);
         for (int tap = 0; tap < p.ntaps; ++tap) {
@@ -418,7 +442,16 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
             mbar_wait(&empty_bar[stage], phase ^ 1);
             uint8_t* sa = ring + stage * stage_bytes;
             uint8_t* sb = sa + kATileBytes;
-            if constexpr (kPair) {
+            if (bres) {
+              if constexpr (kPair) {
+                const uint32_t fb = mapa_u32(&full_bar[stage], 0);
+                if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * kATileBytes);
+                tma_load_4d_pair(ma, fb, sa, kb * kBlockK, cw, ch, tc.n0);
+              } else {
+                mbar_expect_tx(&full_bar[stage], kATileBytes);
+                tma_load_4d(ma, &full_bar[stage], sa, kb * kBlockK, cw, ch, tc.n0);
+              }
+            } else if constexpr (kPair) {
               // both CTAs' boxes complete on the leader's barrier; this CTA stages its half of the weight rows
               const uint32_t fb = mapa_u32(&full_bar[stage], 0);
               if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * C::kStageBytes);
@@ -449,6 +482,7 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           }
         }
       }
+      }
     }
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
@@ -469,13 +503,13 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
       const uint32_t bres_lo = ((smem_u32(smem) & 0x3FFFFu) >> 4) | (1u << 16);
       const uint32_t ident_lo = ((smem_u32(ident_smem) & 0x3FFFFu) >> 4) | (1u << 16);
       const uint32_t stage_units = (uint32_t)(stage_bytes >> 4);
-      const bool halo = p.halo != 0, has_add = p.has_add != 0;
+      const bool halo = p.halo != 0, has_add = p.has_add != 0, bres = p.bres != 0;
       const int ntaps = p.ntaps;
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      if (halo) mbar_wait(bres_bar, 0);
+      if ((halo || bres) && tile0 < total_tiles) mbar_wait(bres_bar, 0);
       for (int tile = tile0; tile < total_tiles; tile += tile_step) {
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
@@ -503,7 +537,8 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
             tc_fence_after();
             if (elect_one()) {
               const uint32_t a_lo = ring_lo + (uint32_t)stage * stage_units;
-              const uint32_t b_lo = a_lo + (uint32_t)(kATileBytes >> 4);
+              const uint32_t b_lo = bres ? bres_lo + (uint32_t)ks * (uint32_t)(C::kBTileBytes >> 4)
+                                         : a_lo + (uint32_t)(kATileBytes >> 4);
 #pragma unroll
               for (int k = 0; k < kBlockK / 16; ++k) {
                 // advance 32 bytes (16 bf16) inside the 128B swizzle row: +2 in 16-byte units
@@ -556,6 +591,7 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
     const int etid = threadIdx.x - kEpiWarp0 * 32;
     int acc = 0;
     uint32_t acc_phase = 0;
+    pdl_wait();          // masks, residuals and the output buffer belong to earlier launches
 
     if (BN == 64 && p.epi == 2) {
       // Stem input gradient.  Accumulator row = pixel (y, x) of a 16-wide box of the 112 x 112 gradient grid
@@ -789,20 +825,39 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
   }
   static const char* force_slots = getenv("ADVB200_OUT_SLOTS");   // tuning knob
   p.out_slots = force_slots ? atoi(force_slots) : (p.ksteps >= 8 ? 2 : 4);
+  int units = kPair ? kNumSMs / 2 : kNumSMs;            // CTAs or CTA pairs
+  // resident-weight mode (pointwise convs): when all k-blocks of one column block fit beside a >= 3-deep ring of
+  // A tiles, each CTA keeps one column block for all of its tiles (tile stride = multiple of tiles_c) and only
+  // activations stream through the ring: halves the L2 -> SM traffic of the wide 1x1 layers
+  static const char* no_bres = getenv("ADVB200_NO_BRES");
+  p.bres = 0;
+  if (!p.halo && !no_bres && BN != 16 && !p.bres_off) {
+    const int res_bytes = p.ksteps * C::kBTileBytes;
+    const int slots = p.out_slots == 4 && res_bytes > 64 * 1024 ? 2 : p.out_slots;
+    const int ring_room = kSmemBudget - Smem<BN>::fixed_bytes(slots) - res_bytes;
+    const int bres_units = units - units % p.tiles_c;
+    if (ring_room >= 3 * kATileBytes && bres_units * 16 >= units * 15 && total >= bres_units) {
+      p.bres = 1; p.ring_off = res_bytes; p.stage_bytes = kATileBytes; p.out_slots = slots; units = bres_units;
+    }
+  }
   int stages = (kSmemBudget - Smem<BN>::fixed_bytes(p.out_slots) - p.ring_off) / p.stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return fail(ADVB200_ERR_ARG, "conv_gemm: tile configuration does not fit shared memory");
   p.stages = stages;
   p.aux_depth = 0;
   const int smem_bytes = p.ring_off + stages * p.stage_bytes + Smem<BN>::fixed_bytes(p.out_slots);
-  const int units = kPair ? kNumSMs / 2 : kNumSMs;            // CTAs or CTA pairs
   const int grid = (int)(total < units ? total : units) * (kPair ? 2 : 1);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = smem_bytes; cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = kPair ? 2 : 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr; cfg.numAttrs = 1;
+  // programmatic dependent launch: this grid may start while the previous kernel of the stream drains; the
+  // kernel orders itself behind it with griddepcontrol.wait
+  static const bool no_pdl = getenv("ADVB200_NO_PDL") != nullptr;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = no_pdl ? 1 : 2;
   ADV_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_gemm_kernel<BN, kPair>, maps, p));
   ADV_LAUNCHED();
   return ADVB200_OK;

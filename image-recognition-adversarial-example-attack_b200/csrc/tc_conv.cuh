@@ -57,6 +57,8 @@ struct ConvGemmParams {
   long long mask_pixels;          // pixels of the output tensor (plane stride of the mask)
   int pix_sub, pix_ph, pix_pw;    // output pixel (h, w) of tile coords (th, tw): (th*sub+ph, tw*sub+pw)
   int full_h, full_w;             // full-resolution output height / width
+  int bres_off;                   // caller opt-out of the resident-weight mode
+  int bres;                       // chosen by launch_conv_gemm: weights resident, ring carries activations only
   int stages;                     // smem ring depth chosen by the host for this launch
   int out_slots;                  // output staging slots (2 or 4), host-chosen
   unsigned long long magic_c, magic_w, magic_h;   // ceil(2^40 / tiles_c|w|h): fast division in tile_coord
