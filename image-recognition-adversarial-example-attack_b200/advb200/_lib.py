@@ -52,6 +52,7 @@ SIGNATURES = {
     "advb200_profile_enable": (c_int, [c_int]),
     "advb200_profile_read": (c_int, [POINTER(ctypes.c_double), POINTER(c_int64)]),
     "advb200_profile_dump": (c_int64, [c_char_p, c_int64]),
+    "advb200_tune_report": (c_int, [c_void_p, POINTER(c_int), POINTER(ctypes.c_double)]),
 }
 
 

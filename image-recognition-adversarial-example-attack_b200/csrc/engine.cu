@@ -8,8 +8,11 @@
 // Reference: model(normalize_batch(x)) attack.py:30,57,111; autograd.grad(loss, x) attack.py:32,59;
 // loss.backward() attack.py:130 (without its unused weight gradients); _layer3_features
 // defense_experiments.py:221-257.
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
+#include <functional>
+#include <map>
 #include <vector>
 
 #include "layers.cuh"
@@ -86,9 +89,17 @@ inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 // rows split across the pair) are used.  Score = wave efficiency x sqrt(MACs per operand element staged
 // per CTA): the L2<->SM fabric, not the tensor pipe, bounds the wide layers.
 struct TileChoice { int bn, pair; };
+// Per-launch override used by the plan-time autotuner (-1 = heuristic / launcher default).
+struct TileForce { int bn = -1, pair = -1, bres = -1, slots = -1; };
+TileForce g_force;
+inline void apply_force(ConvGemmParams& p) {
+  p.bres_off = g_force.bres == 0 ? 1 : 0;
+  p.slots_req = g_force.slots > 0 ? g_force.slots : 0;
+}
 inline TileChoice pick_tile(int gemm_n, long long m_tiles, int ksteps) {
   static const char* force_pair = getenv("ADVB200_PAIR");      // tuning knobs: "0" / "1"
   static const char* force_bn = getenv("ADVB200_BN");
+  if (g_force.bn > 0 && gemm_n % g_force.bn == 0) return TileChoice{g_force.bn, g_force.pair > 0 ? 1 : 0};
   const int cands[3] = {256, 128, 64};
   TileChoice best{64, 0};
   double best_score = -1;
@@ -148,7 +159,7 @@ int build_pw_ops(std::vector<Op>& ops, const PwSrc* src, int nsrc, Act out, int 
     kin += src[i].in.c;
     in_bytes += 2.0 * out.n * lw * lh * src[i].in.c;
   }
-  { const TileChoice tcz = pick_tile(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, ksteps); t.bn = tcz.bn; t.pair = tcz.pair; }
+  { const TileChoice tcz = pick_tile(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, ksteps); t.bn = tcz.bn; t.pair = tcz.pair; apply_force(p); }
   p.tiles_c = gemm_n / t.bn;
   p.out_w = lw; p.out_h = lh; p.out_n = out.n; p.cout = gemm_n;
   p.bias = bias; p.relu = relu; p.mask_in = mask; p.mask_out = mask_out;
@@ -235,7 +246,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     ADV_CHECK_ARG(m < (1ll << 31), "tc conv: too many pixels");
     p.bw = 128; p.bh = 1; p.bn = 1;
     p.tiles_w = (int)((m + 127) / 128); p.tiles_h = 1; p.tiles_n = 1;
-    { const TileChoice tcz = pick_tile(gemm_n, p.tiles_w, p.kblocks); t.bn = tcz.bn; t.pair = tcz.pair; }
+    { const TileChoice tcz = pick_tile(gemm_n, p.tiles_w, p.kblocks); t.bn = tcz.bn; t.pair = tcz.pair; apply_force(p); }
     p.tiles_c = gemm_n / t.bn;
     p.ntaps = 1;
     p.out_w = (int)m; p.out_h = 1; p.out_n = 1;
@@ -289,7 +300,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     ADV_CHECK_ARG(stride == 1 || (in.h % 2 == 0 && in.w % 2 == 0), "tc conv fwd: stride 2 needs even sizes");
     tile_shape(out.w, out.h, p.bw, p.bh, p.bn);
     p.tiles_w = cdiv(out.w, p.bw); p.tiles_h = cdiv(out.h, p.bh); p.tiles_n = cdiv(out.n, p.bn);
-    { const TileChoice tcz = pick_tile(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, kk * p.kblocks); t.bn = tcz.bn; t.pair = tcz.pair; }
+    { const TileChoice tcz = pick_tile(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, kk * p.kblocks); t.bn = tcz.bn; t.pair = tcz.pair; apply_force(p); }
     p.tiles_c = gemm_n / t.bn;
     p.out_w = out.w; p.out_h = out.h; p.out_n = out.n;
     int rc;
@@ -332,7 +343,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     ADV_CHECK_ARG(out.h == in.h && out.w == in.w && in.n == out.n, "tc conv dgrad: shape mismatch");
     tile_shape(out.w, out.h, p.bw, p.bh, p.bn);
     p.tiles_w = cdiv(out.w, p.bw); p.tiles_h = cdiv(out.h, p.bh); p.tiles_n = cdiv(out.n, p.bn);
-    { const TileChoice tcz = pick_tile(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, kk * p.kblocks); t.bn = tcz.bn; t.pair = tcz.pair; }
+    { const TileChoice tcz = pick_tile(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, kk * p.kblocks); t.bn = tcz.bn; t.pair = tcz.pair; apply_force(p); }
     p.tiles_c = gemm_n / t.bn;
     p.out_w = out.w; p.out_h = out.h; p.out_n = out.n;
     int rc = make_a(&t.maps.a[0], in, 1, 0, 0, p.bw, p.bh, p.bn);
@@ -375,7 +386,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
       const int sw = out.w / 2, sh = out.h / 2;
       tile_shape(sw, sh, q.bw, q.bh, q.bn);
       q.tiles_w = cdiv(sw, q.bw); q.tiles_h = cdiv(sh, q.bh); q.tiles_n = cdiv(out.n, q.bn);
-      { const TileChoice tcz = pick_tile(gemm_n, (long long)q.tiles_w * q.tiles_h * q.tiles_n, q.ntaps * q.kblocks); t2.bn = tcz.bn; t2.pair = tcz.pair; }
+      { const TileChoice tcz = pick_tile(gemm_n, (long long)q.tiles_w * q.tiles_h * q.tiles_n, q.ntaps * q.kblocks); t2.bn = tcz.bn; t2.pair = tcz.pair; apply_force(q); }
       q.tiles_c = gemm_n / t2.bn;
       q.out_w = sw; q.out_h = sh; q.out_n = out.n;
       q.pix_sub = 2; q.pix_ph = ph; q.pix_pw = pw;
@@ -476,6 +487,10 @@ struct advb200_model {
   void* g_top = nullptr;        // gradient w.r.t. layer4 output (masked) is written here
   float* g_img_nhwc = nullptr;  // fp32 mode only
   std::vector<Op> ops_conv1, ops_l123, ops_l4, ops_bwd, ops_conv1_bwd;
+  // plan-time autotuner results: "<first op label>#<batch>" -> tile choice per launch of that builder call
+  std::map<std::string, std::vector<TileForce>> tune_cache;
+  double tune_ms = 0;           // wall time spent tuning (reported by advb200_tune_report)
+  int tuned_ops = 0;
 };
 
 namespace advb200 {
@@ -488,6 +503,92 @@ struct Bump {
     void* p = base ? base + off : nullptr;
     off += (bytes + 1023) & ~size_t(1023);
     return p;
+  }
+};
+
+// Plan-time autotuner ("measure, don't guess"): every generic conv launch is built under each candidate
+// tile choice (BN, CTA pair, resident weights, output staging slots), timed cold (L2 flushed) on the real
+// workspace buffers, and the fastest build is kept.  All candidates compute bit-identical results (same K
+// order), so tuning never changes numerics.  ADVB200_NO_AUTOTUNE=1 keeps the heuristic of pick_tile.
+struct Tuner {
+  advb200_model* m; int n; cudaStream_t st; bool on;
+  void* flush = nullptr; size_t flush_bytes = 256u << 20;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  Tuner(advb200_model* m_, int n_, cudaStream_t st_, bool on_) : m(m_), n(n_), st(st_), on(on_) {
+    static const bool off = getenv("ADVB200_NO_AUTOTUNE") != nullptr;
+    if (off) on = false;
+  }
+  ~Tuner() {
+    if (flush) cudaFree(flush);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    g_force = TileForce{};
+  }
+  float time_op(Op& op) {
+    if (!flush) {
+      if (cudaMalloc(&flush, flush_bytes) != cudaSuccess) { flush = nullptr; cudaGetLastError(); return -1.f; }
+      cudaEventCreate(&e0); cudaEventCreate(&e1);
+    }
+    float best = 1e30f;
+    for (int rep = 0; rep < 2; ++rep) {
+      cudaMemsetAsync(flush, rep, flush_bytes, st);
+      cudaEventRecord(e0, st);
+      if (launch_conv_gemm(op.tc.bn, op.tc.pair, op.tc.maps, op.tc.p, st) != ADVB200_OK) return -1.f;
+      cudaEventRecord(e1, st);
+      if (cudaEventSynchronize(e1) != cudaSuccess) return -1.f;
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, e0, e1);
+      if (ms < best) best = ms;
+    }
+    return best;
+  }
+  int emit(std::vector<Op>& ops, const std::function<int(std::vector<Op>&)>& builder) {
+    g_force = TileForce{};
+    std::vector<Op> base;
+    int rc = builder(base);
+    if (rc) return rc;
+    bool tunable = on && !base.empty();
+    for (const Op& o : base) if (o.kind != Op::TC || o.tc.p.halo || o.tc.bn == 16) tunable = false;
+    if (!tunable) { ops.insert(ops.end(), base.begin(), base.end()); return ADVB200_OK; }
+    const std::string key = std::string(base[0].name) + "#" + std::to_string(n);
+    auto it = m->tune_cache.find(key);
+    if (it == m->tune_cache.end()) {
+      const auto t0 = std::chrono::steady_clock::now();
+      const int cout = base[0].tc.p.cout;
+      std::vector<TileForce> cands;
+      for (int bn : {256, 128, 64}) {
+        if (cout % bn || (bn == 64 && cout >= 256)) continue;
+        for (int pair = 0; pair < 2; ++pair)
+          for (int bres : {-1, 0})
+            for (int slots : {2, 4}) { TileForce f; f.bn = bn; f.pair = pair; f.bres = bres; f.slots = slots; cands.push_back(f); }
+      }
+      std::vector<float> best_ms(base.size(), 1e30f);
+      std::vector<TileForce> best(base.size());
+      for (const TileForce& f : cands) {
+        g_force = f;
+        std::vector<Op> v;
+        if (builder(v) != ADVB200_OK || v.size() != base.size()) { set_error(""); continue; }
+        for (size_t j = 0; j < v.size(); ++j) {
+          const float ms = time_op(v[j]);
+          if (ms > 0.f && ms < best_ms[j]) { best_ms[j] = ms; best[j] = f; }
+        }
+      }
+      g_force = TileForce{};
+      cudaGetLastError();
+      for (size_t j = 0; j < base.size(); ++j) if (best_ms[j] > 1e29f) best[j] = TileForce{};
+      it = m->tune_cache.emplace(key, best).first;
+      m->tuned_ops += (int)base.size();
+      m->tune_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
+    for (size_t j = 0; j < base.size(); ++j) {
+      g_force = it->second[j];
+      std::vector<Op> v;
+      rc = builder(v);
+      g_force = TileForce{};
+      if (rc || v.size() != base.size()) { ops.push_back(base[j]); continue; }
+      ops.push_back(v[j]);
+    }
+    return ADVB200_OK;
   }
 };
 
@@ -507,7 +608,7 @@ void make_blocks(advb200_model* m) {
 }
 
 // Lays out the workspace and (when ws != null) builds the launch lists.  Returns bytes needed.
-int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
+int64_t plan(advb200_model* m, int n, void* ws, int* rc_out, cudaStream_t tune_st = nullptr, bool tune = false) {
   const bool tc = m->precision == ADVB200_PREC_BF16;
   const size_t esz = tc ? 2 : 4;
   m->esz = esz;
@@ -526,6 +627,8 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
     else snprintf(lbl, sizeof lbl, "%s %s", dir, conv);
     g_label = lbl;
   };
+  Tuner tuner(m, n, tune_st, tune && build && tc);
+  auto emit = [&](std::vector<Op>& ops, const std::function<int(std::vector<Op>&)>& builder) { return tuner.emit(ops, builder); };
   if (build) {
     m->ops_conv1.clear(); m->ops_l123.clear(); m->ops_l4.clear(); m->ops_bwd.clear(); m->ops_conv1_bwd.clear();
   }
@@ -616,25 +719,25 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
       const ConvW& c1 = m->conv[s.conv_base], &c2 = m->conv[s.conv_base + 1], &c3 = m->conv[s.conv_base + 2];
       if (tc) {
         setl("fwd", &s, "c1");
-        rc = build_tc_ops(ops, c1.b_fwd, 1, 1, false, t.x, t.a, c1.shift, nullptr, nullptr, 1, t.ma);
+        rc = emit(ops, [&](std::vector<Op>& v_) { return build_tc_ops(v_, c1.b_fwd, 1, 1, false, t.x, t.a, c1.shift, nullptr, nullptr, 1, t.ma); });
         setl("fwd", &s, "c2");
-        if (!rc) rc = build_tc_ops(ops, c2.b_fwd, 3, s.stride, false, t.a, t.b, c2.shift, nullptr, nullptr, 1, t.mb);
+        if (!rc) rc = emit(ops, [&](std::vector<Op>& v_) { return build_tc_ops(v_, c2.b_fwd, 3, s.stride, false, t.a, t.b, c2.shift, nullptr, nullptr, 1, t.mb); });
         const bf16* res = reinterpret_cast<const bf16*>(t.x.p);
         if (!rc && s.down && fuse) {
           // conv3 + downsample in one launch: both GEMMs accumulate into the same TMEM tile
           const ConvW& cd = m->conv[s.conv_base + 3];
           setl("fwd", &s, "c3+ds");
           const PwSrc src[2] = {{t.b, 1, 0, 0, c3.b_fwd}, {t.x, s.stride, 0, 0, cd.b_fwd}};
-          rc = build_pw_ops(ops, src, 2, t.out, 1, 0, 0, c3.shift_fused, nullptr, 1, t.mout);
+          rc = emit(ops, [&](std::vector<Op>& v_) { return build_pw_ops(v_, src, 2, t.out, 1, 0, 0, c3.shift_fused, nullptr, 1, t.mout); });
         } else {
           if (!rc && s.down) {
             const ConvW& cd = m->conv[s.conv_base + 3];
             setl("fwd", &s, "ds");
-            rc = build_tc_ops(ops, cd.b_fwd, 1, s.stride, false, t.x, t.idn, cd.shift, nullptr, nullptr, 0);
+            rc = emit(ops, [&](std::vector<Op>& v_) { return build_tc_ops(v_, cd.b_fwd, 1, s.stride, false, t.x, t.idn, cd.shift, nullptr, nullptr, 0); });
             res = reinterpret_cast<const bf16*>(t.idn.p);
           }
           setl("fwd", &s, "c3");
-          if (!rc) rc = build_tc_ops(ops, c3.b_fwd, 1, 1, false, t.b, t.out, c3.shift, res, nullptr, 1, t.mout);
+          if (!rc) rc = emit(ops, [&](std::vector<Op>& v_) { return build_tc_ops(v_, c3.b_fwd, 1, 1, false, t.b, t.out, c3.shift, res, nullptr, 1, t.mout); });
         }
       } else {
         rc = build_simt_op(ops, c1.f_fwd, 1, 1, false, t.x, t.a, c1.shift, nullptr, nullptr, 1);
@@ -669,9 +772,9 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
     if (build) {
       if (tc) {
         setl("bwd", &s, "c3");
-        rc = build_tc_ops(m->ops_bwd, c3.b_dgrad, 1, 1, true, g_sum, g_b, nullptr, nullptr, t.mb, 0);
+        rc = emit(m->ops_bwd, [&](std::vector<Op>& v_) { return build_tc_ops(v_, c3.b_dgrad, 1, 1, true, g_sum, g_b, nullptr, nullptr, t.mb, 0); });
         setl("bwd", &s, "c2");
-        if (!rc) rc = build_tc_ops(m->ops_bwd, c2.b_dgrad, 3, s.stride, true, g_b, g_a, nullptr, nullptr, t.ma, 0);
+        if (!rc) rc = emit(m->ops_bwd, [&](std::vector<Op>& v_) { return build_tc_ops(v_, c2.b_dgrad, 3, s.stride, true, g_b, g_a, nullptr, nullptr, t.ma, 0); });
       } else {
         typedef const float* F;
         rc = build_simt_op(m->ops_bwd, c3.f_dgrad, 1, 1, true, g_sum, g_b, nullptr, nullptr, (F)t.b.p, 0);
@@ -690,7 +793,7 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
         if (s.stride == 1) {
           setl("bwd", &s, "c1+ds");
           const PwSrc src[2] = {{g_a, 1, 0, 0, c1.b_dgrad}, {g_sum, 1, 0, 0, cd.b_dgrad}};
-          rc = build_pw_ops(m->ops_bwd, src, 2, g_x, 1, 0, 0, nullptr, mk, 0, nullptr);
+          rc = emit(m->ops_bwd, [&](std::vector<Op>& v_) { return build_pw_ops(v_, src, 2, g_x, 1, 0, 0, nullptr, mk, 0, nullptr); });
         } else {
           for (int ph = 0; ph < 2 && !rc; ++ph)
             for (int pw = 0; pw < 2 && !rc; ++pw) {
@@ -698,7 +801,7 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
               snprintf(l2, sizeof l2, (ph | pw) ? "c1/%d" : "c1+ds/%d", ph * 2 + pw);
               setl("bwd", &s, l2);
               const PwSrc src[2] = {{g_a, 2, ph, pw, c1.b_dgrad}, {g_sum, 1, 0, 0, cd.b_dgrad}};
-              rc = build_pw_ops(m->ops_bwd, src, (ph | pw) ? 1 : 2, g_x, 2, ph, pw, nullptr, mk, 0, nullptr);
+              rc = emit(m->ops_bwd, [&](std::vector<Op>& v_) { return build_pw_ops(v_, src, (ph | pw) ? 1 : 2, g_x, 2, ph, pw, nullptr, mk, 0, nullptr); });
             }
         }
       }
@@ -713,7 +816,7 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
             m->ops_bwd.push_back(ms);
           }
           setl("bwd", &s, "ds");
-          rc = build_tc_ops(m->ops_bwd, cd.b_dgrad, 1, s.stride, true, g_sum, g_t, nullptr, nullptr, nullptr, 0);
+          rc = emit(m->ops_bwd, [&](std::vector<Op>& v_) { return build_tc_ops(v_, cd.b_dgrad, 1, s.stride, true, g_sum, g_t, nullptr, nullptr, nullptr, 0); });
         } else {
           rc = build_simt_op(m->ops_bwd, cd.f_dgrad, 1, s.stride, true, g_sum, g_t, nullptr, nullptr, nullptr, 0);
         }
@@ -722,8 +825,8 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
       nxt = gacquire(); g_x.p = gbuf[nxt];
       if (build && !rc) {
         setl("bwd", &s, "c1");
-        if (tc) rc = build_tc_ops(m->ops_bwd, c1.b_dgrad, 1, 1, true, g_a, g_x, nullptr, (const bf16*)g_t.p,
-                                  first ? nullptr : t.mx, 0);
+        if (tc) rc = emit(m->ops_bwd, [&](std::vector<Op>& v_) { return build_tc_ops(v_, c1.b_dgrad, 1, 1, true, g_a, g_x, nullptr, (const bf16*)g_t.p,
+                                  first ? nullptr : t.mx, 0); });
         else rc = build_simt_op(m->ops_bwd, c1.f_dgrad, 1, 1, true, g_a, g_x, nullptr, (const float*)g_t.p,
                                 first ? nullptr : (const float*)t.x.p, 0);
       }
@@ -732,8 +835,8 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
       nxt = gacquire(); g_x.p = gbuf[nxt];
       if (build && !rc) {
         setl("bwd", &s, "c1");
-        if (tc) rc = build_tc_ops(m->ops_bwd, c1.b_dgrad, 1, 1, true, g_a, g_x, nullptr, (const bf16*)g_sum.p,
-                                  first ? nullptr : t.mx, 0);
+        if (tc) rc = emit(m->ops_bwd, [&](std::vector<Op>& v_) { return build_tc_ops(v_, c1.b_dgrad, 1, 1, true, g_a, g_x, nullptr, (const bf16*)g_sum.p,
+                                  first ? nullptr : t.mx, 0); });
         else rc = build_simt_op(m->ops_bwd, c1.f_dgrad, 1, 1, true, g_a, g_x, nullptr, (const float*)g_sum.p,
                                 (const float*)t.x.p, 0);
       }
@@ -790,7 +893,7 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out) {
   return (int64_t)bump.off;
 }
 
-int ensure_plan(advb200_model* m, int n, void* ws, int64_t ws_bytes) {
+int ensure_plan(advb200_model* m, int n, void* ws, int64_t ws_bytes, cudaStream_t st = nullptr) {
   ADV_CHECK_ARG(m, "null model");
   ADV_CHECK_ARG(n > 0, "batch must be positive");
   ADV_CHECK_ARG(ws, "workspace is null");
@@ -799,7 +902,7 @@ int ensure_plan(advb200_model* m, int n, void* ws, int64_t ws_bytes) {
   const int64_t need = plan(m, n, nullptr, nullptr);
   if (ws_bytes < need) return fail(ADVB200_ERR_ARG, "workspace too small: need " + std::to_string(need));
   int rc = ADVB200_OK;
-  plan(m, n, ws, &rc);
+  plan(m, n, ws, &rc, st, true);
   if (rc) { m->plan_n = -1; return rc; }
   m->plan_n = n; m->plan_ws = ws;
   return ADVB200_OK;
@@ -973,6 +1076,12 @@ int advb200_model_destroy(advb200_model* m) {
   return ADVB200_OK;
 }
 
+int advb200_tune_report(const advb200_model* m, int* tuned_launches, double* tune_ms) {
+  ADV_CHECK_ARG(m && tuned_launches && tune_ms, "tune_report: null argument");
+  *tuned_launches = m->tuned_ops; *tune_ms = m->tune_ms;
+  return ADVB200_OK;
+}
+
 int advb200_model_precision(const advb200_model* m) { return m ? m->precision : ADVB200_ERR_ARG; }
 
 int64_t advb200_workspace_bytes(const advb200_model* m, int n) {
@@ -985,9 +1094,9 @@ int advb200_forward(advb200_model* m, const float* x, const float* mean3, const 
                     int64_t workspace_bytes, void* stream) {
   ADV_CHECK_ARG(m && x && mean3 && std3, "forward: null argument");
   ADV_CHECK_ARG(stop_at_layer3 || logits_out || preds_out || score_out, "forward: no output requested");
-  int rc = ensure_plan(m, n, workspace, workspace_bytes);
-  if (rc) return rc;
   cudaStream_t st = as_stream(stream);
+  int rc = ensure_plan(m, n, workspace, workspace_bytes, st);
+  if (rc) return rc;
   rc = forward_impl(m, x, mean3, std3, n, stop_at_layer3 != 0, score_out, st);
   if (rc || stop_at_layer3) return rc;
   if (logits_out)
@@ -1002,9 +1111,9 @@ int advb200_input_grad(advb200_model* m, const float* x, const float* mean3, con
                        float* grad_x_out, void* workspace, int64_t workspace_bytes, void* stream) {
   ADV_CHECK_ARG(m && x && mean3 && std3 && y_cmp && grad_x_out, "input_grad: null argument");
   ADV_CHECK_ARG(loss_kind >= ADVB200_LOSS_CE_MEAN && loss_kind <= ADVB200_LOSS_CW_TGT, "input_grad: bad loss kind");
-  int rc = ensure_plan(m, n, workspace, workspace_bytes);
-  if (rc) return rc;
   cudaStream_t st = as_stream(stream);
+  int rc = ensure_plan(m, n, workspace, workspace_bytes, st);
+  if (rc) return rc;
   const bool tc = m->precision == ADVB200_PREC_BF16;
   if ((rc = forward_impl(m, x, mean3, std3, n, false, nullptr, st))) return rc;
   if (logits_out)

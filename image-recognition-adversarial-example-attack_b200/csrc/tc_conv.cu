@@ -824,7 +824,7 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
     p.stage_bytes = (p.halo_rows * 128 + 1023) & ~1023;
   }
   static const char* force_slots = getenv("ADVB200_OUT_SLOTS");   // tuning knob
-  p.out_slots = force_slots ? atoi(force_slots) : (p.ksteps >= 8 ? 2 : 4);
+  p.out_slots = p.slots_req ? p.slots_req : force_slots ? atoi(force_slots) : (p.ksteps >= 8 ? 2 : 4);
   int units = kPair ? kNumSMs / 2 : kNumSMs;            // CTAs or CTA pairs
   // resident-weight mode (pointwise convs): when all k-blocks of one column block fit beside a >= 3-deep ring of
   // A tiles, each CTA keeps one column block for all of its tiles (tile stride = multiple of tiles_c) and only

@@ -58,6 +58,7 @@ struct ConvGemmParams {
   int pix_sub, pix_ph, pix_pw;    // output pixel (h, w) of tile coords (th, tw): (th*sub+ph, tw*sub+pw)
   int full_h, full_w;             // full-resolution output height / width
   int bres_off;                   // caller opt-out of the resident-weight mode
+  int slots_req;                  // caller-requested output staging slots (0 = launcher default)
   int bres;                       // chosen by launch_conv_gemm: weights resident, ring carries activations only
   int stages;                     // smem ring depth chosen by the host for this launch
   int out_slots;                  // output staging slots (2 or 4), host-chosen

@@ -177,6 +177,10 @@ int advb200_profile_read(double* conv_ms_host, int64_t* conv_launches_host);
  * flops / HBM bytes of that launch).  Writes at most cap bytes (NUL-terminated) into buf_host, returns
  * the size needed, and clears the list. */
 int64_t advb200_profile_dump(char* buf_host, int64_t cap);
+/* Plan-time autotuner report: number of conv launches whose tile configuration was chosen by timing
+ * candidates on the device (at the first call for a batch size), and the host wall time that took.
+ * ADVB200_NO_AUTOTUNE=1 in the environment disables tuning (heuristic tile choice). */
+int advb200_tune_report(const advb200_model* m, int* tuned_launches_host, double* tune_ms_host);
 
 #ifdef __cplusplus
 }
