@@ -166,6 +166,7 @@ int build_pw_ops(std::vector<Op>& ops, const PwSrc* src, int nsrc, Act out, int 
   p.mask_pixels = (long long)out.n * out.h * out.w;
   p.pix_sub = osub; p.pix_ph = oph; p.pix_pw = opw; p.full_h = out.h; p.full_w = out.w;
   p.ntaps = nsrc; p.ksteps = ksteps; p.has_b2 = nsrc > 1; p.kblocks = 0;
+  p.out = out.p;
   int rc = tmap_act(&t.maps.out, out, osub, oph, opw, p.bw, p.bh, p.bn);
   for (int i = 0; i < nsrc && !rc; ++i) {
     p.tap_map[i] = i; p.tap_dw[i] = 0; p.tap_dh[i] = 0; p.tap_brow[i] = 0;
@@ -228,7 +229,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
   p.mask_pixels = (long long)out.n * out.h * out.w;
   p.pix_sub = 1; p.pix_ph = 0; p.pix_pw = 0; p.full_h = out.h; p.full_w = out.w;
   p.cout = gemm_n;
-  p.out = nullptr;
+  p.out = out.p;
   const int n_aux = p.has_add;
   // output-shaped maps (store target, residual, mask): 64-channel boxes over the same pixel box as A
   auto make_out_maps = [&](TcOp& tt, const Act& o, int sub, int ph, int pw) {
@@ -481,7 +482,7 @@ struct advb200_model {
   // tensors
   Act t_in, c1, p1, l3out, l4out;
   uint8_t* pool_idx = nullptr;
-  float *feat = nullptr, *logits = nullptr, *dlogits = nullptr, *dfeat = nullptr;
+  float *feat = nullptr, *logits = nullptr, *dlogits = nullptr, *dfeat = nullptr, *fc_part = nullptr;
   void* g_final = nullptr;      // gradient w.r.t. p1 lives here after the body backward
   void* g_c1 = nullptr;
   void* g_top = nullptr;        // gradient w.r.t. layer4 output (masked) is written here
@@ -560,7 +561,7 @@ struct Tuner {
         if (cout % bn || (bn == 64 && cout >= 256)) continue;
         for (int pair = 0; pair < 2; ++pair)
           for (int bres : {-1, 0})
-            for (int slots : {2, 4}) { TileForce f; f.bn = bn; f.pair = pair; f.bres = bres; f.slots = slots; cands.push_back(f); }
+            for (int slots : {1, 2, 4}) { TileForce f; f.bn = bn; f.pair = pair; f.bres = bres; f.slots = slots; cands.push_back(f); }
       }
       std::vector<float> best_ms(base.size(), 1e30f);
       std::vector<TileForce> best(base.size());
@@ -652,6 +653,7 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out, cudaStream_t tune_s
   m->logits = reinterpret_cast<float*>(bump.take((size_t)n * kClasses * 4));
   m->dlogits = reinterpret_cast<float*>(bump.take((size_t)n * kClasses * 4));
   m->dfeat = reinterpret_cast<float*>(bump.take((size_t)n * kFeat * 4));
+  m->fc_part = reinterpret_cast<float*>(bump.take((size_t)fc_nt_partial_bytes(n, kFeat)));
   m->g_img_nhwc = tc ? nullptr : reinterpret_cast<float*>(bump.take((size_t)n * kImg * kImg * 3 * 4));
 
   // ---- conv1 forward
@@ -931,7 +933,7 @@ int forward_impl(advb200_model* m, const float* x, const float* mean3, const flo
   else rc = launch_avgpool_fwd<float>((const float*)m->l4out.p, m->feat, n, 49, kFeat, st);
   if (rc) return rc;
   // fc forward: logits = feat * W^T + b   (fp32 in both modes)
-  return launch_fc_nt(m->feat, m->fc_w, m->fc_b, m->logits, n, kClasses, kFeat, st);
+  return launch_fc_nt(m->feat, m->fc_w, m->fc_b, m->logits, m->fc_part, n, kClasses, kFeat, st);
 }
 
 }  // namespace
@@ -1123,7 +1125,7 @@ int advb200_input_grad(advb200_model* m, const float* x, const float* mean3, con
                              loss_out, success_out, st)))
     return rc;
   // fc input gradient: dfeat = dlogits * W
-  if ((rc = launch_fc_nt(m->dlogits, m->fc_wt, nullptr, m->dfeat, n, kFeat, kClasses, st))) return rc;
+  if ((rc = launch_fc_nt(m->dlogits, m->fc_wt, nullptr, m->dfeat, m->fc_part, n, kFeat, kClasses, st))) return rc;
   if (tc) rc = launch_avgpool_bwd<bf16>(m->dfeat, (const bf16*)m->l4out.p, (bf16*)m->g_top, n, 49, kFeat, st);
   else rc = launch_avgpool_bwd<float>(m->dfeat, (const float*)m->l4out.p, (float*)m->g_top, n, 49, kFeat, st);
   if (rc) return rc;

@@ -158,6 +158,16 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
   return make_uint4(w[0], w[1], w[2], w[3]);
 }
 
+// Packed-SIMD versions (these kernels are instruction-bound otherwise): values stay bf16x2, the running
+// argmax position lives in the matching 16-bit lanes and is selected with the comparison mask.
+__device__ __forceinline__ uint32_t hgt2_mask(uint32_t a, uint32_t b) {      // per 16-bit lane: a > b ? 0xffff : 0
+  return __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+}
+__device__ __forceinline__ uint32_t hadd2_u(uint32_t a, uint32_t b) {
+  __nv_bfloat162 r = __hadd2(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+
 __global__ void __launch_bounds__(kT)
 maxpool_fwd_bf16x8_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, uint8_t* __restrict__ idx, int hi,
                           int wi, int ho, int wo, int c8, long long total) {
@@ -168,9 +178,9 @@ maxpool_fwd_bf16x8_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, u
   const int ow = (int)(r % wo); r /= wo;
   const int oh = (int)(r % ho);
   const long long n = r / ho;
-  float best[8]; int pos[8];
+  uint32_t best[4], pos[4];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) { best[i] = -INFINITY; pos[i] = 0; }
+  for (int i = 0; i < 4; ++i) { best[i] = 0xFF80FF80u; pos[i] = 0; }       // -inf, position 0
 #pragma unroll
   for (int dr = 0; dr < 3; ++dr) {
     const int ih = 2 * oh - 1 + dr;
@@ -180,21 +190,24 @@ maxpool_fwd_bf16x8_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, u
       const int iw = 2 * ow - 1 + ds;
       if (iw < 0 || iw >= wi) continue;
       const uint4 u = __ldg(reinterpret_cast<const uint4*>(in + (((n * hi + ih) * wi + iw) * c8 + cg) * 8));
-      float f[8];
-      unpack8(u, f);
+      const uint32_t v[4] = {u.x, u.y, u.z, u.w};
+      const uint32_t code = (uint32_t)(dr * 3 + ds) * 0x00010001u;
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
-        if (f[i] > best[i]) { best[i] = f[i]; pos[i] = dr * 3 + ds; }
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t m = hgt2_mask(v[i], best[i]);            // strict: the first maximum wins (torch tie rule)
+        best[i] = (v[i] & m) | (best[i] & ~m);
+        pos[i] = (code & m) | (pos[i] & ~m);
+      }
     }
   }
-  *reinterpret_cast<uint4*>(out + t * 8) = pack8(best);
-  uint32_t lo = 0, hi32 = 0;
+  *reinterpret_cast<uint4*>(out + t * 8) = make_uint4(best[0], best[1], best[2], best[3]);
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    lo |= (uint32_t)(best[i] > 0.f ? pos[i] : 255) << (8 * i);
-    hi32 |= (uint32_t)(best[4 + i] > 0.f ? pos[4 + i] : 255) << (8 * i);
+    const uint32_t m = hgt2_mask(best[i], 0u);                  // ReLU-blocked outputs route no gradient: 255
+    pos[i] = (pos[i] & m) | (0x00FF00FFu & ~m);
   }
-  *reinterpret_cast<uint2*>(idx + t * 8) = make_uint2(lo, hi32);
+  *reinterpret_cast<uint2*>(idx + t * 8) =
+      make_uint2(__byte_perm(pos[0], pos[1], 0x6420), __byte_perm(pos[2], pos[3], 0x6420));
 }
 
 // one thread = a 2x2 input patch (rows 2a,2a+1; cols 2b,2b+1) x 8 channels: the four windows that can
@@ -225,34 +238,26 @@ maxpool_bwd_bf16x8_kernel(const bf16* __restrict__ gout, const uint8_t* __restri
         gv[i][j] = make_uint4(0, 0, 0, 0);
       }
     }
-  float gf[2][2][8];
-#pragma unroll
-  for (int i = 0; i < 2; ++i)
-#pragma unroll
-    for (int j = 0; j < 2; ++j) unpack8(gv[i][j], gf[i][j]);
 #pragma unroll
   for (int dy = 0; dy < 2; ++dy)
 #pragma unroll
     for (int dx = 0; dx < 2; ++dx) {
       const int ih = 2 * pa + dy, iw = 2 * pb + dx;
-      float g[8];
+      uint32_t g[4] = {0u, 0u, 0u, 0u};
+      // windows containing (ih, iw): row a (dr = 1 + dy) and, for dy = 1, row a+1 (dr = 0); likewise columns.
+      // Same visiting order as the scalar kernel; sums of two addends round exactly like its fp32 sum.
 #pragma unroll
-      for (int k = 0; k < 8; ++k) g[k] = 0.f;
-      // windows containing (ih, iw): oh in {ih>>1 .. (ih+1)>>1}, likewise ow  (same order as the scalar kernel)
+      for (int i = 0; i <= dy; ++i)
 #pragma unroll
-      for (int i = 0; i < 2; ++i)
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          const int oh = pa + i, ow = pb + j;
-          if (oh < (ih >> 1) || oh > ((ih + 1) >> 1) || ow < (iw >> 1) || ow > ((iw + 1) >> 1)) continue;
-          const uint32_t want = (uint32_t)((ih - (2 * oh - 1)) * 3 + (iw - (2 * ow - 1)));
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            if (((ix[i][j].x >> (8 * k)) & 0xffu) == want) g[k] += gf[i][j][k];
-            if (((ix[i][j].y >> (8 * k)) & 0xffu) == want) g[4 + k] += gf[i][j][4 + k];
-          }
+        for (int j = 0; j <= dx; ++j) {
+          const uint32_t want = (uint32_t)((i ? 0 : 1 + dy) * 3 + (j ? 0 : 1 + dx)) * 0x01010101u;
+          const uint32_t mlo = __vcmpeq4(ix[i][j].x, want), mhi = __vcmpeq4(ix[i][j].y, want);
+          g[0] = hadd2_u(g[0], gv[i][j].x & __byte_perm(mlo, 0, 0x1100));
+          g[1] = hadd2_u(g[1], gv[i][j].y & __byte_perm(mlo, 0, 0x3322));
+          g[2] = hadd2_u(g[2], gv[i][j].z & __byte_perm(mhi, 0, 0x1100));
+          g[3] = hadd2_u(g[3], gv[i][j].w & __byte_perm(mhi, 0, 0x3322));
         }
-      *reinterpret_cast<uint4*>(gin + (((n * hi + ih) * wi + iw) * c8 + cg) * 8) = pack8(g);
+      *reinterpret_cast<uint4*>(gin + (((n * hi + ih) * wi + iw) * c8 + cg) * 8) = make_uint4(g[0], g[1], g[2], g[3]);
     }
 }
 

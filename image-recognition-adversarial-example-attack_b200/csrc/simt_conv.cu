@@ -99,61 +99,82 @@ simt_conv_kernel(const SimtConvParams p) {
   }
 }
 
-// out[m, n] = sum_k a[m, k] * b[n, k] (+ bias[n]) — both operands K-contiguous (fp32 classifier head)
+// out[m, n] = sum_k a[m, k] * b[n, k] (+ bias[n]) — both operands K-contiguous (fp32 classifier head).
+// Deterministic split-K: kSplit slices of K write partial sums, a second kernel adds them in a fixed order
+// (fp32 atomics would make the logits run-to-run different).  64 x 64 block tile, 4 x 4 outputs per thread.
+constexpr int kFcSplit = 4;
 __global__ void __launch_bounds__(256)
-fc_nt_kernel(const float* __restrict__ a, const float* __restrict__ b, const float* __restrict__ bias,
-             float* __restrict__ out, int m_total, int n_total, int k_total) {
-  __shared__ float As[32][33];
-  __shared__ float Bs[64][33];
+fc_nt_splitk_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ part,
+                    int m_total, int n_total, int k_total, int k_chunk) {
+  __shared__ __align__(16) float As[16][68];
+  __shared__ __align__(16) float Bs[16][68];
   const int tid = threadIdx.x;
-  const int tx = tid & 15, ty = tid >> 4;          // 16 x 16 threads, 2 x 4 outputs each
-  const int m0 = blockIdx.x * 32, n0 = blockIdx.y * 64;
-  float acc[2][4] = {};
-  for (int k0 = 0; k0 < k_total; k0 += 32) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int idx = tid + i * 256, r = idx >> 5, kk = idx & 31;
-      const int m = m0 + r, k = k0 + kk;
-      As[r][kk] = (m < m_total && k < k_total) ? __ldg(a + (long long)m * k_total + k) : 0.f;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int m0 = blockIdx.x * 64, n0 = blockIdx.y * 64;
+  const int kbeg = blockIdx.z * k_chunk;
+  const int kend = min(k_total, kbeg + k_chunk);
+  const int lr = tid >> 2, lk = (tid & 3) * 4;          // this thread's load: row lr, k offset lk (one float4)
+  float acc[4][4] = {};
+  for (int k0 = kbeg; k0 < kend; k0 += 16) {
+    float4 va = make_float4(0.f, 0.f, 0.f, 0.f), vb = va;
+    const int k = k0 + lk;
+    if (k < kend) {
+      if (m0 + lr < m_total) va = __ldg(reinterpret_cast<const float4*>(a + (long long)(m0 + lr) * k_total + k));
+      if (n0 + lr < n_total) vb = __ldg(reinterpret_cast<const float4*>(b + (long long)(n0 + lr) * k_total + k));
     }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int idx = tid + i * 256, r = idx >> 5, kk = idx & 31;
-      const int n = n0 + r, k = k0 + kk;
-      Bs[r][kk] = (n < n_total && k < k_total) ? __ldg(b + (long long)n * k_total + k) : 0.f;
-    }
+    As[lk][lr] = va.x; As[lk + 1][lr] = va.y; As[lk + 2][lr] = va.z; As[lk + 3][lr] = va.w;
+    Bs[lk][lr] = vb.x; Bs[lk + 1][lr] = vb.y; Bs[lk + 2][lr] = vb.z; Bs[lk + 3][lr] = vb.w;
     __syncthreads();
 #pragma unroll
-    for (int kk = 0; kk < 32; ++kk) {
-      const float a0 = As[ty * 2][kk], a1 = As[ty * 2 + 1][kk];
+    for (int kk = 0; kk < 16; ++kk) {
+      const float4 a4 = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
+      const float4 b4 = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+      const float av[4] = {a4.x, a4.y, a4.z, a4.w}, bv[4] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float bv = Bs[tx * 4 + j][kk];
-        acc[0][j] = fmaf(a0, bv, acc[0][j]);
-        acc[1][j] = fmaf(a1, bv, acc[1][j]);
-      }
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
     }
     __syncthreads();
   }
+  float* po = part + (long long)blockIdx.z * m_total * n_total;
 #pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const int m = m0 + ty * 2 + i;
+  for (int i = 0; i < 4; ++i) {
+    const int m = m0 + ty * 4 + i;
     if (m >= m_total) continue;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int n = n0 + tx * 4 + j;
-      if (n < n_total) out[(long long)m * n_total + n] = acc[i][j] + (bias ? __ldg(bias + n) : 0.f);
+      if (n < n_total) po[(long long)m * n_total + n] = acc[i][j];
     }
   }
 }
 
+__global__ void __launch_bounds__(256)
+fc_reduce_kernel(const float* __restrict__ part, const float* __restrict__ bias, float* __restrict__ out,
+                 long long mn, int n_total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= mn) return;
+  float s = 0.f;
+#pragma unroll
+  for (int z = 0; z < kFcSplit; ++z) s += part[z * mn + t];
+  out[t] = s + (bias ? __ldg(bias + (int)(t % n_total)) : 0.f);
+}
+
 }  // namespace
 
-int launch_fc_nt(const float* a, const float* b, const float* bias, float* out, int m, int n, int k,
-                 cudaStream_t stream) {
+int64_t fc_nt_partial_bytes(int m, int n) { return (int64_t)kFcSplit * m * n * 4; }
+
+int launch_fc_nt(const float* a, const float* b, const float* bias, float* out, float* partial, int m, int n,
+                 int k, cudaStream_t stream) {
   if (m == 0) return ADVB200_OK;
-  dim3 grid((unsigned)((m + 31) / 32), (unsigned)((n + 63) / 64));
-  fc_nt_kernel<<<grid, 256, 0, stream>>>(a, b, bias, out, m, n, k);
+  ADV_CHECK_ARG(k % 4 == 0 && partial, "fc: K must be a multiple of 4 and the split-K scratch non-null");
+  const int k_chunk = (((k + kFcSplit - 1) / kFcSplit) + 15) / 16 * 16;
+  dim3 grid((unsigned)((m + 63) / 64), (unsigned)((n + 63) / 64), kFcSplit);
+  fc_nt_splitk_kernel<<<grid, 256, 0, stream>>>(a, b, partial, m, n, k, k_chunk);
+  ADV_LAUNCHED();
+  const long long mn = (long long)m * n;
+  fc_reduce_kernel<<<(unsigned)((mn + 255) / 256), 256, 0, stream>>>(partial, bias, out, mn, n);
   ADV_LAUNCHED();
   return ADVB200_OK;
 }

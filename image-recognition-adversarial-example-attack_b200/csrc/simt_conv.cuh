@@ -20,7 +20,9 @@ struct SimtConvParams {
 int launch_simt_conv(const SimtConvParams& p, cudaStream_t stream);
 
 // out[m, n] = sum_k a[m, k] * b[n, k] (+ bias[n]); fp32, both operands K-contiguous
-int launch_fc_nt(const float* a, const float* b, const float* bias, float* out, int m, int n, int k,
-                 cudaStream_t stream);
+// (deterministic split-K: `partial` is scratch of fc_nt_partial_bytes(m, n) bytes)
+int64_t fc_nt_partial_bytes(int m, int n);
+int launch_fc_nt(const float* a, const float* b, const float* bias, float* out, float* partial, int m, int n,
+                 int k, cudaStream_t stream);
 
 }  // namespace advb200

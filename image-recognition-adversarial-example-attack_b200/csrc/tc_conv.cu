@@ -751,18 +751,29 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
 #pragma unroll
             for (int i = 0; i < 32; ++i) f[i] = ((mw >> i) & 1u) ? f[i] : 0.f;
           }
+          uint4 o[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            uint4 o;
             if (relu) {
-              o.x = pack_bf16x2_relu(f[8 * i], f[8 * i + 1]); o.y = pack_bf16x2_relu(f[8 * i + 2], f[8 * i + 3]);
-              o.z = pack_bf16x2_relu(f[8 * i + 4], f[8 * i + 5]); o.w = pack_bf16x2_relu(f[8 * i + 6], f[8 * i + 7]);
+              o[i].x = pack_bf16x2_relu(f[8 * i], f[8 * i + 1]); o[i].y = pack_bf16x2_relu(f[8 * i + 2], f[8 * i + 3]);
+              o[i].z = pack_bf16x2_relu(f[8 * i + 4], f[8 * i + 5]); o[i].w = pack_bf16x2_relu(f[8 * i + 6], f[8 * i + 7]);
             } else {
-              o.x = pack_bf16x2(f[8 * i], f[8 * i + 1]); o.y = pack_bf16x2(f[8 * i + 2], f[8 * i + 3]);
-              o.z = pack_bf16x2(f[8 * i + 4], f[8 * i + 5]); o.w = pack_bf16x2(f[8 * i + 6], f[8 * i + 7]);
+              o[i].x = pack_bf16x2(f[8 * i], f[8 * i + 1]); o[i].y = pack_bf16x2(f[8 * i + 2], f[8 * i + 3]);
+              o[i].z = pack_bf16x2(f[8 * i + 4], f[8 * i + 5]); o[i].w = pack_bf16x2(f[8 * i + 6], f[8 * i + 7]);
             }
-            sts128(obase + row_off + ((((uint32_t)(half * 4 + i)) ^ sw) << 4), o);
           }
+          if (n_out_slots == 0) {
+            // direct mode: this thread's 32 channels (64 contiguous bytes of its pixel) go straight to global
+            // memory — no staging tile, no barrier, and the smem goes to the operand ring instead
+            if (valid) {
+              uint4* gp = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + pixel * p.cout + tc.c0 + 64 * j + half * 32);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) gp[i] = o[i];
+            }
+            continue;
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) sts128(obase + row_off + ((((uint32_t)(half * 4 + i)) ^ sw) << 4), o[i]);
           fence_async_smem();          // generic-proxy smem writes -> visible to the TMA store
           epi_bar();
           if (leader) {
@@ -824,7 +835,7 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
     p.stage_bytes = (p.halo_rows * 128 + 1023) & ~1023;
   }
   static const char* force_slots = getenv("ADVB200_OUT_SLOTS");   // tuning knob
-  p.out_slots = p.slots_req ? p.slots_req : force_slots ? atoi(force_slots) : (p.ksteps >= 8 ? 2 : 4);
+  p.out_slots = p.slots_req == 1 ? 0 : p.slots_req ? p.slots_req : force_slots ? atoi(force_slots) : (p.ksteps >= 8 ? 2 : 4);
   int units = kPair ? kNumSMs / 2 : kNumSMs;            // CTAs or CTA pairs
   // resident-weight mode (pointwise convs): when all k-blocks of one column block fit beside a >= 3-deep ring of
   // A tiles, each CTA keeps one column block for all of its tiles (tile stride = multiple of tiles_c) and only

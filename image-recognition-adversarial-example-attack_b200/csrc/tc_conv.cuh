@@ -45,7 +45,8 @@ struct ConvGemmParams {
   int tap_row[kMaxTaps];
   // output extent in tile coordinates (w, h, n) and channels
   int out_w, out_h, out_n, cout;
-  void* out;                      // epi 1 only: fp32 NCHW image gradient (epi 0 stores through maps.out)
+  void* out;                      // epi 0: bf16 NHWC output tensor (direct-store epilogue); epi 1/2: fp32 NCHW
+                                  // image gradient
   const float* bias;              // [cout] or null
   int has_add;                    // residual / other-branch gradient tile read through maps.add
   int relu;
@@ -58,7 +59,8 @@ struct ConvGemmParams {
   int pix_sub, pix_ph, pix_pw;    // output pixel (h, w) of tile coords (th, tw): (th*sub+ph, tw*sub+pw)
   int full_h, full_w;             // full-resolution output height / width
   int bres_off;                   // caller opt-out of the resident-weight mode
-  int slots_req;                  // caller-requested output staging slots (0 = launcher default)
+  int slots_req;                  // caller-requested output staging slots (0 = launcher default, 1 = none:
+                                  // the epilogue stores straight to global memory through `out`)
   int bres;                       // chosen by launch_conv_gemm: weights resident, ring carries activations only
   int stages;                     // smem ring depth chosen by the host for this launch
   int out_slots;                  // output staging slots (2 or 4), host-chosen
