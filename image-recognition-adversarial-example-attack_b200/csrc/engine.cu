@@ -167,7 +167,7 @@ int build_pw_ops(std::vector<Op>& ops, const PwSrc* src, int nsrc, Act out, int 
   p.pix_sub = osub; p.pix_ph = oph; p.pix_pw = opw; p.full_h = out.h; p.full_w = out.w;
   p.ntaps = nsrc; p.ksteps = ksteps; p.has_b2 = nsrc > 1; p.kblocks = 0;
   p.out = out.p;
-  int rc = tmap_act(&t.maps.out, out, osub, oph, opw, p.bw, p.bh, p.bn);
+  int rc = tmap_act(&t.maps.out[0], out, osub, oph, opw, p.bw, p.bh, p.bn);
   for (int i = 0; i < nsrc && !rc; ++i) {
     p.tap_map[i] = i; p.tap_dw[i] = 0; p.tap_dh[i] = 0; p.tap_brow[i] = 0;
     p.tap_kb[i] = src[i].in.c / 64; p.tap_bmap[i] = i;
@@ -181,6 +181,67 @@ int build_pw_ops(std::vector<Op>& ops, const PwSrc* src, int nsrc, Act out, int 
   const double pix = (double)out.n * lw * lh;
   label_op(op, "", 2.0 * pix * gemm_n * kin,
            in_bytes + 2.0 * pix * gemm_n * (1.0 + (mask ? 1.0 / 16 : 0) + (mask_out ? 1.0 / 16 : 0)) + 2.0 * gemm_n * kin);
+  ops.push_back(op);
+  return ADVB200_OK;
+}
+
+// Input gradient of a stride-2 downsample block entry in ONE multi-class launch:
+//   g_x[2h+ph, 2w+pw] = mask . (W1^T g_a[2h+ph, 2w+pw]  (+ Wds^T g_sum[h, w] on the (0,0) lattice))
+// class c = ph*2+pw reads g_a's own sub-lattice through maps.a[c]; class 0 also reads g_sum through maps.a[4].
+int build_pw_s2_ops(std::vector<Op>& ops, Act g_a, const bf16* w1, Act g_sum, const bf16* wds, Act g_x,
+                    const uint32_t* mask) {
+  const int gemm_n = g_x.c;
+  const int lw = g_x.w / 2, lh = g_x.h / 2;
+  ADV_CHECK_ARG(g_a.h == g_x.h && g_a.w == g_x.w && g_sum.h == lh && g_sum.w == lw && g_a.c % 64 == 0 &&
+                    g_sum.c % 64 == 0 && g_a.n == g_x.n && g_sum.n == g_x.n, "pw s2: shape mismatch");
+  Op op;
+  op.kind = Op::TC;
+  TcOp& t = op.tc;
+  ConvGemmParams& p = t.p;
+  memset(&p, 0, sizeof p);
+  memset(&t.maps, 0, sizeof t.maps);
+  tile_shape(lw, lh, p.bw, p.bh, p.bn);
+  p.tiles_w = cdiv(lw, p.bw); p.tiles_h = cdiv(lh, p.bh); p.tiles_n = cdiv(g_x.n, p.bn);
+  const int kb1 = g_a.c / 64, kbd = g_sum.c / 64;
+  { const TileChoice tcz = pick_tile(gemm_n, 4ll * p.tiles_w * p.tiles_h * p.tiles_n, kb1 + kbd / 4); t.bn = tcz.bn; t.pair = tcz.pair; apply_force(p); }
+  p.tiles_c = gemm_n / t.bn;
+  p.out_w = lw; p.out_h = lh; p.out_n = g_x.n; p.cout = gemm_n;
+  p.mask_in = mask;
+  p.mask_pixels = (long long)g_x.n * g_x.h * g_x.w;
+  p.pix_sub = 2; p.full_h = g_x.h; p.full_w = g_x.w;
+  p.out = g_x.p;
+  p.has_b2 = 1; p.kblocks = 0; p.nclass = 4;
+  p.ntaps = 0;
+  int rc = ADVB200_OK;
+  for (int c = 0; c < 4 && !rc; ++c) {
+    p.cls_tap0[c] = p.ntaps; p.cls_ph[c] = c >> 1; p.cls_pw[c] = c & 1;
+    int i = p.ntaps++;
+    p.tap_map[i] = c; p.tap_kb[i] = kb1; p.tap_bmap[i] = 0;
+    if (c == 0) { i = p.ntaps++; p.tap_map[i] = 4; p.tap_kb[i] = kbd; p.tap_bmap[i] = 1; }
+    p.cls_ntaps[c] = p.ntaps - p.cls_tap0[c];
+    rc = tmap_act(&t.maps.a[c], g_a, 2, c >> 1, c & 1, p.bw, p.bh, p.bn);
+    if (!rc) rc = tmap_act(&t.maps.out[c], g_x, 2, c >> 1, c & 1, p.bw, p.bh, p.bn);
+  }
+  p.ksteps = kb1 + kbd;        // the launcher recomputes the per-class k-steps
+  if (!rc) rc = tmap_act(&t.maps.a[4], g_sum, 1, 0, 0, p.bw, p.bh, p.bn);
+  const uint32_t brows = (uint32_t)(t.pair ? t.bn / 2 : t.bn);
+  {
+    const uint64_t dims[2] = {(uint64_t)g_a.c, (uint64_t)gemm_n};
+    const uint64_t strides[1] = {(uint64_t)g_a.c * 2};
+    const uint32_t box[2] = {64, brows};
+    if (!rc) rc = make_tmap_bf16(&t.maps.b, w1, 2, dims, strides, box);
+  }
+  {
+    const uint64_t dims[2] = {(uint64_t)g_sum.c, (uint64_t)gemm_n};
+    const uint64_t strides[1] = {(uint64_t)g_sum.c * 2};
+    const uint32_t box[2] = {64, brows};
+    if (!rc) rc = make_tmap_bf16(&t.maps.b2, wds, 2, dims, strides, box);
+  }
+  if (rc) return rc;
+  const double pix = (double)g_x.n * lw * lh;
+  label_op(op, "", 2.0 * pix * gemm_n * (4.0 * g_a.c + g_sum.c),
+           2.0 * (4.0 * pix * g_a.c + pix * g_sum.c + 4.0 * pix * gemm_n * (1.0 + (mask ? 1.0 / 16 : 0)) +
+                  (double)gemm_n * (g_a.c + g_sum.c)));
   ops.push_back(op);
   return ADVB200_OK;
 }
@@ -235,7 +296,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
   auto make_out_maps = [&](TcOp& tt, const Act& o, int sub, int ph, int pw) {
     Act v = o;
     const ConvGemmParams& q = tt.p;
-    int rc = make_a(&tt.maps.out, v, sub, ph, pw, q.bw, q.bh, q.bn);
+    int rc = make_a(&tt.maps.out[0], v, sub, ph, pw, q.bw, q.bh, q.bn);
     if (!rc && add) { v.p = const_cast<bf16*>(add); rc = make_a(&tt.maps.add, v, sub, ph, pw, q.bw, q.bh, q.bn); }
     return rc;
   };
@@ -259,7 +320,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
       return make_tmap_bf16(mp, base, 4, dims, strides, box);
     };
     int rc = flat_map(&t.maps.a[0], in.p, gemm_k);
-    if (!rc) rc = flat_map(&t.maps.out, out.p, gemm_n);
+    if (!rc) rc = flat_map(&t.maps.out[0], out.p, gemm_n);
     if (!rc && add) rc = flat_map(&t.maps.add, add, gemm_n);
     if (!rc) rc = make_b(&t.maps.b, t.bn, t.pair);
     if (rc) return rc;
@@ -364,10 +425,47 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     return ADVB200_OK;
   }
 
-  // stride-2 dgrad: one launch per input-pixel parity class (ph, pw); each class is a stride-1
-  // gather over dY with the subset of taps whose parity matches, written to that sub-lattice of dX.
+  // stride-2 dgrad: each input-pixel parity class (ph, pw) is a stride-1 gather over dY with the subset of taps
+  // whose parity matches, written to that sub-lattice of dX.  All classes that receive gradient go into ONE
+  // multi-class launch (tile index -> class), so the four small GEMMs share one grid and its tail.
   ADV_CHECK_ARG(out.h == in.h * 2 && out.w == in.w * 2 && in.n == out.n, "tc conv dgrad s2: shape mismatch");
   const int pad = (ksize == 3) ? 1 : 0;
+  static const bool multiclass = !getenv("ADVB200_NO_MULTICLASS");
+  const int sw = out.w / 2, sh = out.h / 2;
+  if (multiclass && ksize == 3) {
+    Op o2 = op;
+    TcOp& t2 = o2.tc;
+    ConvGemmParams& q = t2.p;
+    q.ntaps = 0; q.nclass = 4;
+    for (int ph = 0; ph < 2; ++ph)
+      for (int pw = 0; pw < 2; ++pw) {
+        const int c = ph * 2 + pw;
+        q.cls_tap0[c] = q.ntaps; q.cls_ph[c] = ph; q.cls_pw[c] = pw;
+        for (int r = 0; r < 3; ++r)
+          for (int s = 0; s < 3; ++s) {
+            const int eh = ph + pad - r, ew = pw + pad - s;
+            if ((eh & 1) || (ew & 1)) continue;
+            const int i = q.ntaps++;
+            q.tap_map[i] = 0; q.tap_dh[i] = eh / 2; q.tap_dw[i] = ew / 2;
+            q.tap_brow[i] = (r * 3 + s) * gemm_n;
+          }
+        q.cls_ntaps[c] = q.ntaps - q.cls_tap0[c];
+      }
+    tile_shape(sw, sh, q.bw, q.bh, q.bn);
+    q.tiles_w = cdiv(sw, q.bw); q.tiles_h = cdiv(sh, q.bh); q.tiles_n = cdiv(out.n, q.bn);
+    { const TileChoice tcz = pick_tile(gemm_n, 4ll * q.tiles_w * q.tiles_h * q.tiles_n, (q.ntaps * q.kblocks) / 4); t2.bn = tcz.bn; t2.pair = tcz.pair; apply_force(q); }
+    q.tiles_c = gemm_n / t2.bn;
+    q.out_w = sw; q.out_h = sh; q.out_n = out.n;
+    q.pix_sub = 2;
+    int rc = make_a(&t2.maps.a[0], in, 1, 0, 0, q.bw, q.bh, q.bn);
+    for (int c = 0; c < 4 && !rc; ++c) rc = make_a(&t2.maps.out[c], out, 2, c >> 1, c & 1, q.bw, q.bh, q.bn);
+    if (!rc) rc = make_b(&t2.maps.b, t2.bn, t2.pair);
+    if (rc) return rc;
+    annotate(o2, "/*", 4.0 * out.n * sh * sw, q.ntaps, 1.0);
+    o2.flops *= 0.25;                                     // every class visits a quarter of the pixels
+    ops.push_back(o2);
+    return ADVB200_OK;
+  }
   for (int ph = 0; ph < 2; ++ph)
     for (int pw = 0; pw < 2; ++pw) {
       Op o2 = op;
@@ -384,7 +482,6 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
           q.tap_brow[i] = (r * ksize + s) * gemm_n;
         }
       if (q.ntaps == 0) continue;   // 1x1/2: only the (0,0) lattice receives gradient
-      const int sw = out.w / 2, sh = out.h / 2;
       tile_shape(sw, sh, q.bw, q.bh, q.bn);
       q.tiles_w = cdiv(sw, q.bw); q.tiles_h = cdiv(sh, q.bh); q.tiles_n = cdiv(out.n, q.bn);
       { const TileChoice tcz = pick_tile(gemm_n, (long long)q.tiles_w * q.tiles_h * q.tiles_n, q.ntaps * q.kblocks); t2.bn = tcz.bn; t2.pair = tcz.pair; apply_force(q); }
@@ -683,7 +780,7 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out, cudaStream_t tune_s
         const uint64_t od[4] = {64, 112, 112, (uint64_t)n};
         const uint64_t os[3] = {128, 128ull * 112, 128ull * 112 * 112};
         const uint32_t obox[4] = {64, 8, 16, 1};
-        if (!rc) rc = make_tmap_bf16(&t.maps.out, m->c1.p, 4, od, os, obox);
+        if (!rc) rc = make_tmap_bf16(&t.maps.out[0], m->c1.p, 4, od, os, obox);
       }
       const uint64_t bd[2] = {64, 256};
       const uint64_t bs[1] = {128};
@@ -797,6 +894,11 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out, cudaStream_t tune_s
           const PwSrc src[2] = {{g_a, 1, 0, 0, c1.b_dgrad}, {g_sum, 1, 0, 0, cd.b_dgrad}};
           rc = emit(m->ops_bwd, [&](std::vector<Op>& v_) { return build_pw_ops(v_, src, 2, g_x, 1, 0, 0, nullptr, mk, 0, nullptr); });
         } else {
+          static const bool multiclass = !getenv("ADVB200_NO_MULTICLASS");
+          if (multiclass) {
+            setl("bwd", &s, "c1+ds/*");
+            rc = emit(m->ops_bwd, [&](std::vector<Op>& v_) { return build_pw_s2_ops(v_, g_a, c1.b_dgrad, g_sum, cd.b_dgrad, g_x, mk); });
+          } else
           for (int ph = 0; ph < 2 && !rc; ++ph)
             for (int pw = 0; pw < 2 && !rc; ++pw) {
               static char l2[16];
@@ -877,7 +979,7 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out, cudaStream_t tune_s
       const uint32_t box[4] = {64, 16, 11, 1};
       memset(&t.maps, 0, sizeof t.maps);
       rc = make_tmap_bf16(&t.maps.a[0], m->g_c1, 4, dims, strides, box);
-      t.maps.out = t.maps.a[0];   // unused by the scatter epilogue; keeps the prefetch well-defined
+      t.maps.out[0] = t.maps.a[0];   // unused by the scatter epilogue; keeps the prefetch well-defined
       const uint64_t bd[2] = {64, 256};
       const uint64_t bs[1] = {128};
       const uint32_t bb[2] = {64, 64};

@@ -106,27 +106,40 @@ constexpr int kFcSplit = 4;
 __global__ void __launch_bounds__(256)
 fc_nt_splitk_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ part,
                     int m_total, int n_total, int k_total, int k_chunk) {
-  __shared__ __align__(16) float As[16][68];
-  __shared__ __align__(16) float Bs[16][68];
+  constexpr int KC = 32;                                 // K elements staged per iteration
+  __shared__ __align__(16) float As[KC][68];
+  __shared__ __align__(16) float Bs[KC][68];
   const int tid = threadIdx.x;
   const int tx = tid & 15, ty = tid >> 4;
   const int m0 = blockIdx.x * 64, n0 = blockIdx.y * 64;
   const int kbeg = blockIdx.z * k_chunk;
   const int kend = min(k_total, kbeg + k_chunk);
-  const int lr = tid >> 2, lk = (tid & 3) * 4;          // this thread's load: row lr, k offset lk (one float4)
-  float acc[4][4] = {};
-  for (int k0 = kbeg; k0 < kend; k0 += 16) {
-    float4 va = make_float4(0.f, 0.f, 0.f, 0.f), vb = va;
-    const int k = k0 + lk;
-    if (k < kend) {
-      if (m0 + lr < m_total) va = __ldg(reinterpret_cast<const float4*>(a + (long long)(m0 + lr) * k_total + k));
-      if (n0 + lr < n_total) vb = __ldg(reinterpret_cast<const float4*>(b + (long long)(n0 + lr) * k_total + k));
-    }
-    As[lk][lr] = va.x; As[lk + 1][lr] = va.y; As[lk + 2][lr] = va.z; As[lk + 3][lr] = va.w;
-    Bs[lk][lr] = vb.x; Bs[lk + 1][lr] = vb.y; Bs[lk + 2][lr] = vb.z; Bs[lk + 3][lr] = vb.w;
-    __syncthreads();
+  const int lr = tid >> 2, lk = (tid & 3) * 8;          // this thread's loads: row lr, k offsets lk .. lk+7
+  const bool a_ok = m0 + lr < m_total, b_ok = n0 + lr < n_total;
+  const float* ap = a + (long long)(m0 + lr) * k_total;
+  const float* bp = b + (long long)(n0 + lr) * k_total;
+  float4 va[2], vb[2];
+  auto fetch = [&](int k0) {
 #pragma unroll
-    for (int kk = 0; kk < 16; ++kk) {
+    for (int h = 0; h < 2; ++h) {
+      const int k = k0 + lk + 4 * h;
+      va[h] = (a_ok && k < kend) ? __ldg(reinterpret_cast<const float4*>(ap + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      vb[h] = (b_ok && k < kend) ? __ldg(reinterpret_cast<const float4*>(bp + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  };
+  float acc[4][4] = {};
+  fetch(kbeg);
+  for (int k0 = kbeg; k0 < kend; k0 += KC) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int r = lk + 4 * h;
+      As[r][lr] = va[h].x; As[r + 1][lr] = va[h].y; As[r + 2][lr] = va[h].z; As[r + 3][lr] = va[h].w;
+      Bs[r][lr] = vb[h].x; Bs[r + 1][lr] = vb[h].y; Bs[r + 2][lr] = vb[h].z; Bs[r + 3][lr] = vb[h].w;
+    }
+    __syncthreads();
+    if (k0 + KC < kend) fetch(k0 + KC);                  // next slice in flight while this one is consumed
+#pragma unroll
+    for (int kk = 0; kk < KC; ++kk) {
       const float4 a4 = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
       const float4 b4 = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
       const float av[4] = {a4.x, a4.y, a4.z, a4.w}, bv[4] = {b4.x, b4.y, b4.z, b4.w};
@@ -169,7 +182,7 @@ int launch_fc_nt(const float* a, const float* b, const float* bias, float* out, 
                  int k, cudaStream_t stream) {
   if (m == 0) return ADVB200_OK;
   ADV_CHECK_ARG(k % 4 == 0 && partial, "fc: K must be a multiple of 4 and the split-K scratch non-null");
-  const int k_chunk = (((k + kFcSplit - 1) / kFcSplit) + 15) / 16 * 16;
+  const int k_chunk = (((k + kFcSplit - 1) / kFcSplit) + 31) / 32 * 32;
   dim3 grid((unsigned)((m + 63) / 64), (unsigned)((n + 63) / 64), kFcSplit);
   fc_nt_splitk_kernel<<<grid, 256, 0, stream>>>(a, b, partial, m, n, k, k_chunk);
   ADV_LAUNCHED();

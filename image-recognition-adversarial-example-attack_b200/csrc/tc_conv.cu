@@ -277,7 +277,7 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint4 v) {
 }
 
 // ---------------------------------------------------------------- the kernel
-struct TileCoord { int w0, h0, n0, c0; };
+struct TileCoord { int w0, h0, n0, c0, cls; };
 // pair mode: `tile` indexes (pair of consecutive pixel tiles, column block); CTA `rank` takes pixel tile
 // 2*pair + rank (an odd tile count leaves the last rank-1 tile out of bounds in n: loads zero-fill,
 // stores clip)
@@ -288,6 +288,11 @@ __device__ __forceinline__ TileCoord tile_coord(const ConvGemmParams& p, int til
   // divisions by launch constants through host-made reciprocals: q = (n * ceil(2^40 / d)) >> 40 (n < 2^20)
   int q = (int)(((unsigned long long)(unsigned)tile * p.magic_c) >> 40);
   const int tc = tile - q * p.tiles_c; tile = q;
+  t.cls = 0;
+  if (p.nclass > 1) {
+    t.cls = (int)(((unsigned long long)(unsigned)tile * p.magic_cls) >> 40);
+    tile -= t.cls * p.units_per_class;
+  }
   if (kPair) tile = 2 * tile + rank;
   q = (int)(((unsigned long long)(unsigned)tile * p.magic_w) >> 40);
   const int tw = tile - q * p.tiles_w; tile = q;
@@ -334,10 +339,10 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
 
   if (warp == 0 && lane == 0) {
     if (smem_u32(smem) & 1023u) __trap();                   // swizzled tiles need 1024-byte alignment
-    for (int i = 0; i < 4; ++i) prefetch_tmap(&maps.a[i]);
+    for (int i = 0; i < 5; ++i) prefetch_tmap(&maps.a[i]);
     prefetch_tmap(&maps.b);
     if (p.has_b2) prefetch_tmap(&maps.b2);
-    prefetch_tmap(&maps.out);
+    for (int i = 0; i < 4; ++i) prefetch_tmap(&maps.out[i]);
     if (p.has_add) prefetch_tmap(&maps.add);
     for (int s = 0; s < kMaxStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], kPair ? 16 : 8); }
@@ -359,8 +364,7 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
       asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
   }
-  const int pixel_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
-  const int total_tiles = (kPair ? (pixel_tiles + 1) / 2 : pixel_tiles) * p.tiles_c;
+  const int total_tiles = p.total_tiles;
   if (warp >= kEpiWarp0 && p.bias && BN != 16) {
     // folded-BN shift of the first tile's column block (accumulator 0's copy)
     const int i = threadIdx.x - kEpiWarp0 * 32;
@@ -433,7 +437,9 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
       pdl_wait();
       for (int tile = tile0; tile < total_tiles; tile += tile_step) {
         const TileCoord tc = tile_coord<kPair>(p, tile, BN, rank);
-        for (int tap = 0; tap < p.ntaps; ++tap) {
+        const int tap_lo = p.nclass > 1 ? p.cls_tap0[tc.cls] : 0;
+        const int tap_hi = p.nclass > 1 ? tap_lo + p.cls_ntaps[tc.cls] : p.ntaps;
+        for (int tap = tap_lo; tap < tap_hi; ++tap) {
           const CUtensorMap* ma = &maps.a[p.tap_map[tap]];
           const CUtensorMap* mb = p.tap_bmap[tap] ? &maps.b2 : &maps.b;
           const int cw = tc.w0 + p.tap_dw[tap], ch = tc.h0 + p.tap_dh[tap];
@@ -532,7 +538,8 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           __syncwarp();
           if (++stage == nstages) { stage = 0; phase ^= 1; }
         } else {
-          for (int ks = 0; ks < ksteps; ++ks) {
+          const int ksteps_t = p.nclass > 1 ? p.cls_ksteps[tile_coord<kPair>(p, tile, BN, 0).cls] : ksteps;
+          for (int ks = 0; ks < ksteps_t; ++ks) {
             mbar_wait(&full_bar[stage], phase);
             tc_fence_after();
             if (elect_one()) {
@@ -704,8 +711,9 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
         // output pixel of this thread's row (bit-mask addressing) and whether it exists
         const int tw = tc.w0 + wi, th = tc.h0 + hi, tn = tc.n0 + ni;
         const bool valid = (tw < p.out_w) && (th < p.out_h) && (tn < p.out_n);
-        const long long pixel = ((long long)tn * p.full_h + (th * p.pix_sub + p.pix_ph)) * p.full_w +
-                                (tw * p.pix_sub + p.pix_pw);
+        const int pix_ph = p.nclass > 1 ? p.cls_ph[tc.cls] : p.pix_ph, pix_pw = p.nclass > 1 ? p.cls_pw[tc.cls] : p.pix_pw;
+        const long long pixel = ((long long)tn * p.full_h + (th * p.pix_sub + pix_ph)) * p.full_w +
+                                (tw * p.pix_sub + pix_pw);
         const long long mword0 = ((long long)(tc.c0 >> 6) * p.mask_pixels + pixel) * 2 + half;
         // folded-BN shift of the NEXT tile goes to the other accumulator's copy
         if (has_bias && etid < BN && tile + tile_step < total_tiles)
@@ -766,7 +774,7 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
             // direct mode: this thread's 32 channels (64 contiguous bytes of its pixel) go straight to global
             // memory — no staging tile, no barrier, and the smem goes to the operand ring instead
             if (valid) {
-              uint4* gp = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + pixel * p.cout + tc.c0 + 64 * j + half * 32);
+              uint4* gp = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + pixel * p.cout + tc.c0 + 64 * j + half * 32);
 #pragma unroll
               for (int i = 0; i < 4; ++i) gp[i] = o[i];
             }
@@ -777,7 +785,7 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           fence_async_smem();          // generic-proxy smem writes -> visible to the TMA store
           epi_bar();
           if (leader) {
-            tma_store_4d(&maps.out, out_smem + oslot * kSubTileBytes, tc.c0 + 64 * j, tc.w0, tc.h0, tc.n0);
+            tma_store_4d(&maps.out[tc.cls], out_smem + oslot * kSubTileBytes, tc.c0 + 64 * j, tc.w0, tc.h0, tc.n0);
             bulk_commit();
             // n staging slots: before the next barrier all but the newest (n - 2) stores must have
             // finished reading their slot
@@ -812,7 +820,9 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
     configured = true;
   }
   const long long pixel_tiles = (long long)p.tiles_w * p.tiles_h * p.tiles_n;
-  const long long total = (kPair ? (pixel_tiles + 1) / 2 : pixel_tiles) * p.tiles_c;
+  const int nclass = p.nclass > 1 ? p.nclass : 1;
+  p.units_per_class = (int)(kPair ? (pixel_tiles + 1) / 2 : pixel_tiles);
+  const long long total = (long long)p.units_per_class * nclass * p.tiles_c;
   if (total <= 0) return ADVB200_OK;
   p.total_tiles = (int)total;
   if (p.step_w == 0) p.step_w = p.bw;
@@ -821,12 +831,24 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
   ADV_CHECK_ARG(total < (1ll << 20) && pixel_tiles * 2 < (1ll << 20), "conv_gemm: too many tiles for the fast division");
   ADV_CHECK_ARG((p.bw & (p.bw - 1)) == 0 && (p.bh & (p.bh - 1)) == 0, "conv_gemm: tile box must be a power of two");
   p.magic_c = magic(p.tiles_c); p.magic_w = magic(p.tiles_w); p.magic_h = magic(p.tiles_h);
+  p.magic_cls = magic(p.units_per_class);
   p.bw_shift = ilog2(p.bw); p.bh_shift = ilog2(p.bh);
   p.ring_off = 0;
   p.stage_bytes = C::kStageBytes;
   if (p.ksteps == 0) {                       // plain conv: every tap spans all kblocks of one weight matrix
     for (int t = 0; t < p.ntaps; ++t) { p.tap_kb[t] = p.kblocks; p.tap_bmap[t] = 0; }
     p.ksteps = p.ntaps * p.kblocks;
+  }
+  if (nclass > 1) {
+    ADV_CHECK_ARG(!p.halo && nclass <= 4, "conv_gemm: multi-class launches are generic-mode, at most 4 classes");
+    p.bres_off = 1;                          // classes have different weights: no resident-weight mode
+    p.ksteps = 0;
+    for (int c = 0; c < nclass; ++c) {
+      int ks = 0;
+      for (int t = p.cls_tap0[c]; t < p.cls_tap0[c] + p.cls_ntaps[c]; ++t) ks += p.tap_kb[t];
+      p.cls_ksteps[c] = ks;
+      if (ks > p.ksteps) p.ksteps = ks;
+    }
   }
   if (p.halo) {
     ADV_CHECK_ARG(p.kblocks == 1 && p.tiles_c == 1 && !p.has_add && !kPair,
