@@ -194,15 +194,20 @@ def main():
     adist.allreduce_counters(counters)
 
     # ---------------- end to end through the public API from pinned host memory ----------------
+    # every step: H2D of that step's pinned input batch, the attack, D2H of its result.  The public host-buffer
+    # front end (advb200.pipeline.HostBatchPipeline) overlaps the copies of neighbouring steps with the attack.
+    import itertools
+    from advb200.pipeline import HostBatchPipeline
     xh = x.cpu().pin_memory()
-    outh = torch.empty_like(xh).pin_memory()
-    for _ in range(2):
-        outh.copy_(attack(xh.to(dev, non_blocking=True)), non_blocking=True)
+    outs = [torch.empty_like(xh).pin_memory() for _ in range(2)]
+    pipe = HostBatchPipeline(attack, dev)
+    for _ in pipe.run([xh, xh], itertools.cycle(outs)):
+        pass
     adist.barrier(); torch.cuda.synchronize()
     e0.record()
-    for _ in range(args.steps):
-        xd = xh.to(dev, non_blocking=True)
-        outh.copy_(attack(xd), non_blocking=True)
+    for _ in pipe.run((xh for _ in range(args.steps)), itertools.cycle(outs)):
+        pass
+    torch.cuda.current_stream().wait_stream(pipe.d2h)
     e1.record()
     torch.cuda.synchronize(); adist.barrier()
     ms_e2e = adist.max_over_ranks(e0.elapsed_time(e1), device=dev)
@@ -229,6 +234,11 @@ def main():
 
     if rank != 0:
         return
+    # DRAM traffic of the conv launches from the committed ncu --set full capture (per launch, like `achieved`)
+    traffic = None
+    tfile = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_conv_traffic.json")
+    if os.path.isfile(tfile) and n == BATCH:
+        traffic = json.load(open(tfile)).get("dram_bytes_per_launch")
     cpu = None
     if not args.no_cpu_baseline and world == 1:
         threads = host_threads()
@@ -247,7 +257,7 @@ def main():
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                     "frac": achieved / peak, "traffic": None,
+                     "frac": achieved / peak, "traffic": traffic,
                      "kernel": "conv_gemm_kernel<BN> (tcgen05 implicit-GEMM conv, all fwd+dgrad launches)",
                      "peak_source": f"{peak_kind} bf16_tflops_sustained (kernel timed inside a long step)",
                      "launches_per_attack": int(conv_n.value), "conv_ms_per_attack": conv_ms.value,

@@ -9,3 +9,4 @@ from .defenses import (  # noqa: F401
     is_adversarial_by_feature, run_attack, COUNTER_KEYS,
 )
 from .model import NativeResNet50, get_default_precision, native_model, set_default_precision  # noqa: F401
+from .pipeline import HostBatchPipeline  # noqa: F401

@@ -379,3 +379,23 @@ def test_pgd10_batch256_bf16_properties(advb200_mod, native, dev):
     g_shard = nm.input_grad(xs, mean, std, y[lo:hi], inv_n_global=1 / 256)["grad"]
     g_full = nm.input_grad((x + noise).clamp(0, 1), mean, std, y, inv_n_global=1 / 256)["grad"][lo:hi]
     assert torch.equal(g_shard, g_full)
+
+
+@pytest.mark.gpu
+def test_host_batch_pipeline_equals_direct_calls(advb200_mod, native, dev):
+    """The overlapped host-buffer front end returns exactly what direct calls on device tensors return."""
+    import functools
+    from oracle import weights
+    nm = native["bf16"]
+    mean, std = weights.mean_std()
+    batches = [weights.synthetic_images(3, seed=50 + i).pin_memory() for i in range(4)]
+    y = torch.zeros(3, dtype=torch.int64, device=dev)
+    fn = functools.partial(advb200_mod.fgsm_attack, nm, y_true=y, eps=8 / 255, mean=mean, std=std)
+    pipe = advb200_mod.HostBatchPipeline(fn, dev)
+    got = [r.clone() for r in pipe.run(batches)]
+    assert len(got) == 4
+    for b, r in zip(batches, got):
+        want = fn(b.to(dev)).cpu()
+        assert torch.equal(r, want)
+    with pytest.raises(ValueError):
+        list(pipe.run([torch.zeros(3, 3, 224, 224)]))

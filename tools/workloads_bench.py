@@ -1,0 +1,100 @@
+"""Secondary measurements of SURVEY section 8(d), one JSON object on stdout:
+  * HBM-bound update / defense kernels at N=256: achieved GB/s against MEASURED_PEAKS hbm_gbs
+    (algorithmic bytes per element from DESIGN.md section 4.2);
+  * config 3: CW-L2 (100 steps, c=1, lr=0.01), untargeted and targeted(805), batch 256, images/s;
+  * config 5 (per GPU share): defense sweep FGSM+PGD x eps {4,8}/255 through the batched evaluator.
+Usage: python tools/workloads_bench.py [batch] > gpurun_out/workloads.json"""
+import ctypes
+import json
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT / "image-recognition-adversarial-example-attack_b200"))
+sys.path.insert(0, str(ROOT))
+import torch  # noqa: E402
+import advb200  # noqa: E402
+from advb200 import _lib, defenses  # noqa: E402
+from oracle import weights  # noqa: E402
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 256
+dev = torch.device("cuda:0")
+torch.cuda.set_device(dev)
+peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()) if (ROOT / "MEASURED_PEAKS.json").is_file() else {}
+PBW = float(peaks.get("hbm_gbs", 6650.0))
+lib = _lib.load()
+
+
+def timed(fn, reps=20, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+out = {"batch": n, "hbm_peak_gbs": PBW, "kernels": {}}
+x = weights.synthetic_images(min(n, 64)).to(dev)
+x = x.repeat((n + x.shape[0] - 1) // x.shape[0], 1, 1, 1)[:n].contiguous()
+elems = x.numel()
+g = torch.randn_like(x)
+x0 = x.clone()
+xa = x.clone()
+
+
+def rec(name, ms, bytes_per_elem):
+    gbs = bytes_per_elem * elems / (ms * 1e-3) / 1e9
+    out["kernels"][name] = {"ms": ms, "bytes_per_elem": bytes_per_elem, "gbs": gbs, "frac_of_hbm_peak": gbs / PBW}
+
+
+# the three rotating input sets keep every launch's working set (> 450 MB) out of the 126 MB L2
+rec("linf_step(project)", timed(lambda: advb200.attack._linf_step(xa, x0, g, 2 / 255, 8 / 255, True)), 16)
+rec("linf_step(fgsm)", timed(lambda: advb200.attack._linf_step(xa, x0, g, 8 / 255, 8 / 255, False)), 12)
+rec("smooth3x3", timed(lambda: defenses._defense_smoothing(x)), 8)
+rec("quantize16", timed(lambda: defenses._defense_quantization(x)), 8)
+rec("defend_input", timed(lambda: defenses.defend_input(x)), 8)
+
+model = weights.seeded_resnet50(0).to(dev)
+mean, std = weights.mean_std()
+nm = advb200.NativeResNet50(model, precision="bf16")
+y = nm.forward(x, mean, std, want_logits=False, want_preds=True)["preds"]
+
+# CW step kernel alone (32 B/elem): time a short attack with and without ... simpler: whole CW attack rates
+cw = {}
+for name, kw in (("untargeted", {}), ("targeted_805", {"targeted": True, "y_target": torch.full_like(y, 805)})):
+    steps = 100
+    advb200.cw_l2_attack(nm, x, y, mean=mean, std=std, c=1.0, lr=0.01, steps=3, **kw)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    res, l2 = advb200.cw_l2_attack(nm, x, y, mean=mean, std=std, c=1.0, lr=0.01, steps=steps, return_l2=True, **kw)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    ok = res.success
+    cw[name] = {"steps": steps, "ms": ms, "images_per_s": n / (ms * 1e-3), "success_rate": float(ok.float().mean()),
+                "mean_l2_sq_of_successes": float(l2[ok].mean()) if bool(ok.any()) else None}
+out["cw_l2_batch%d" % n] = cw
+
+# defense sweep: threshold calibrated on the first 100 images (quantile 0.95), then 2 attacks x 2 eps
+scores = nm.forward(x[:100], mean, std, want_logits=False, want_score=True)["score"]
+thr = defenses.calibrate_threshold_from_scores(scores, 0.95)
+sweep = {"threshold": thr, "rows": []}
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+torch.cuda.synchronize()
+e0.record()
+for attack in ("fgsm", "pgd"):
+    for eps in (4 / 255, 8 / 255):
+        c = defenses.evaluate_defenses_batched(nm, x, y, mean, std, attack, eps, 2 / 255, 10, 1.0, 0.0, 100, 0.01, thr)
+        sweep["rows"].append({"attack": attack, "eps": eps, "counters": [int(v) for v in c.cpu()]})
+e1.record()
+torch.cuda.synchronize()
+sweep["ms_total"] = e0.elapsed_time(e1)
+sweep["images_per_s_per_config"] = 4 * n / (sweep["ms_total"] * 1e-3)
+out["defense_sweep_batch%d" % n] = sweep
+print(json.dumps(out, indent=1))
