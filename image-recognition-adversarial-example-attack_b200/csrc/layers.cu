@@ -18,30 +18,63 @@ template <> __device__ __forceinline__ float from_f<float>(float v) { return v; 
 template <> __device__ __forceinline__ bf16 from_f<bf16>(float v) { return __float2bfloat16_rn(v); }
 
 // ---------------------------------------------------------------- input preparation
-// one block per output row (n, hp): the two source image rows (3 channels each) are read
-// coalesced into shared memory, normalised once, then scattered into the 64-channel hcol pixels
+// Stages the normalised image rows behind kRowsPer16 stem-operand rows hp0.. of image n in shared memory:
+// src[(r*2+ph)*3+c][col+4] = norm(x)[c, 2(hp0+r-2)+ph, col], zero outside the image (cols -4..227).
+constexpr int kRowsPer16 = 5;
+__device__ __forceinline__ void stage_norm_rows(const float* __restrict__ x, const float* __restrict__ mean3,
+                                                const float* __restrict__ std3, int n, int hp0, float* src0) {
+  // all of this thread's 16-byte image loads are issued before the first one is used (the kernel is latency-bound
+  // otherwise): kSegs (row, ph, c) image rows of 56 float4 each
+  constexpr int kSegs = kRowsPer16 * 2 * 3, kLoads = (kSegs * 56 + kT - 1) / kT;
+  float4 v[kLoads];
+#pragma unroll
+  for (int k = 0; k < kLoads; ++k) {
+    const int idx = threadIdx.x + k * kT;
+    v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (idx < kSegs * 56) {
+      const int seg = idx / 56, c4 = idx - seg * 56;
+      const int c = seg % 3, ph = (seg / 3) & 1, r = seg / 6;
+      const int row = 2 * (hp0 + r - 2) + ph;
+      if (row >= 0 && row < 224)
+        v[k] = __ldg(reinterpret_cast<const float4*>(x + (((long long)n * 3 + c) * 224 + row) * 224) + c4);
+    }
+  }
+  if (threadIdx.x < kSegs * 8) {                     // zero the 4 + 4 pad columns of every row
+    const int seg = threadIdx.x >> 3, j = threadIdx.x & 7;
+    src0[seg * 232 + (j < 4 ? j : 224 + j)] = 0.f;
+  }
+#pragma unroll
+  for (int k = 0; k < kLoads; ++k) {
+    const int idx = threadIdx.x + k * kT;
+    if (idx < kSegs * 56) {
+      const int seg = idx / 56, c4 = idx - seg * 56;
+      const int c = seg % 3;
+      const int row = 2 * (hp0 + seg / 6 - 2) + ((seg / 3) & 1);
+      float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (row >= 0 && row < 224) {
+        const float mu = __ldg(mean3 + c), sd = __ldg(std3 + c);
+        o.x = __fdiv_rn(__fsub_rn(v[k].x, mu), sd); o.y = __fdiv_rn(__fsub_rn(v[k].y, mu), sd);   // attack.py:17
+        o.z = __fdiv_rn(__fsub_rn(v[k].z, mu), sd); o.w = __fdiv_rn(__fsub_rn(v[k].w, mu), sd);
+      }
+      *reinterpret_cast<float4*>(&src0[seg * 232 + 4 + c4 * 4]) = o;
+    }
+  }
+}
+
+// one block per kRowsPer16 operand rows (n, hp0..): the source image rows are staged normalised in shared memory
+// (all loads of a thread in flight at once), then scattered into the 64-channel hcol pixels
 __global__ void __launch_bounds__(kT)
 prep_hcol_kernel(const float* __restrict__ x, const float* __restrict__ mean3, const float* __restrict__ std3,
                  bf16* __restrict__ out) {
-  __shared__ float src[2][3][224 + 8];     // [ph][c][col + 4]: cols -4..227 so the halo reads stay in range
-  const int hp = blockIdx.x % 115;
-  const int n = blockIdx.x / 115;
-  for (int i = threadIdx.x; i < 2 * 3 * 232; i += kT) {
-    const int col = i % 232 - 4;
-    const int c = (i / 232) % 3;
-    const int ph = i / (232 * 3);
-    const int row = 2 * (hp - 2) + ph;
-    float v = 0.f;
-    if (row >= 0 && row < 224 && col >= 0 && col < 224) {
-      const float px = __ldg(x + (((long long)n * 3 + c) * 224 + row) * 224 + col);
-      v = __fdiv_rn(__fsub_rn(px, __ldg(mean3 + c)), __ldg(std3 + c));   // attack.py:17
-    }
-    src[ph][c][col + 4] = v;
-  }
+  __shared__ __align__(16) float src[kRowsPer16][2][3][232];     // [row][ph][c][col + 4]: cols -4..227
+  const int hp0 = (blockIdx.x % (115 / kRowsPer16)) * kRowsPer16;
+  const int n = blockIdx.x / (115 / kRowsPer16);
+  stage_norm_rows(x, mean3, std3, n, hp0, &src[0][0][0][0]);
   __syncthreads();
-  bf16* orow = out + ((long long)n * 115 + hp) * 112 * 64;
-  for (int t = threadIdx.x; t < 112 * 8; t += kT) {
-    const int j8 = t & 7, wo = t >> 3;
+  bf16* obase = out + ((long long)n * 115 + hp0) * 112 * 64;
+  for (int t = threadIdx.x; t < kRowsPer16 * 112 * 8; t += kT) {
+    const int r = t / (112 * 8), tt = t - r * (112 * 8);
+    const int j8 = tt & 7, wo = tt >> 3;
     const int u = j8 >> 1, q0 = (j8 & 1) * 8;
     __align__(16) bf16 v[8];
 #pragma unroll
@@ -50,11 +83,42 @@ prep_hcol_kernel(const float* __restrict__ x, const float* __restrict__ mean3, c
       float val = 0.f;
       if (q < 12) {
         const int c = q % 3, pw = (q / 3) & 1, ph = q / 6;
-        val = src[ph][c][2 * (wo - 2 + u) + pw + 4];
+        val = src[r][ph][c][2 * (wo - 2 + u) + pw + 4];
       }
       v[i] = __float2bfloat16_rn(val);
     }
-    *reinterpret_cast<uint4*>(orow + (long long)t * 8) = *reinterpret_cast<const uint4*>(v);
+    *reinterpret_cast<uint4*>(obase + (long long)t * 8) = *reinterpret_cast<const uint4*>(v);
+  }
+}
+
+// Compact stem operand: [N, 115, 115, 16] bf16, pixel (hp, wp) = the 2x2x3 space-to-depth patch of image rows
+// 2(hp-2)+{0,1}, columns 2(wp-2)+{0,1} (12 of 16 slots used), normalised, zero outside the image.  The conv1
+// kernel reads 32-byte rows (SWIZZLE_32B) and takes both the vertical and the horizontal taps as row shifts.
+// One block = kRowsPer16 operand rows of one image.
+__global__ void __launch_bounds__(kT)
+prep_hcol16_kernel(const float* __restrict__ x, const float* __restrict__ mean3, const float* __restrict__ std3,
+                   bf16* __restrict__ out) {
+  __shared__ __align__(16) float src[kRowsPer16][2][3][232];     // [row][ph][c][col + 4]: cols -4..227
+  const int hp0 = (blockIdx.x % (115 / kRowsPer16)) * kRowsPer16;
+  const int n = blockIdx.x / (115 / kRowsPer16);
+  stage_norm_rows(x, mean3, std3, n, hp0, &src[0][0][0][0]);
+  __syncthreads();
+  bf16* obase = out + ((long long)n * 115 + hp0) * 115 * 16;
+  for (int t = threadIdx.x; t < kRowsPer16 * 230; t += kT) {
+    const int r = t / 230, j = t - r * 230;
+    const int wp = j >> 1, q0 = (j & 1) * 8;
+    __align__(16) bf16 v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int q = q0 + i;
+      float val = 0.f;
+      if (q < 12) {
+        const int c = q % 3, pw = (q / 3) & 1, ph = q / 6;
+        val = src[r][ph][c][2 * (wp - 2) + pw + 4];
+      }
+      v[i] = __float2bfloat16_rn(val);
+    }
+    *reinterpret_cast<uint4*>(obase + (long long)t * 8) = *reinterpret_cast<const uint4*>(v);
   }
 }
 
@@ -494,7 +558,7 @@ __global__ void pack_kernel(const float* __restrict__ w, const float* __restrict
 }
 
 __global__ void pack_conv1_kernel(const float* __restrict__ w, const float* __restrict__ scale,
-                                  bf16* __restrict__ fwd, bf16* __restrict__ dgrad) {
+                                  bf16* __restrict__ fwd, bf16* __restrict__ dgrad, bf16* __restrict__ fwd16) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;    // (tt, u, q, co) : 4*4*16*64
   if (t >= 4 * 4 * 16 * 64) return;
   const int co = t & 63, q = (t >> 6) & 15, u = (t >> 10) & 3, tt = t >> 12;
@@ -506,6 +570,7 @@ __global__ void pack_conv1_kernel(const float* __restrict__ w, const float* __re
   }
   const bf16 b = __float2bfloat16_rn(v);
   fwd[(tt * 64 + co) * 64 + u * 16 + q] = b;
+  if (fwd16) fwd16[((tt * 4 + u) * 64 + co) * 16 + q] = b;       // 32-byte rows: one (vertical, horizontal) tap each
   // input gradient: vertical taps (tt) stay in the K loop, horizontal taps (u) go to the N dimension:
   // row tt*64 + qi*4 + u, qi = slot of q in the store-friendly order {0,3,1,4,2,5,6,9 | 7,10,8,11}
   // (pairs (pw=0, pw=1) of the same (c, ph) adjacent, so the epilogue writes 8-byte pixel pairs)
@@ -562,10 +627,17 @@ int launch_pack_mask_bits(const bf16* act, uint32_t* bits, long long pixels, int
 
 int launch_prep_hcol(const float* x, const float* mean3, const float* std3, bf16* out, int n, cudaStream_t st) {
   if (!n) return ADVB200_OK;
-  prep_hcol_kernel<<<n * 115, kT, 0, st>>>(x, mean3, std3, out);
+  prep_hcol_kernel<<<n * (115 / kRowsPer16), kT, 0, st>>>(x, mean3, std3, out);
   ADV_LAUNCHED();
   return ADVB200_OK;
 }
+int launch_prep_hcol16(const float* x, const float* mean3, const float* std3, bf16* out, int n, cudaStream_t st) {
+  if (!n) return ADVB200_OK;
+  prep_hcol16_kernel<<<n * (115 / kRowsPer16), kT, 0, st>>>(x, mean3, std3, out);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+
 int launch_prep_nhwc(const float* x, const float* mean3, const float* std3, float* out, int n, int h, int w,
                      cudaStream_t st) {
   const long long total = (long long)n * h * w * 3;
@@ -692,8 +764,8 @@ int launch_pack_bf16(const float* w, const float* scale, bf16* fwd, bf16* dgrad,
   ADV_LAUNCHED();
   return ADVB200_OK;
 }
-int launch_pack_conv1_bf16(const float* w, const float* scale, bf16* fwd, bf16* dgrad, cudaStream_t st) {
-  pack_conv1_kernel<<<(4 * 4 * 16 * 64 + 255) / 256, 256, 0, st>>>(w, scale, fwd, dgrad);
+int launch_pack_conv1_bf16(const float* w, const float* scale, bf16* fwd, bf16* dgrad, bf16* fwd16, cudaStream_t st) {
+  pack_conv1_kernel<<<(4 * 4 * 16 * 64 + 255) / 256, 256, 0, st>>>(w, scale, fwd, dgrad, fwd16);
   ADV_LAUNCHED();
   return ADVB200_OK;
 }

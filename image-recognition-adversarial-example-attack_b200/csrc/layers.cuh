@@ -12,6 +12,8 @@ typedef __nv_bfloat16 bf16;
 //            holds norm(x)[c, 2*(hp-2)+ph, 2*(wo-2+u)+pw] (zero outside the image / q>=12)
 int launch_prep_hcol(const float* x, const float* mean3, const float* std3, bf16* out, int n,
                      cudaStream_t st);
+// compact stem operand [N,115,115,16] (32-byte rows; conv1 takes all 16 taps as row shifts)
+int launch_prep_hcol16(const float* x, const float* mean3, const float* std3, bf16* out, int n, cudaStream_t st);
 // fp32 mode: NHWC [N,224,224,3]
 int launch_prep_nhwc(const float* x, const float* mean3, const float* std3, float* out, int n, int h, int w,
                      cudaStream_t st);
@@ -59,7 +61,7 @@ int launch_pack_bf16(const float* w, const float* scale, bf16* fwd, bf16* dgrad,
                      cudaStream_t st);
 // conv1 (7x7/2, 3->64) in its space-to-depth form:
 //   fwd  [t*64 + co][u*16+q]      dgrad [t*64 + slot(q)*4 + u][co]    (t,u in 0..3; see launch_prep_hcol)
-int launch_pack_conv1_bf16(const float* w, const float* scale, bf16* fwd, bf16* dgrad, cudaStream_t st);
+int launch_pack_conv1_bf16(const float* w, const float* scale, bf16* fwd, bf16* dgrad, bf16* fwd16, cudaStream_t st);
 // fc: transpose [classes, feat] -> [feat, classes]
 int launch_transpose_f32(const float* in, float* out, int rows, int cols, cudaStream_t st);
 

@@ -206,13 +206,13 @@ __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepc
 // K-major, 128B-swizzled operand tile: rows of 128 bytes, 8-row atoms of 1024 bytes.
 // sbo_bytes: distance between consecutive 8-row groups (1024 for a dense tile; the halo-mode A
 // operand uses the halo box width * 128, and start addresses shifted by whole rows).
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t sbo_bytes = 1024) {
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t sbo_bytes = 1024, uint32_t swizzle_code = 2) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);   // start address, 16-byte units
   d |= (uint64_t)1 << 16;                        // leading byte offset (unused for swizzled K-major)
   d |= (uint64_t)(sbo_bytes >> 4) << 32;         // stride byte offset between 8-row groups
   d |= (uint64_t)1 << 46;                        // descriptor version (Blackwell)
-  d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
+  d |= (uint64_t)swizzle_code << 61;             // 2 = SWIZZLE_128B, 6 = SWIZZLE_32B
   return d;
 }
 
@@ -406,13 +406,14 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
       pdl_launch_dependents();
       if (p.halo) {
         // all taps' weights once, then one halo box of input pixels per tile
-        mbar_expect_tx(bres_bar, (uint32_t)(p.ntaps * BN * 128));
-        for (int tap = 0; tap < p.ntaps; ++tap) tma_load_2d(&maps.b, bres_bar, smem + tap * BN * 128, 0, p.tap_brow[tap]);
+        const int rb = p.row_bytes ? p.row_bytes : 128;
+        mbar_expect_tx(bres_bar, (uint32_t)(p.ntaps * BN * rb));
+        for (int tap = 0; tap < p.ntaps; ++tap) tma_load_2d(&maps.b, bres_bar, smem + tap * BN * rb, 0, p.tap_brow[tap]);
         pdl_wait();
         for (int tile = tile0; tile < total_tiles; tile += tile_step) {
           const TileCoord tc = tile_coord<kPair>(p, tile, BN, rank);
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_expect_tx(&full_bar[stage], (uint32_t)(p.halo_rows * 128));
+          mbar_expect_tx(&full_bar[stage], (uint32_t)(p.halo_rows * rb));
           tma_load_4d(&maps.a[0], &full_bar[stage], ring + stage * stage_bytes, 0, tc.w0 + p.halo_w0,
                       tc.h0 + p.halo_h0, tc.n0);
           if (++stage == nstages) { stage = 0; phase ^= 1; }
@@ -504,7 +505,11 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
       constexpr uint32_t idesc64 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(64 >> 3) << 17) |
                                    ((uint32_t)(kMmaM >> 4) << 24);
       const uint32_t desc_hi = (uint32_t)(make_smem_desc(0) >> 32);
-      const uint32_t a_hi_halo = (uint32_t)(make_smem_desc(0, (uint32_t)(p.sbo_rows * 128)) >> 32);
+      const uint32_t rb = p.row_bytes ? (uint32_t)p.row_bytes : 128u;      // halo-mode operand row pitch
+      const uint32_t sw_code = rb == 32 ? 6u : 2u;
+      const uint32_t a_hi_halo = (uint32_t)(make_smem_desc(0, (uint32_t)p.sbo_rows * rb, sw_code) >> 32);
+      const uint32_t b_hi_halo = (uint32_t)(make_smem_desc(0, 8u * rb, sw_code) >> 32);
+      const int kslices = (int)(rb >> 5);                                  // K = 16 slices per row
       const uint32_t ring_lo = ((smem_u32(ring) & 0x3FFFFu) >> 4) | (1u << 16);
       const uint32_t bres_lo = ((smem_u32(smem) & 0x3FFFFu) >> 4) | (1u << 16);
       const uint32_t ident_lo = ((smem_u32(ident_smem) & 0x3FFFFu) >> 4) | (1u << 16);
@@ -525,13 +530,21 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           tc_fence_after();
           if (elect_one()) {
             const uint32_t a_lo0 = ring_lo + (uint32_t)stage * stage_units;
-            for (int tap = 0; tap < ntaps; ++tap) {
-              const uint32_t a_lo = a_lo0 + (uint32_t)(p.tap_row[tap] * 8);
-              const uint32_t b_lo = bres_lo + (uint32_t)(tap * BN * 8);
+            if (kslices == 1) {
+              // 32-byte rows: one MMA per tap; unrolled so the single issuing thread batches the tap-offset loads
+#pragma unroll 8
+              for (int tap = 0; tap < ntaps; ++tap)
+                umma_bf16(d_tmem, ((uint64_t)a_hi_halo << 32) | (a_lo0 + (uint32_t)p.tap_row[tap] * 2u),
+                          ((uint64_t)b_hi_halo << 32) | (bres_lo + (uint32_t)(tap * BN) * 2u), idesc, tap != 0 ? 1u : 0u);
+            } else {
+              for (int tap = 0; tap < ntaps; ++tap) {
+                const uint32_t a_lo = a_lo0 + (uint32_t)(p.tap_row[tap] * 8);
+                const uint32_t b_lo = bres_lo + (uint32_t)(tap * BN * 8);
 #pragma unroll
-              for (int k = 0; k < kBlockK / 16; ++k)
-                umma_bf16(d_tmem, ((uint64_t)a_hi_halo << 32) | (a_lo + 2u * k), ((uint64_t)desc_hi << 32) | (b_lo + 2u * k),
-                          idesc, (tap | k) != 0 ? 1u : 0u);
+                for (int k = 0; k < kBlockK / 16; ++k)
+                  umma_bf16(d_tmem, ((uint64_t)a_hi_halo << 32) | (a_lo + 2u * k), ((uint64_t)b_hi_halo << 32) | (b_lo + 2u * k),
+                            idesc, (tap | k) != 0 ? 1u : 0u);
+              }
             }
             umma_commit(&empty_bar[stage]);
           }
@@ -853,8 +866,10 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
   if (p.halo) {
     ADV_CHECK_ARG(p.kblocks == 1 && p.tiles_c == 1 && !p.has_add && !kPair,
                   "conv_gemm: halo mode needs K = 64, one column block, one CTA per tile");
-    p.ring_off = (p.ntaps * BN * 128 + 1023) & ~1023;
-    p.stage_bytes = (p.halo_rows * 128 + 1023) & ~1023;
+    const int rb = p.row_bytes ? p.row_bytes : 128;
+    ADV_CHECK_ARG(rb == 128 || rb == 32, "conv_gemm: halo rows are 128 or 32 bytes");
+    p.ring_off = (p.ntaps * BN * rb + 1023) & ~1023;
+    p.stage_bytes = (p.halo_rows * rb + 1023) & ~1023;
   }
   static const char* force_slots = getenv("ADVB200_OUT_SLOTS");   // tuning knob
   p.out_slots = p.slots_req == 1 ? 0 : p.slots_req ? p.slots_req : force_slots ? atoi(force_slots) : (p.ksteps >= 8 ? 2 : 4);
@@ -911,7 +926,7 @@ int launch_conv_gemm(int bn_cols, int pair, const ConvGemmMaps& maps, ConvGemmPa
 }
 
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
-                   const uint64_t* strides_bytes, const uint32_t* box) {
+                   const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes) {
   static PFN_cuTensorMapEncodeTiled_v12000 encode = nullptr;
   static std::once_flag once;
   std::call_once(once, [] {
@@ -929,7 +944,8 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t*
   for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
   for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
   CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim,
-                      gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                      gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                      swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_128B,
                       CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     char buf[256];

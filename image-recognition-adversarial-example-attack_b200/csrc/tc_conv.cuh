@@ -50,6 +50,8 @@ struct ConvGemmParams {
   int halo_rows;                  // pixels in the halo box
   int sbo_rows;                   // rows between consecutive 8-row groups (= halo box width)
   int tap_row[kMaxTaps];
+  int row_bytes;                  // halo mode: bytes per operand row, 128 (64 channels, SWIZZLE_128B; 0 means 128) or
+                                  // 32 (16 channels, SWIZZLE_32B: the stem, one K = 16 MMA per tap)
   // output extent in tile coordinates (w, h, n) and channels
   int out_w, out_h, out_n, cout;
   void* out;                      // epi 0: bf16 NHWC output tensor (direct-store epilogue); epi 1/2: fp32 NCHW
@@ -97,6 +99,6 @@ int launch_conv_gemm(int bn_cols, int pair, const ConvGemmMaps& maps, ConvGemmPa
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda needed).
 // dims/strides innermost-first; strides in BYTES for dims 1..rank-1; bf16 elements; 128B swizzle.
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
-                   const uint64_t* strides_bytes, const uint32_t* box);
+                   const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes = 128);
 
 }  // namespace advb200
