@@ -199,6 +199,39 @@ class NativeResNet50:
         return out
 
 
+    # -- one fused attack step (bf16 mode) ----------------------------------------------------
+    def attack_step(self, x_adv, x_orig, mean, std, y_true, *, alpha, eps, inv_n_global=None):
+        """x_adv <- clamp(project(x_adv + alpha*sign(grad CE(x_adv)))) in place (attack.py:61-63; x_orig=None:
+        no projection, attack.py:33-34).  The update runs in the epilogue of the stem's input-gradient kernel,
+        so the gradient never goes through memory; bit-identical to input_grad + the linf step kernel."""
+        if self.precision != "bf16":
+            raise RuntimeError("attack_step is the bf16 fused path; use input_grad + the linf step in fp32 mode")
+        if x_adv.dtype != torch.float32 or not x_adv.is_contiguous() or not x_adv.is_cuda:
+            raise ValueError("x_adv must be a contiguous fp32 CUDA tensor (it is updated in place)")
+        self._check_x(x_adv)
+        mean, std = self._vec3(mean, x_adv.device), self._vec3(std, x_adv.device)
+        n = x_adv.shape[0]
+        y = y_true.detach().to(device=x_adv.device, dtype=torch.int64).contiguous()
+        if y.shape != (n,):
+            raise ValueError("labels must have shape [N]")
+        if x_orig is not None and (x_orig.shape != x_adv.shape or x_orig.dtype != torch.float32
+                                   or not x_orig.is_contiguous()):
+            raise ValueError("x_orig must match x_adv (contiguous fp32)")
+        if inv_n_global is None:
+            inv_n_global = 1.0 / n
+        with torch.cuda.device(x_adv.device):
+            for lo in range(0, n, self.max_chunk):
+                hi = min(n, lo + self.max_chunk)
+                _, ws, nbytes = self._workspace(hi - lo)
+                rc = self.lib.advb200_attack_step(self.handle, _lib.ptr(x_adv[lo:hi]),
+                                                  _lib.ptr(x_orig[lo:hi]) if x_orig is not None else None,
+                                                  _lib.ptr(mean), _lib.ptr(std), _lib.ptr(y[lo:hi]), hi - lo,
+                                                  float(inv_n_global), float(alpha), float(eps), None,
+                                                  c_void_p(ws), nbytes, _lib.stream_ptr())
+                _lib.check(rc, "advb200_attack_step")
+        return x_adv
+
+
 _CACHE: "weakref.WeakKeyDictionary[torch.nn.Module, dict]" = weakref.WeakKeyDictionary()
 
 

@@ -1243,11 +1243,39 @@ int advb200_forward(advb200_model* m, const float* x, const float* mean3, const 
   return rc;
 }
 
+static int input_grad_impl(advb200_model* m, const float* x, const float* mean3, const float* std3,
+                           const int64_t* y_cmp, int n, int loss_kind, float c, float kappa, float inv_n_global,
+                           float* logits_out, int64_t* preds_out, float* loss_out, uint8_t* success_out,
+                           float* grad_x_out, float* upd_x, const float* upd_x0, float upd_alpha, float upd_eps,
+                           void* workspace, int64_t workspace_bytes, void* stream);
+
 int advb200_input_grad(advb200_model* m, const float* x, const float* mean3, const float* std3,
                        const int64_t* y_cmp, int n, int loss_kind, float c, float kappa, float inv_n_global,
                        float* logits_out, int64_t* preds_out, float* loss_out, uint8_t* success_out,
                        float* grad_x_out, void* workspace, int64_t workspace_bytes, void* stream) {
-  ADV_CHECK_ARG(m && x && mean3 && std3 && y_cmp && grad_x_out, "input_grad: null argument");
+  ADV_CHECK_ARG(grad_x_out, "input_grad: null argument");
+  return input_grad_impl(m, x, mean3, std3, y_cmp, n, loss_kind, c, kappa, inv_n_global, logits_out, preds_out,
+                         loss_out, success_out, grad_x_out, nullptr, nullptr, 0.f, 0.f, workspace, workspace_bytes,
+                         stream);
+}
+
+int advb200_attack_step(advb200_model* m, float* x_adv_inout, const float* x_orig, const float* mean3,
+                        const float* std3, const int64_t* y_true, int n, float inv_n_global, float alpha, float eps,
+                        int64_t* preds_out, void* workspace, int64_t workspace_bytes, void* stream) {
+  ADV_CHECK_ARG(m && x_adv_inout, "attack_step: null argument");
+  if (m->precision != ADVB200_PREC_BF16)
+    return fail(ADVB200_ERR_UNSUPPORTED, "attack_step: fused update exists in bf16 mode only (use input_grad + linf_step)");
+  return input_grad_impl(m, x_adv_inout, mean3, std3, y_true, n, ADVB200_LOSS_CE_MEAN, 0.f, 0.f, inv_n_global, nullptr,
+                         preds_out, nullptr, nullptr, nullptr, x_adv_inout, x_orig, alpha, eps, workspace,
+                         workspace_bytes, stream);
+}
+
+static int input_grad_impl(advb200_model* m, const float* x, const float* mean3, const float* std3,
+                           const int64_t* y_cmp, int n, int loss_kind, float c, float kappa, float inv_n_global,
+                           float* logits_out, int64_t* preds_out, float* loss_out, uint8_t* success_out,
+                           float* grad_x_out, float* upd_x, const float* upd_x0, float upd_alpha, float upd_eps,
+                           void* workspace, int64_t workspace_bytes, void* stream) {
+  ADV_CHECK_ARG(m && x && mean3 && std3 && y_cmp && (grad_x_out || upd_x), "input_grad: null argument");
   ADV_CHECK_ARG(loss_kind >= ADVB200_LOSS_CE_MEAN && loss_kind <= ADVB200_LOSS_CW_TGT, "input_grad: bad loss kind");
   cudaStream_t st = as_stream(stream);
   int rc = ensure_plan(m, n, workspace, workspace_bytes, st);
@@ -1274,6 +1302,7 @@ int advb200_input_grad(advb200_model* m, const float* x, const float* mean3, con
     Op& op = m->ops_conv1_bwd[0];
     op.tc.p.out = grad_x_out;
     op.tc.p.std_dev = std3;
+    op.tc.p.upd_x = upd_x; op.tc.p.upd_x0 = upd_x0; op.tc.p.upd_alpha = upd_alpha; op.tc.p.upd_eps = upd_eps;
     rc = run_ops(m->ops_conv1_bwd, st);
   } else {
     if ((rc = run_ops(m->ops_conv1_bwd, st))) return rc;

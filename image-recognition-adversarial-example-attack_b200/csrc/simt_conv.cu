@@ -102,7 +102,7 @@ simt_conv_kernel(const SimtConvParams p) {
 // out[m, n] = sum_k a[m, k] * b[n, k] (+ bias[n]) — both operands K-contiguous (fp32 classifier head).
 // Deterministic split-K: kSplit slices of K write partial sums, a second kernel adds them in a fixed order
 // (fp32 atomics would make the logits run-to-run different).  64 x 64 block tile, 4 x 4 outputs per thread.
-constexpr int kFcSplit = 4;
+constexpr int kFcSplit = 8;
 __global__ void __launch_bounds__(256)
 fc_nt_splitk_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ part,
                     int m_total, int n_total, int k_total, int k_chunk) {

@@ -276,6 +276,17 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint4 v) {
                : "memory");
 }
 
+// attack.py:61-63 (project) / 33-34 (no projection); same arithmetic as elementwise.cu::linf_one
+__device__ __forceinline__ float linf_update_one(float x, float x0, float g, float a, float e, bool project) {
+  const float sgn = (float)((g > 0.f) - (g < 0.f));          // torch.sign: NaN and +-0 map to 0
+  float x1 = __fadd_rn(x, __fmul_rn(a, sgn));
+  if (project) {
+    const float hi = __fadd_rn(x0, e), lo = __fsub_rn(x0, e);
+    x1 = fmaxf(fminf(x1, hi), lo);
+  }
+  return fminf(fmaxf(x1, 0.f), 1.f);
+}
+
 // ---------------------------------------------------------------- the kernel
 struct TileCoord { int w0, h0, n0, c0, cls; };
 // pair mode: `tile` indexes (pair of consecutive pixel tiles, column block); CTA `rank` takes pixel tile
@@ -656,7 +667,18 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
               float2 v2;               // bf16 path: x (1/std) instead of the true division (fp32 mode keeps it)
               v2.x = o[2 * k] * inv_std[c];
               v2.y = o[2 * k + 1] * inv_std[c];
-              *reinterpret_cast<float2*>(g + off) = v2;
+              if (p.upd_x) {
+                // fused sign step + eps-ball projection + [0,1] clamp on the two pixels this lane owns
+                float2 xa = *reinterpret_cast<const float2*>(p.upd_x + off);
+                float2 x0 = make_float2(0.f, 0.f);
+                const bool project = p.upd_x0 != nullptr;
+                if (project) x0 = __ldg(reinterpret_cast<const float2*>(p.upd_x0 + off));
+                xa.x = linf_update_one(xa.x, x0.x, v2.x, p.upd_alpha, p.upd_eps, project);
+                xa.y = linf_update_one(xa.y, x0.y, v2.y, p.upd_alpha, p.upd_eps, project);
+                *reinterpret_cast<float2*>(p.upd_x + off) = xa;
+              } else {
+                *reinterpret_cast<float2*>(g + off) = v2;
+              }
             }
           }
         }

@@ -82,6 +82,11 @@ struct ConvGemmParams {
                                   // taps in the N dimension, reduced by warp shuffles (BN = 64)
   const float* std_dev;           // epi 1: device pointer to std[3]; gradient is divided by std[c]
   int img_h, img_w;               // epi 1: full-resolution image size
+  // epi 2 only, fused attack step (attack.py:33-34 / 61-63): instead of storing the gradient, update upd_x in
+  // place: x = clamp(project(x + alpha*sign(g))) — bit-identical to storing g and running linf_step on it
+  float* upd_x;                   // x_adv (fp32 NCHW), null = store the gradient to `out`
+  const float* upd_x0;            // x_orig of the eps-ball projection (null = no projection: FGSM)
+  float upd_alpha, upd_eps;
 };
 
 struct ConvGemmMaps {

@@ -110,6 +110,15 @@ int advb200_cw_init_f32(const float* x, float* x0, float* w, float* m, float* v,
                         float* best_adv, float* best_l2, uint8_t* best_success, float* l2_partials,
                         int n_img, int64_t elems_per_img, void* stream);
 
+/* One fused attack step (bf16 mode): forward + CE input gradient as advb200_input_grad(CE_MEAN), with the sign
+ * step, eps-ball projection and [0,1] clamp of attack.py:61-63 (x_orig != NULL) or attack.py:33-34
+ * (x_orig == NULL: FGSM, no projection) applied to x_adv IN PLACE by the epilogue of the stem's input-gradient
+ * kernel — the gradient tensor is never written to memory.  Bit-identical to advb200_input_grad followed by
+ * advb200_linf_step_f32.  Returns ADVB200_ERR_UNSUPPORTED for an fp32-mode model (use the two calls). */
+int advb200_attack_step(advb200_model* m, float* x_adv_inout, const float* x_orig, const float* mean3,
+                        const float* std3, const int64_t* y_true, int n, float inv_n_global, float alpha,
+                        float eps, int64_t* preds_out, void* workspace, int64_t workspace_bytes, void* stream);
+
 /* One CW iteration after advb200_input_grad(CW_*) produced grad_x and success for the current
  * x_adv (attack.py:126-137 + torch.optim.Adam single-tensor update):
  *   l2_n = sum(l2_partials_in[n,:])                     (distance of the CURRENT x_adv)

@@ -399,3 +399,23 @@ def test_host_batch_pipeline_equals_direct_calls(advb200_mod, native, dev):
         assert torch.equal(r, want)
     with pytest.raises(ValueError):
         list(pipe.run([torch.zeros(3, 3, 224, 224)]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("project", [True, False])
+def test_fused_attack_step_is_bit_identical_to_gradient_plus_update(advb200_mod, native, dev, project):
+    """advb200_attack_step (update fused into the stem input-gradient epilogue) == input_grad + linf step."""
+    nm = native["bf16"]
+    mean, std = weights.mean_std()
+    x0 = weights.synthetic_images(5, seed=77).to(dev)
+    y = torch.tensor([1, 713, 5, 713, 999], dtype=torch.int64, device=dev)
+    xa = (x0 + 0.01 * torch.randn_like(x0)).clamp(0, 1).contiguous()
+    g = nm.input_grad(xa, mean, std, y, loss="ce")["grad"]
+    want = xa.clone()
+    advb200_mod.attack._linf_step(want, x0 if project else None, g, 2 / 255, 8 / 255, project)
+    got = xa.clone()
+    nm.attack_step(got, x0 if project else None, mean, std, y, alpha=2 / 255, eps=8 / 255)
+    assert torch.equal(got, want)
+    assert not torch.equal(got, xa)
+    with pytest.raises(RuntimeError):
+        native["fp32"].attack_step(got, x0, mean, std, y, alpha=2 / 255, eps=8 / 255)
