@@ -665,8 +665,9 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
               const int c = pi % 3, ph = pi / 3;
               const long long off = (((long long)n * 3 + c) * p.img_h + (2 * h + ph)) * p.img_w + 2 * w;
               float2 v2;               // bf16 path: x (1/std) instead of the true division (fp32 mode keeps it)
-              v2.x = o[2 * k] * inv_std[c];
-              v2.y = o[2 * k + 1] * inv_std[c];
+              const float is = c == 0 ? inv_std[0] : (c == 1 ? inv_std[1] : inv_std[2]);   // registers, not local memory
+              v2.x = o[2 * k] * is;
+              v2.y = o[2 * k + 1] * is;
               if (p.upd_x) {
                 // fused sign step + eps-ball projection + [0,1] clamp on the two pixels this lane owns
                 float2 xa = *reinterpret_cast<const float2*>(p.upd_x + off);
