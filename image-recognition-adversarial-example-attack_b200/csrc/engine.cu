@@ -338,6 +338,10 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     p.bw = 8; p.bh = 16; p.bn = 1;
     p.tiles_w = out.w / 8; p.tiles_h = cdiv(out.h, 16); p.tiles_n = out.n; p.tiles_c = 1;
     t.bn = 64;
+    // CTA pair: M = 256 across two CTAs, each holding half of every tap's weight rows (5 instead of 6 KB of
+    // shared-memory operand reads per MMA; the cout = 64 layers are operand-fetch bound)
+    static const char* halo_pair = getenv("ADVB200_HALO_PAIR");
+    t.pair = g_force.pair >= 0 ? g_force.pair : (halo_pair ? atoi(halo_pair) : 0);
     p.out_w = out.w; p.out_h = out.h; p.out_n = out.n;
     p.halo = 1; p.halo_w0 = -1; p.halo_h0 = -1; p.halo_rows = 10 * 18; p.sbo_rows = 10;
     p.ntaps = 0;
@@ -350,7 +354,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
       }
     int rc = make_a(&t.maps.a[0], in, 1, 0, 0, 10, 18, 1);
     if (!rc) rc = make_out_maps(t, out, 1, 0, 0);
-    if (!rc) rc = make_b(&t.maps.b, 64);
+    if (!rc) rc = make_b(&t.maps.b, 64, t.pair);
     if (rc) return rc;
     annotate(op, "", (double)out.n * out.h * out.w, 9, 1.0);
     ops.push_back(op);

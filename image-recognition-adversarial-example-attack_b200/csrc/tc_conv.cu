@@ -418,15 +418,30 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
       if (p.halo) {
         // all taps' weights once, then one halo box of input pixels per tile
         const int rb = p.row_bytes ? p.row_bytes : 128;
-        mbar_expect_tx(bres_bar, (uint32_t)(p.ntaps * BN * rb));
-        for (int tap = 0; tap < p.ntaps; ++tap) tma_load_2d(&maps.b, bres_bar, smem + tap * BN * rb, 0, p.tap_brow[tap]);
+        if constexpr (kPair) {
+          // CTA pair: each CTA keeps HALF of every tap's weight rows and its own halo box; everything completes
+          // on the leader's barriers
+          const uint32_t rbar = mapa_u32(bres_bar, 0);
+          if (rank == 0) mbar_expect_tx(bres_bar, (uint32_t)(2 * p.ntaps * C::kBRows * rb));
+          for (int tap = 0; tap < p.ntaps; ++tap)
+            tma_load_2d_pair(&maps.b, rbar, smem + tap * C::kBRows * rb, 0, p.tap_brow[tap] + rank * C::kBRows);
+        } else {
+          mbar_expect_tx(bres_bar, (uint32_t)(p.ntaps * BN * rb));
+          for (int tap = 0; tap < p.ntaps; ++tap) tma_load_2d(&maps.b, bres_bar, smem + tap * BN * rb, 0, p.tap_brow[tap]);
+        }
         pdl_wait();
         for (int tile = tile0; tile < total_tiles; tile += tile_step) {
           const TileCoord tc = tile_coord<kPair>(p, tile, BN, rank);
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_expect_tx(&full_bar[stage], (uint32_t)(p.halo_rows * rb));
-          tma_load_4d(&maps.a[0], &full_bar[stage], ring + stage * stage_bytes, 0, tc.w0 + p.halo_w0,
-                      tc.h0 + p.halo_h0, tc.n0);
+          if constexpr (kPair) {
+            const uint32_t fb = mapa_u32(&full_bar[stage], 0);
+            if (rank == 0) mbar_expect_tx(&full_bar[stage], (uint32_t)(2 * p.halo_rows * rb));
+            tma_load_4d_pair(&maps.a[0], fb, ring + stage * stage_bytes, 0, tc.w0 + p.halo_w0, tc.h0 + p.halo_h0, tc.n0);
+          } else {
+            mbar_expect_tx(&full_bar[stage], (uint32_t)(p.halo_rows * rb));
+            tma_load_4d(&maps.a[0], &full_bar[stage], ring + stage * stage_bytes, 0, tc.w0 + p.halo_w0,
+                        tc.h0 + p.halo_h0, tc.n0);
+          }
           if (++stage == nstages) { stage = 0; phase ^= 1; }
         }
       } else {
@@ -541,23 +556,30 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           tc_fence_after();
           if (elect_one()) {
             const uint32_t a_lo0 = ring_lo + (uint32_t)stage * stage_units;
+            const uint32_t b_tap = (uint32_t)C::kBRows * (rb >> 4);       // 16-byte units between taps' weights
             if (kslices == 1) {
               // 32-byte rows: one MMA per tap; unrolled so the single issuing thread batches the tap-offset loads
 #pragma unroll 8
-              for (int tap = 0; tap < ntaps; ++tap)
-                umma_bf16(d_tmem, ((uint64_t)a_hi_halo << 32) | (a_lo0 + (uint32_t)p.tap_row[tap] * 2u),
-                          ((uint64_t)b_hi_halo << 32) | (bres_lo + (uint32_t)(tap * BN) * 2u), idesc, tap != 0 ? 1u : 0u);
+              for (int tap = 0; tap < ntaps; ++tap) {
+                const uint64_t ad = ((uint64_t)a_hi_halo << 32) | (a_lo0 + (uint32_t)p.tap_row[tap] * 2u);
+                const uint64_t bd = ((uint64_t)b_hi_halo << 32) | (bres_lo + (uint32_t)tap * b_tap);
+                if constexpr (kPair) umma_bf16_pair(d_tmem, ad, bd, idesc, tap != 0 ? 1u : 0u);
+                else umma_bf16(d_tmem, ad, bd, idesc, tap != 0 ? 1u : 0u);
+              }
             } else {
               for (int tap = 0; tap < ntaps; ++tap) {
                 const uint32_t a_lo = a_lo0 + (uint32_t)(p.tap_row[tap] * 8);
-                const uint32_t b_lo = bres_lo + (uint32_t)(tap * BN * 8);
+                const uint32_t b_lo = bres_lo + (uint32_t)tap * b_tap;
 #pragma unroll
-                for (int k = 0; k < kBlockK / 16; ++k)
-                  umma_bf16(d_tmem, ((uint64_t)a_hi_halo << 32) | (a_lo + 2u * k), ((uint64_t)b_hi_halo << 32) | (b_lo + 2u * k),
-                            idesc, (tap | k) != 0 ? 1u : 0u);
+                for (int k = 0; k < kBlockK / 16; ++k) {
+                  const uint64_t ad = ((uint64_t)a_hi_halo << 32) | (a_lo + 2u * k);
+                  const uint64_t bd = ((uint64_t)b_hi_halo << 32) | (b_lo + 2u * k);
+                  if constexpr (kPair) umma_bf16_pair(d_tmem, ad, bd, idesc, (tap | k) != 0 ? 1u : 0u);
+                  else umma_bf16(d_tmem, ad, bd, idesc, (tap | k) != 0 ? 1u : 0u);
+                }
               }
             }
-            umma_commit(&empty_bar[stage]);
+            if constexpr (kPair) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
           }
           __syncwarp();
           if (++stage == nstages) { stage = 0; phase ^= 1; }
@@ -887,11 +909,11 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
     }
   }
   if (p.halo) {
-    ADV_CHECK_ARG(p.kblocks == 1 && p.tiles_c == 1 && !p.has_add && !kPair,
-                  "conv_gemm: halo mode needs K = 64, one column block, one CTA per tile");
+    ADV_CHECK_ARG(p.kblocks == 1 && p.tiles_c == 1 && !p.has_add && (!kPair || p.epi == 0),
+                  "conv_gemm: halo mode needs K = 64 and one column block (CTA pairs: plain bf16 epilogue only)");
     const int rb = p.row_bytes ? p.row_bytes : 128;
     ADV_CHECK_ARG(rb == 128 || rb == 32, "conv_gemm: halo rows are 128 or 32 bytes");
-    p.ring_off = (p.ntaps * BN * rb + 1023) & ~1023;
+    p.ring_off = (p.ntaps * C::kBRows * rb + 1023) & ~1023;
     p.stage_bytes = (p.halo_rows * rb + 1023) & ~1023;
   }
   static const char* force_slots = getenv("ADVB200_OUT_SLOTS");   // tuning knob
