@@ -342,6 +342,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     // shared-memory operand reads per MMA; the cout = 64 layers are operand-fetch bound)
     static const char* halo_pair = getenv("ADVB200_HALO_PAIR");
     t.pair = g_force.pair >= 0 ? g_force.pair : (halo_pair ? atoi(halo_pair) : 0);
+    apply_force(p);
     p.out_w = out.w; p.out_h = out.h; p.out_n = out.n;
     p.halo = 1; p.halo_w0 = -1; p.halo_h0 = -1; p.halo_rows = 10 * 18; p.sbo_rows = 10;
     p.ntaps = 0;
@@ -660,7 +661,11 @@ struct Tuner {
     int rc = builder(base);
     if (rc) return rc;
     bool tunable = on && !base.empty();
-    for (const Op& o : base) if (o.kind != Op::TC || o.tc.p.halo || o.tc.bn == 16) tunable = false;
+    bool halo = false;
+    for (const Op& o : base) {
+      if (o.kind != Op::TC || o.tc.bn == 16) tunable = false;
+      else if (o.tc.p.halo) halo = true;
+    }
     if (!tunable) { ops.insert(ops.end(), base.begin(), base.end()); return ADVB200_OK; }
     const std::string key = std::string(base[0].name) + "#" + std::to_string(n);
     auto it = m->tune_cache.find(key);
@@ -668,6 +673,9 @@ struct Tuner {
       const auto t0 = std::chrono::steady_clock::now();
       const int cout = base[0].tc.p.cout;
       std::vector<TileForce> cands;
+      if (halo) {      // halo-mode 3x3: the tile is fixed; only the output path (staging slots / direct stores) is open
+        for (int slots : {1, 2, 4}) { TileForce f; f.pair = 0; f.slots = slots; cands.push_back(f); }
+      } else
       for (int bn : {256, 128, 64}) {
         if (cout % bn || (bn == 64 && cout >= 256)) continue;
         for (int pair = 0; pair < 2; ++pair)
