@@ -50,6 +50,7 @@ SIGNATURES = {
     "advb200_defend_input_f32": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
     "advb200_eval_counters": (c_int, [c_void_p] * 5 + [c_float, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "advb200_test_conv": (c_int, [c_int] + [c_void_p] * 6 + [c_int] * 9 + [c_void_p]),
+    "advb200_test_force_tile": (c_int, [c_int, c_int, c_int, c_int]),
     "advb200_launch_count": (c_int64, []),
     "advb200_profile_enable": (c_int, [c_int]),
     "advb200_profile_read": (c_int, [POINTER(ctypes.c_double), POINTER(c_int64)]),

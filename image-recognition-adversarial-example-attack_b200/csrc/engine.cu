@@ -438,7 +438,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
   const int pad = (ksize == 3) ? 1 : 0;
   static const bool multiclass = !getenv("ADVB200_NO_MULTICLASS");
   const int sw = out.w / 2, sh = out.h / 2;
-  if (multiclass && ksize == 3) {
+  if (multiclass && ksize == 3 && !add) {   // (a residual operand would need one map per class: per-class launches)
     Op o2 = op;
     TcOp& t2 = o2.tc;
     ConvGemmParams& q = t2.p;
@@ -1321,6 +1321,12 @@ static int input_grad_impl(advb200_model* m, const float* x, const float* mean3,
     rc = launch_grad_nhwc_to_nchw(m->g_img_nhwc, std3, grad_x_out, n, kImg, kImg, st);
   }
   return rc;
+}
+
+int advb200_test_force_tile(int bn, int pair, int bres, int slots) {
+  // test hook: tile configuration of the next advb200_test_conv calls (-1 = default heuristic)
+  g_force.bn = bn; g_force.pair = pair; g_force.bres = bres; g_force.slots = slots;
+  return ADVB200_OK;
 }
 
 int advb200_test_conv(int precision, const void* x, const float* wgt, const float* bias, const void* add,

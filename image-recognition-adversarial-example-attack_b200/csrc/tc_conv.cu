@@ -773,6 +773,9 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
         const long long pixel = ((long long)tn * p.full_h + (th * p.pix_sub + pix_ph)) * p.full_w +
                                 (tw * p.pix_sub + pix_pw);
         const long long mword0 = ((long long)(tc.c0 >> 6) * p.mask_pixels + pixel) * 2 + half;
+        // direct-store mode has no per-sub-tile barrier: one barrier per tile keeps a fast warp from overwriting the
+        // shift copy that slower warps still read for the previous tile (found by the candidate-equivalence test)
+        if (n_out_slots == 0 && has_bias) epi_bar();
         // folded-BN shift of the NEXT tile goes to the other accumulator's copy
         if (has_bias && etid < BN && tile + tile_step < total_tiles)
           bias_smem[(acc ^ 1) * 256 + etid] = __ldg(p.bias + tile_coord<kPair>(p, tile + tile_step, BN, rank).c0 + etid);

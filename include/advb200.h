@@ -173,6 +173,10 @@ int advb200_eval_counters(const int64_t* pred_clean, const int64_t* pred_adv, co
 int advb200_test_conv(int precision, const void* x, const float* wgt, const float* bias,
                       const void* add, const void* mask, void* out, int n, int h, int w, int cin,
                       int cout, int ksize, int stride, int relu, int dgrad, void* stream);
+/* Test hook: forces the tile configuration (BN columns, CTA pair, resident weights, output staging slots; -1 =
+ * heuristic) of the following advb200_test_conv calls — the candidates the plan-time autotuner chooses between;
+ * the parity tests check that every candidate gives bit-identical results. */
+int advb200_test_force_tile(int bn, int pair, int bres, int slots);
 
 /* number of kernels launched by this library since load (bench.py's gpu_launches) */
 int64_t advb200_launch_count(void);
