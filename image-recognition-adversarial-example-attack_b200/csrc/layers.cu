@@ -232,16 +232,29 @@ __device__ __forceinline__ uint32_t hadd2_u(uint32_t a, uint32_t b) {
   return *reinterpret_cast<uint32_t*>(&r);
 }
 
+// kStem: the ResNet-50 stem geometry (112 x 112 x 64 -> 56 x 56) as compile-time constants — the index math of the
+// generic version (three 64-bit div/mod per thread) was ~45 % of the instructions of this instruction-bound kernel
+template <bool kStem>
 __global__ void __launch_bounds__(kT)
-maxpool_fwd_bf16x8_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, uint8_t* __restrict__ idx, int hi,
-                          int wi, int ho, int wo, int c8, long long total) {
+maxpool_fwd_bf16x8_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, uint8_t* __restrict__ idx, int hi_,
+                          int wi_, int ho_, int wo_, int c8_, long long total) {
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // (n, oh, ow, c8)
   if (t >= total) return;
-  const int cg = (int)(t % c8);
-  long long r = t / c8;
-  const int ow = (int)(r % wo); r /= wo;
-  const int oh = (int)(r % ho);
-  const long long n = r / ho;
+  const int hi = kStem ? 112 : hi_, wi = kStem ? 112 : wi_, ho = kStem ? 56 : ho_, wo = kStem ? 56 : wo_;
+  const int c8 = kStem ? 8 : c8_;
+  int cg, ow, oh; long long n;
+  if (kStem) {
+    const unsigned per_img = 56u * 56u * 8u;
+    n = t / per_img;
+    const unsigned rem = (unsigned)(t - n * per_img);
+    cg = rem & 7; ow = (rem >> 3) % 56u; oh = (rem >> 3) / 56u;
+  } else {
+    cg = (int)(t % c8);
+    long long r = t / c8;
+    ow = (int)(r % wo); r /= wo;
+    oh = (int)(r % ho);
+    n = r / ho;
+  }
   uint32_t best[4], pos[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) { best[i] = 0xFF80FF80u; pos[i] = 0; }       // -inf, position 0
@@ -276,16 +289,27 @@ maxpool_fwd_bf16x8_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, u
 
 // one thread = a 2x2 input patch (rows 2a,2a+1; cols 2b,2b+1) x 8 channels: the four windows that can
 // route gradient into the patch, (a..a+1, b..b+1), are each loaded once (all loads issued up front)
+template <bool kStem>
 __global__ void __launch_bounds__(kT)
 maxpool_bwd_bf16x8_kernel(const bf16* __restrict__ gout, const uint8_t* __restrict__ idx, bf16* __restrict__ gin,
-                          int hi, int wi, int ho, int wo, int c8, long long total) {
+                          int hi_, int wi_, int ho_, int wo_, int c8_, long long total) {
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // (n, a, b, c8)
   if (t >= total) return;
-  const int cg = (int)(t % c8);
-  long long r = t / c8;
-  const int pb = (int)(r % (wi / 2)); r /= (wi / 2);
-  const int pa = (int)(r % (hi / 2));
-  const long long n = r / (hi / 2);
+  const int hi = kStem ? 112 : hi_, wi = kStem ? 112 : wi_, ho = kStem ? 56 : ho_, wo = kStem ? 56 : wo_;
+  const int c8 = kStem ? 8 : c8_;
+  int cg, pb, pa; long long n;
+  if (kStem) {
+    const unsigned per_img = 56u * 56u * 8u;
+    n = t / per_img;
+    const unsigned rem = (unsigned)(t - n * per_img);
+    cg = rem & 7; pb = (rem >> 3) % 56u; pa = (rem >> 3) / 56u;
+  } else {
+    cg = (int)(t % c8);
+    long long r = t / c8;
+    pb = (int)(r % (wi / 2)); r /= (wi / 2);
+    pa = (int)(r % (hi / 2));
+    n = r / (hi / 2);
+  }
   uint2 ix[2][2];
   uint4 gv[2][2];
 #pragma unroll
@@ -662,7 +686,10 @@ int launch_maxpool_fwd(const T* in, T* out, uint8_t* idx, int n, int hi, int wi,
   if (!total) return ADVB200_OK;
   if constexpr (std::is_same<T, bf16>::value) {
     if (c % 8 == 0) {
-      maxpool_fwd_bf16x8_kernel<<<nblocks(total / 8), kT, 0, st>>>(in, out, idx, hi, wi, ho, wo, c / 8, total / 8);
+      if (hi == 112 && wi == 112 && c == 64)
+        maxpool_fwd_bf16x8_kernel<true><<<nblocks(total / 8), kT, 0, st>>>(in, out, idx, hi, wi, ho, wo, c / 8, total / 8);
+      else
+        maxpool_fwd_bf16x8_kernel<false><<<nblocks(total / 8), kT, 0, st>>>(in, out, idx, hi, wi, ho, wo, c / 8, total / 8);
       ADV_LAUNCHED();
       return ADVB200_OK;
     }
@@ -679,7 +706,10 @@ int launch_maxpool_bwd(const T* gout, const uint8_t* idx, T* gin, int n, int hi,
   if (!total) return ADVB200_OK;
   if constexpr (std::is_same<T, bf16>::value) {
     if (c % 8 == 0 && hi % 2 == 0 && wi % 2 == 0) {
-      maxpool_bwd_bf16x8_kernel<<<nblocks(total / 32), kT, 0, st>>>(gout, idx, gin, hi, wi, ho, wo, c / 8, total / 32);
+      if (hi == 112 && wi == 112 && c == 64)
+        maxpool_bwd_bf16x8_kernel<true><<<nblocks(total / 32), kT, 0, st>>>(gout, idx, gin, hi, wi, ho, wo, c / 8, total / 32);
+      else
+        maxpool_bwd_bf16x8_kernel<false><<<nblocks(total / 32), kT, 0, st>>>(gout, idx, gin, hi, wi, ho, wo, c / 8, total / 32);
       ADV_LAUNCHED();
       return ADVB200_OK;
     }

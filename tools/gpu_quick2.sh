@@ -15,19 +15,18 @@ except Exception as e:
 PY
 done
 if [ "${LIST:-0}" = "1" ]; then
-  timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/pass_launches.csv \
-    python tools/one_pass.py 256 2 > gpurun_out/ncu_pass.log 2>&1; echo "ncu list rc=$?"
+  timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/pass_launches.csv \
+    python tools/one_pass.py 256 grad > gpurun_out/ncu_pass.log 2>&1; echo "ncu list rc=$?"
   python - <<'PY'
 import csv, collections
 rows = list(csv.reader(open("gpurun_out/pass_launches.csv")))
 hi = [i for i, r in enumerate(rows) if "Kernel Name" in r][0]
 h = rows[hi]; kn = h.index("Kernel Name"); mv = h.index("Metric Value")
 seq = [(r[kn].split("(")[0][-48:], float(r[mv].replace(",", ""))) for r in rows[hi + 1:] if len(r) > mv]
-seq = seq[len(seq) // 2:]
 agg = collections.OrderedDict()
 for k, v in seq:
     a = agg.setdefault(k, [0, 0.0]); a[0] += 1; a[1] += v
-print("second pass: kernels", len(seq), "total us", sum(v for _, v in seq) / 1000)
+print("one pass: kernels", len(seq), "total us", sum(v for _, v in seq) / 1000)
 for k, (c, v) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     print(f"{k:50s} n={c:4d} sum_us={v/1000:9.1f}")
 PY
