@@ -57,8 +57,10 @@ struct TcOp {
 };
 
 struct Op {
-  enum Kind { TC, SIMT, MEMSET } kind;
+  enum Kind { TC, SIMT, MEMSET, FUSED } kind;
   TcOp tc;
+  FusedBlockMaps fmaps;
+  FusedBlockParams fp;
   SimtConvParams simt;
   void* ms_ptr = nullptr;
   size_t ms_bytes = 0;
@@ -243,6 +245,67 @@ int build_pw_s2_ops(std::vector<Op>& ops, Act g_a, const bf16* w1, Act g_sum, co
   label_op(op, "", 2.0 * pix * gemm_n * (4.0 * g_a.c + g_sum.c),
            2.0 * (4.0 * pix * g_a.c + pix * g_sum.c + 4.0 * pix * gemm_n * (1.0 + (mask ? 1.0 / 16 : 0)) +
                   (double)gemm_n * (g_a.c + g_sum.c)));
+  ops.push_back(op);
+  return ADVB200_OK;
+}
+
+// ---- fused bottleneck tail (layer1): 3x3 halo conv (64 -> 64) + pointwise conv (64 -> 256) + residual ----------
+// forward : in = a (conv1 output), w1 = conv2 fwd pack, w2 = conv3 fwd pack, res = block input x, out = block output
+// backward: in = g_b, w1 = conv2 dgrad pack, w2 = conv1 dgrad pack, res = g_sum (skip gradient), out = g_x
+int build_fused_block(std::vector<Op>& ops, bool dgrad, Act in, const bf16* w1, const bf16* w2, Act out, const void* res,
+                      const float* bias1, const float* bias2, int relu, const uint32_t* mask1_in, uint32_t* mask1_out,
+                      const uint32_t* mask2_in, uint32_t* mask2_out) {
+  ADV_CHECK_ARG(in.c == 64 && out.c == 256 && in.h == out.h && in.w == out.w && in.n == out.n && in.w % 8 == 0,
+                "fused block: needs a 64-channel 3x3 input and a 256-channel output of the same pixel grid");
+  Op op;
+  op.kind = Op::FUSED;
+  memset(&op.tc, 0, sizeof op.tc);
+  FusedBlockParams& p = op.fp;
+  memset(&p, 0, sizeof p);
+  memset(&op.fmaps, 0, sizeof op.fmaps);
+  p.tiles_w = in.w / 8; p.tiles_h = cdiv(in.h, 16); p.tiles_n = in.n;
+  p.img_h = in.h; p.img_w = in.w; p.img_n = in.n;
+  for (int r = 0; r < 3; ++r)
+    for (int s = 0; s < 3; ++s) {
+      const int i = r * 3 + s;
+      const int dh = dgrad ? 1 - r : r - 1, dw = dgrad ? 1 - s : s - 1;
+      p.tap_row[i] = (1 + dh) * 10 + (1 + dw);
+      p.tap_brow[i] = i * 64;
+    }
+  p.bias1 = bias1; p.bias2 = bias2; p.relu = relu;
+  p.mask1_in = mask1_in; p.mask1_out = mask1_out; p.mask2_in = mask2_in; p.mask2_out = mask2_out;
+  p.mask_pixels = (long long)in.n * in.h * in.w;
+  p.res = res; p.out = out.p;
+  int rc;
+  {
+    const uint64_t dims[4] = {64, (uint64_t)in.w, (uint64_t)in.h, (uint64_t)in.n};
+    const uint64_t strides[3] = {128, 128ull * in.w, 128ull * in.w * in.h};
+    const uint32_t box[4] = {64, 10, 18, 1};
+    rc = make_tmap_bf16(&op.fmaps.a, in.p, 4, dims, strides, box);
+  }
+  {
+    const uint64_t dims[2] = {64, 9 * 64};
+    const uint64_t strides[1] = {128};
+    const uint32_t box[2] = {64, 64};
+    if (!rc) rc = make_tmap_bf16(&op.fmaps.w1, w1, 2, dims, strides, box);
+  }
+  {
+    const uint64_t dims[2] = {64, 256};
+    const uint64_t strides[1] = {128};
+    const uint32_t box[2] = {64, 256};
+    if (!rc) rc = make_tmap_bf16(&op.fmaps.w2, w2, 2, dims, strides, box);
+  }
+  {
+    const uint64_t dims[4] = {256, (uint64_t)out.w, (uint64_t)out.h, (uint64_t)out.n};
+    const uint64_t strides[3] = {512, 512ull * out.w, 512ull * out.w * out.h};
+    const uint32_t box[4] = {64, 8, 16, 1};
+    if (!rc) rc = make_tmap_bf16(&op.fmaps.res, res, 4, dims, strides, box);
+    if (!rc) rc = make_tmap_bf16(&op.fmaps.out, out.p, 4, dims, strides, box);
+  }
+  if (rc) return rc;
+  const double pix = (double)in.n * in.h * in.w;
+  label_op(op, "", 2.0 * pix * (64.0 * 64 * 9 + 64.0 * 256),
+           2.0 * pix * (64 + 256 + 256) + 2.0 * pix * (64 + 256) / 16 + 2.0 * (9 * 64 * 64 + 64 * 256));
   ops.push_back(op);
   return ADVB200_OK;
 }
@@ -549,6 +612,14 @@ int run_ops(std::vector<Op>& ops, cudaStream_t st) {
         }
         break;
       }
+      case Op::FUSED: {
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (g_prof_on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, st); }
+        rc = launch_fused_block(op.fmaps, op.fp, st);
+        if (g_prof_on) { cudaEventRecord(e1, st); g_prof_events.push_back(ProfRec{e0, e1, &op}); }
+        ++g_snake;
+        break;
+      }
       case Op::SIMT: rc = launch_simt_conv(op.simt, st); break;
       case Op::MEMSET: {
         cudaError_t e = cudaMemsetAsync(op.ms_ptr, 0, op.ms_bytes, st);
@@ -742,6 +813,7 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out, cudaStream_t tune_s
     return a;
   };
   static const bool fuse = !getenv("ADVB200_NO_FUSE");   // conv3+downsample / conv1-dgrad+downsample-dgrad fusion
+  static const bool fuse_blk = !getenv("ADVB200_NO_FUSEBLK");   // layer1 conv2+conv3 / conv2-dgrad+conv1-dgrad fusion
   static char lbl[48];
   auto setl = [&](const char* dir, const BlockSpec* s, const char* conv) {
     if (s) snprintf(lbl, sizeof lbl, "%s l%d.%d.%s", dir, s->layer + 1, s->idx, conv);
@@ -864,10 +936,20 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out, cudaStream_t tune_s
       if (tc) {
         setl("fwd", &s, "c1");
         rc = emit(ops, [&](std::vector<Op>& v_) { return build_tc_ops(v_, c1.b_fwd, 1, 1, false, t.x, t.a, c1.shift, nullptr, nullptr, 1, t.ma); });
+        const bf16* res = reinterpret_cast<const bf16*>(t.x.p);
+        // layer1 blocks without a downsample: conv2 (3x3, 64 -> 64) and conv3 (1x1, 64 -> 256, + x) in ONE launch —
+        // the 64-channel intermediate never goes through HBM
+        const bool fuse_tail = fuse_blk && s.layer == 0 && !s.down && s.width == 64;
+        if (fuse_tail) {
+          setl("fwd", &s, "c2+c3");
+          if (!rc) rc = build_fused_block(ops, false, t.a, c2.b_fwd, c3.b_fwd, t.out, res, c2.shift, c3.shift, 1, nullptr,
+                                          t.mb, nullptr, t.mout);
+        } else {
         setl("fwd", &s, "c2");
         if (!rc) rc = emit(ops, [&](std::vector<Op>& v_) { return build_tc_ops(v_, c2.b_fwd, 3, s.stride, false, t.a, t.b, c2.shift, nullptr, nullptr, 1, t.mb); });
-        const bf16* res = reinterpret_cast<const bf16*>(t.x.p);
-        if (!rc && s.down && fuse) {
+        }
+        if (fuse_tail) {
+        } else if (!rc && s.down && fuse) {
           // conv3 + downsample in one launch: both GEMMs accumulate into the same TMEM tile
           const ConvW& cd = m->conv[s.conv_base + 3];
           setl("fwd", &s, "c3+ds");
@@ -913,19 +995,25 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out, cudaStream_t tune_s
     const int ia = gacquire(); Act g_a = t.a; g_a.p = gbuf[ia];
     const bool first = bi == 0;   // block input is the max-pool output: its ReLU is handled there
     int nxt;
+    // layer1 blocks without a downsample: conv2-dgrad (3x3) + conv1-dgrad (1x1, + skip gradient) in ONE launch
+    const bool fused_b = tc && fuse_blk && s.layer == 0 && !s.down && s.width == 64;
     if (build) {
       if (tc) {
         setl("bwd", &s, "c3");
         rc = emit(m->ops_bwd, [&](std::vector<Op>& v_) { return build_tc_ops(v_, c3.b_dgrad, 1, 1, true, g_sum, g_b, nullptr, nullptr, t.mb, 0); });
+        if (fused_b) {
+          // built below, once the output buffer is known
+        } else {
         setl("bwd", &s, "c2");
         if (!rc) rc = emit(m->ops_bwd, [&](std::vector<Op>& v_) { return build_tc_ops(v_, c2.b_dgrad, 3, s.stride, true, g_b, g_a, nullptr, nullptr, t.ma, 0); });
+        }
       } else {
         typedef const float* F;
         rc = build_simt_op(m->ops_bwd, c3.f_dgrad, 1, 1, true, g_sum, g_b, nullptr, nullptr, (F)t.b.p, 0);
         if (!rc) rc = build_simt_op(m->ops_bwd, c2.f_dgrad, 3, s.stride, true, g_b, g_a, nullptr, nullptr, (F)t.a.p, 0);
       }
     }
-    gbusy[ib] = false;                                   // g_b is dead after conv2's dgrad
+    if (!fused_b) gbusy[ib] = false;                     // g_b is dead after conv2's dgrad
     Act g_x = t.x;
     if (s.down && tc && fuse) {
       // conv1-dgrad + downsample-dgrad accumulate in TMEM: g_x = mask(x) * (W1^T g_a + Wds^T g_sum).
@@ -982,6 +1070,12 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out, cudaStream_t tune_s
       gbusy[it] = false;
     } else {
       nxt = gacquire(); g_x.p = gbuf[nxt];
+      if (fused_b) gbusy[ib] = false;                    // (g_b is the fused launch's input: released after g_x is placed)
+      if (build && !rc && fused_b) {
+        setl("bwd", &s, "c2+c1");
+        rc = build_fused_block(m->ops_bwd, true, g_b, c2.b_dgrad, c1.b_dgrad, g_x, g_sum.p, nullptr, nullptr, 0, t.ma,
+                               nullptr, first ? nullptr : t.mx, nullptr);
+      } else
       if (build && !rc) {
         setl("bwd", &s, "c1");
         if (tc) rc = emit(m->ops_bwd, [&](std::vector<Op>& v_) { return build_tc_ops(v_, c1.b_dgrad, 1, 1, true, g_a, g_x, nullptr, (const bf16*)g_sum.p,

@@ -959,7 +959,379 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
   return ADVB200_OK;
 }
 
+
+// ================================================================ fused 3x3 (halo) + pointwise kernel
+// Warp roles as in conv_gemm_kernel.  Per tile: [MMA] 36 N=64 MMAs -> D1 (TMEM cols 0..63); [epilogue] D1 -> shift,
+// ReLU / masks -> bf16 -> swizzled `mid` tile in shared memory; [MMA] 4 N=256 MMAs, A = mid, B = resident pointwise
+// weights -> D2 (TMEM cols 64..319); [epilogue] D2 + residual (global loads) + shift -> ReLU / masks -> bf16 ->
+// 64-byte runs straight to global memory.  The second epilogue of tile i overlaps the first GEMM of tile i+1; the
+// kernel is HBM-bound (residual read + output write), so nothing more is pipelined.
+constexpr int kFbW1Bytes = 9 * 64 * 128;
+constexpr int kFbW2Bytes = 256 * 128;
+constexpr int kFbHaloRows = 10 * 18;
+constexpr int kFbHaloBytes = (kFbHaloRows * 128 + 1023) & ~1023;
+constexpr int kFbMidBytes = kBlockM * 128;
+constexpr int kFbBiasBytes = (64 + 256) * 4;
+constexpr int kFbBarBytes = 256;
+constexpr int kFbMaxStages = 4;
+constexpr int kFbResSlots = 5;                 // residual sub-tile ring; each slot is also its sub-tile's output staging
+
+struct FbCoord { int w0, h0, n; };
+__device__ __forceinline__ FbCoord fb_coord(const FusedBlockParams& p, int tile) {
+  FbCoord c;
+  int q = (int)(((unsigned long long)(unsigned)tile * p.magic_w) >> 40);
+  c.w0 = (tile - q * p.tiles_w) * 8; tile = q;
+  q = (int)(((unsigned long long)(unsigned)tile * p.magic_h) >> 40);
+  c.h0 = (tile - q * p.tiles_h) * 16; c.n = q;
+  return c;
+}
+
+constexpr int kFbThreads = (2 + 8 + 4) * 32;   // TMA, MMA, 8 second-epilogue warps, 4 first-epilogue warps
+
+__global__ void __launch_bounds__(kFbThreads, 1)
+fused_block_kernel(const __grid_constant__ FusedBlockMaps maps, const __grid_constant__ FusedBlockParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* w1_smem = smem;
+  uint8_t* w2_smem = smem + kFbW1Bytes;
+  uint8_t* ring = w2_smem + kFbW2Bytes;
+  uint8_t* mid_smem = ring + p.stages * kFbHaloBytes;
+  uint8_t* res_smem = mid_smem + kFbMidBytes;                                    // kFbResSlots x 16 KB
+  float* bias_smem = reinterpret_cast<float*>(res_smem + kFbResSlots * kSubTileBytes);   // [64] then [256]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(bias_smem) + kFbBiasBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + kFbMaxStages;
+  uint64_t* wres_bar = bars + 2 * kFbMaxStages;
+  uint64_t* d1_full = wres_bar + 1;
+  uint64_t* mid_full = wres_bar + 2;
+  uint64_t* d2_full = wres_bar + 3;
+  uint64_t* d2_empty = wres_bar + 4;
+  uint64_t* res_full = wres_bar + 5;
+  uint64_t* res_empty = res_full + kFbResSlots;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_empty + kFbResSlots);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int nstages = p.stages;
+  const int total_tiles = p.total_tiles;
+
+  if (warp == 0 && lane == 0) {
+    if (smem_u32(smem) & 1023u) __trap();
+    prefetch_tmap(&maps.a); prefetch_tmap(&maps.w1); prefetch_tmap(&maps.w2);
+    prefetch_tmap(&maps.res); prefetch_tmap(&maps.out);
+    for (int s = 0; s < kFbMaxStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < kFbResSlots; ++s) { mbar_init(&res_full[s], 1); mbar_init(&res_empty[s], 1); }
+    mbar_init(wres_bar, 1); mbar_init(d1_full, 1); mbar_init(mid_full, 1); mbar_init(d2_full, 1);
+    mbar_init(d2_empty, 8);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(512)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (warp >= kEpiWarp0) {
+    const int i = threadIdx.x - kEpiWarp0 * 32;
+    if (i < 64) bias_smem[i] = p.bias1 ? __ldg(p.bias1 + i) : 0.f;
+    if (i < 256) bias_smem[64 + i] = p.bias2 ? __ldg(p.bias2 + i) : 0.f;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // =========================== TMA producer ===========================
+    if (lane == 0) {
+      pdl_launch_dependents();
+      mbar_expect_tx(wres_bar, (uint32_t)(kFbW1Bytes + kFbW2Bytes));
+      for (int tap = 0; tap < 9; ++tap) tma_load_2d(&maps.w1, wres_bar, w1_smem + tap * 64 * 128, 0, p.tap_brow[tap]);
+      tma_load_2d(&maps.w2, wres_bar, w2_smem, 0, 0);
+      pdl_wait();
+      int stage = 0, rs = 0;
+      uint32_t phase = 0, rphase = 0;
+      auto load_halo = [&](int tile) {
+        const FbCoord tc = fb_coord(p, tile);
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        mbar_expect_tx(&full_bar[stage], (uint32_t)(kFbHaloRows * 128));
+        tma_load_4d(&maps.a, &full_bar[stage], ring + stage * kFbHaloBytes, 0, tc.w0 - 1, tc.h0 - 1, tc.n);
+        if (++stage == nstages) { stage = 0; phase ^= 1; }
+      };
+      // one halo stage is enough: the box of tile i+1 is requested as soon as the first GEMM of tile i has drained it,
+      // a whole (first epilogue + second GEMM + second epilogue) ahead of its use
+      if ((int)blockIdx.x < total_tiles) load_halo(blockIdx.x);
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const FbCoord tc = fb_coord(p, tile);
+        for (int j = 0; j < 4; ++j) {
+          mbar_wait(&res_empty[rs], rphase ^ 1);
+          mbar_expect_tx(&res_full[rs], (uint32_t)kSubTileBytes);
+          tma_load_4d(&maps.res, &res_full[rs], res_smem + rs * kSubTileBytes, 64 * j, tc.w0, tc.h0, tc.n);
+          if (++rs == kFbResSlots) { rs = 0; rphase ^= 1; }
+        }
+        if (tile + (int)gridDim.x < total_tiles) load_halo(tile + gridDim.x);
+      }
+    }
+  } else if (warp == 1) {
+    // =========================== MMA issuer ===========================
+    constexpr uint32_t idesc64 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+    constexpr uint32_t idesc256 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(256 >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+    const uint32_t dense_hi = (uint32_t)(make_smem_desc(0) >> 32);
+    const uint32_t halo_hi = (uint32_t)(make_smem_desc(0, 10u * 128u) >> 32);
+    const uint32_t ring_lo = ((smem_u32(ring) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t w1_lo = ((smem_u32(w1_smem) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t w2_lo = ((smem_u32(w2_smem) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t mid_lo = ((smem_u32(mid_smem) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t d1 = tmem_base, d2 = tmem_base + 64u;
+    int stage = 0;
+    uint32_t phase = 0, par = 0;
+    if (blockIdx.x < total_tiles) mbar_wait(wres_bar, 0);
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      mbar_wait(&full_bar[stage], phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t a_lo0 = ring_lo + (uint32_t)stage * (uint32_t)(kFbHaloBytes >> 4);
+        for (int tap = 0; tap < 9; ++tap) {
+          const uint32_t a_lo = a_lo0 + (uint32_t)(p.tap_row[tap] * 8);
+          const uint32_t b_lo = w1_lo + (uint32_t)(tap * 64 * 8);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_bf16(d1, ((uint64_t)halo_hi << 32) | (a_lo + 2u * k), ((uint64_t)dense_hi << 32) | (b_lo + 2u * k), idesc64,
+                      (tap | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[stage]);
+        umma_commit(d1_full);
+      }
+      __syncwarp();
+      if (++stage == nstages) { stage = 0; phase ^= 1; }
+      mbar_wait(mid_full, par);            // the intermediate tile is in shared memory (and D1 has been read)
+      mbar_wait(d2_empty, par ^ 1);        // the previous tile's D2 has been read
+      tc_fence_after();
+      if (elect_one()) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          umma_bf16(d2, ((uint64_t)dense_hi << 32) | (mid_lo + 2u * k), ((uint64_t)dense_hi << 32) | (w2_lo + 2u * k), idesc256,
+                    k != 0 ? 1u : 0u);
+        umma_commit(d2_full);
+      }
+      __syncwarp();
+      par ^= 1;
+    }
+  } else if (warp >= kEpiWarp0 + 8) {
+    // =========================== first epilogue (4 warps, one per TMEM lane quadrant) ===========================
+    // D1 -> shift, ReLU / masks -> bf16 -> `mid` tile.  Its own warps, so it runs while the other eight are still in
+    // the second epilogue of the previous tile.
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
+    const uint32_t mid0 = smem_u32(mid_smem);
+    const uint32_t bias0 = smem_u32(bias_smem);
+    const uint32_t row_off = (uint32_t)row * 128u;
+    const uint32_t sw = (uint32_t)(row & 7);
+    const int wi = row & 7, hi = row >> 3;
+    const bool relu = p.relu != 0;
+    const bool leader1 = threadIdx.x == (kEpiWarp0 + 8) * 32;
+    uint32_t par = 0;
+    pdl_wait();
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const FbCoord tc = fb_coord(p, tile);
+      const int w = tc.w0 + wi, h = tc.h0 + hi;
+      const bool valid = w < p.img_w && h < p.img_h && tc.n < p.img_n;
+      const long long pixel = ((long long)tc.n * p.img_h + h) * p.img_w + w;
+      uint32_t m1[2] = {0xffffffffu, 0xffffffffu};
+      if (p.mask1_in) {
+        const uint2 mm = valid ? __ldg(reinterpret_cast<const uint2*>(p.mask1_in + pixel * 2)) : make_uint2(0u, 0u);
+        m1[0] = mm.x; m1[1] = mm.y;
+      }
+      mbar_wait(d1_full, par);
+      tc_fence_after();
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        float f[32];
+        tmem_ld32f(tmem_base + lane_off + (uint32_t)(half * 32), f);
+        tmem_ld_wait();
+        if (half == 1) tc_fence_before();
+        if (p.bias1) {
+          const uint32_t bb = bias0 + (uint32_t)(half * 32 * 4);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 b = lds_f4(bb + 16u * i);
+            add2(f[4 * i], f[4 * i + 1], b.x, b.y);
+            add2(f[4 * i + 2], f[4 * i + 3], b.z, b.w);
+          }
+        }
+        if (relu && p.mask1_out) {
+          uint32_t bits = 0;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) bits |= (f[i] > 0.f ? 1u : 0u) << i;
+          if (valid) p.mask1_out[pixel * 2 + half] = bits;
+        }
+        if (p.mask1_in) {
+          const uint32_t mw = m1[half];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] = ((mw >> i) & 1u) ? f[i] : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          uint4 o;
+          if (relu) {
+            o.x = pack_bf16x2_relu(f[8 * i], f[8 * i + 1]); o.y = pack_bf16x2_relu(f[8 * i + 2], f[8 * i + 3]);
+            o.z = pack_bf16x2_relu(f[8 * i + 4], f[8 * i + 5]); o.w = pack_bf16x2_relu(f[8 * i + 6], f[8 * i + 7]);
+          } else {
+            o.x = pack_bf16x2(f[8 * i], f[8 * i + 1]); o.y = pack_bf16x2(f[8 * i + 2], f[8 * i + 3]);
+            o.z = pack_bf16x2(f[8 * i + 4], f[8 * i + 5]); o.w = pack_bf16x2(f[8 * i + 6], f[8 * i + 7]);
+          }
+          sts128(mid0 + row_off + ((((uint32_t)(half * 4 + i)) ^ sw) << 4), o);
+        }
+      }
+      fence_async_smem();                  // generic-proxy writes -> visible to the tensor core's operand reads
+      asm volatile("bar.sync 2, 128;" ::: "memory");
+      if (leader1) mbar_arrive(mid_full);
+      par ^= 1;
+    }
+  } else {
+    // =========================== second epilogue (8 warps) ===========================
+    const int ew = warp - kEpiWarp0;
+    const int quad = warp & 3;
+    const int half = ew >> 2;
+    const int row = quad * 32 + lane;
+    const int etid = threadIdx.x - kEpiWarp0 * 32;
+    const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
+    const uint32_t res0 = smem_u32(res_smem);
+    const uint32_t bias0 = smem_u32(bias_smem);
+    const uint32_t row_off = (uint32_t)row * 128u;
+    const uint32_t sw = (uint32_t)(row & 7);
+    const int wi = row & 7, hi = row >> 3;
+    const bool relu = p.relu != 0;
+    int rs = 0, prev_rs = -1;
+    uint32_t rphase = 0;
+    uint32_t par = 0;
+    pdl_wait();
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const FbCoord tc = fb_coord(p, tile);
+      const int w = tc.w0 + wi, h = tc.h0 + hi;
+      const bool valid = w < p.img_w && h < p.img_h && tc.n < p.img_n;
+      const long long pixel = ((long long)tc.n * p.img_h + h) * p.img_w + w;
+      // gate words of this thread's pixel for the four output sub-tiles (backward)
+      uint32_t m2[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        m2[j] = (p.mask2_in && valid) ? __ldg(p.mask2_in + ((long long)j * p.mask_pixels + pixel) * 2 + half) : 0xffffffffu;
+      // ---- second epilogue: D2 + residual + shift -> output.  The residual sub-tile arrives by TMA in a ring slot;
+      // each thread reads its row's 64 bytes from it, writes the result back IN PLACE, and the slot is TMA-stored.
+      mbar_wait(d2_full, par);
+      tc_fence_after();
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float f[32];
+        tmem_ld32f(tmem_base + lane_off + (uint32_t)(64 + j * 64 + half * 32), f);
+        mbar_wait(&res_full[rs], rphase);
+        const uint32_t slot = res0 + (uint32_t)(rs * kSubTileBytes) + row_off;
+        uint4 r[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) r[i] = lds128(slot + ((((uint32_t)(half * 4 + i)) ^ sw) << 4));
+        tmem_ld_wait();
+        if (j == 3) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(d2_empty);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint32_t u[4] = {r[i].x, r[i].y, r[i].z, r[i].w};
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            f[8 * i + 2 * q] += bf16_lo(u[q]);
+            f[8 * i + 2 * q + 1] += bf16_hi(u[q]);
+          }
+        }
+        if (p.bias2) {
+          const uint32_t bb = bias0 + (uint32_t)((64 + j * 64 + half * 32) * 4);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float4 b = lds_f4(bb + 16u * i);
+            add2(f[4 * i], f[4 * i + 1], b.x, b.y);
+            add2(f[4 * i + 2], f[4 * i + 3], b.z, b.w);
+          }
+        }
+        if (relu && p.mask2_out) {
+          uint32_t bits = 0;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) bits |= (f[i] > 0.f ? 1u : 0u) << i;
+          if (valid) p.mask2_out[((long long)j * p.mask_pixels + pixel) * 2 + half] = bits;
+        }
+        if (p.mask2_in) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] = ((m2[j] >> i) & 1u) ? f[i] : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          uint4 o;
+          if (relu) {
+            o.x = pack_bf16x2_relu(f[8 * i], f[8 * i + 1]); o.y = pack_bf16x2_relu(f[8 * i + 2], f[8 * i + 3]);
+            o.z = pack_bf16x2_relu(f[8 * i + 4], f[8 * i + 5]); o.w = pack_bf16x2_relu(f[8 * i + 6], f[8 * i + 7]);
+          } else {
+            o.x = pack_bf16x2(f[8 * i], f[8 * i + 1]); o.y = pack_bf16x2(f[8 * i + 2], f[8 * i + 3]);
+            o.z = pack_bf16x2(f[8 * i + 4], f[8 * i + 5]); o.w = pack_bf16x2(f[8 * i + 6], f[8 * i + 7]);
+          }
+          sts128(slot + ((((uint32_t)(half * 4 + i)) ^ sw) << 4), o);
+        }
+        fence_async_smem();
+        epi_bar();
+        if (etid == 0) {
+          tma_store_4d(&maps.out, res_smem + rs * kSubTileBytes, 64 * j, tc.w0, tc.h0, tc.n);
+          bulk_commit();
+          bulk_wait_read<1>();                 // the store issued one sub-tile ago has finished reading its slot
+          if (prev_rs >= 0) mbar_arrive(&res_empty[prev_rs]);
+          prev_rs = rs;
+        }
+        if (++rs == kFbResSlots) { rs = 0; rphase ^= 1; }
+      }
+      par ^= 1;
+    }
+    if (etid == 0) bulk_wait_read<0>();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
+  }
+}
+
 }  // namespace
+
+int launch_fused_block(const FusedBlockMaps& maps, FusedBlockParams& p, cudaStream_t stream) {
+  static bool configured = false;
+  if (!configured) {
+    ADV_CHECK_CUDA(cudaFuncSetAttribute(fused_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget));
+    configured = true;
+  }
+  ADV_CHECK_ARG(p.img_w % 8 == 0 && p.tiles_w == p.img_w / 8 && p.tiles_h == (p.img_h + 15) / 16 && p.tiles_n == p.img_n,
+                "fused_block: tiles are 8 x 16 pixels of one image");
+  const long long total = (long long)p.tiles_w * p.tiles_h * p.tiles_n;
+  if (total <= 0) return ADVB200_OK;
+  ADV_CHECK_ARG(total < (1ll << 20), "fused_block: too many tiles for the fast division");
+  p.total_tiles = (int)total;
+  auto magic = [](int d) { return (unsigned long long)(((1ull << 40) + (unsigned long long)d - 1) / (unsigned long long)d); };
+  p.magic_w = magic(p.tiles_w); p.magic_h = magic(p.tiles_h);
+  const int fixed = kFbW1Bytes + kFbW2Bytes + kFbMidBytes + kFbResSlots * kSubTileBytes + kFbBiasBytes + kFbBarBytes;
+  const int stages = 1;                                    // see the producer: one halo stage suffices
+  static_assert(kFbW1Bytes + kFbW2Bytes + kFbMidBytes + kFbResSlots * kSubTileBytes + kFbBiasBytes + kFbBarBytes +
+                    kFbHaloBytes <= kSmemBudget, "fused_block: shared memory carve-up");
+  p.stages = stages;
+  const int smem_bytes = fixed + stages * kFbHaloBytes;
+  const int grid = (int)(total < kNumSMs ? total : kNumSMs);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kFbThreads); cfg.dynamicSmemBytes = smem_bytes; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  static const bool no_pdl = getenv("ADVB200_NO_PDL") != nullptr;
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = no_pdl ? 0 : 1;
+  ADV_CHECK_CUDA(cudaLaunchKernelEx(&cfg, fused_block_kernel, maps, p));
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
 
 int launch_conv_gemm(int bn_cols, int pair, const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream) {
   ADV_CHECK_ARG(p.bw * p.bh * p.bn == kBlockM, "conv_gemm: tile must hold 128 pixels");

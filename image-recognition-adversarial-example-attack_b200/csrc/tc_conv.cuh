@@ -101,6 +101,38 @@ struct ConvGemmMaps {
 // the weight tensor map must then have a box of bn_cols/2 rows.  Fills p.stages.
 int launch_conv_gemm(int bn_cols, int pair, const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream);
 
+// ---- fused 3x3 (halo mode, 64 -> 64) + pointwise (64 -> 256, + residual) launch ------------------------------
+// One layer1 bottleneck tail in one kernel: forward  out = relu(W3 . relu(conv3x3(a, W2) + b2) + b3 + x),
+// backward  g_x = mask_x . (W1^T . (mask_a . dgrad3x3(g_b, W2)) + g_sum).  The 64-channel intermediate tile goes
+// TMEM -> registers -> bf16 -> a swizzled shared-memory tile that is the A operand of the second GEMM, so it never
+// touches HBM (nor does a second launch re-read it).  Tile = 8 x 16 pixels of one image.
+struct FusedBlockParams {
+  int tiles_w, tiles_h, tiles_n, total_tiles;
+  unsigned long long magic_w, magic_h;
+  int img_h, img_w, img_n;        // pixel grid (56 x 56 x N)
+  int tap_row[9];                 // halo-box row shift of tap t (rows of 128 B; box is 10 wide)
+  int tap_brow[9];                // first row of tap t's weights in the packed 3x3 matrix
+  const float* bias1;             // folded-BN shift of the 3x3 conv (64) or null
+  const float* bias2;             // shift of the pointwise conv (256) or null
+  int relu;                       // forward: ReLU after both convs
+  const uint32_t* mask1_in;       // backward: gates the intermediate gradient (ReLU bits of the 3x3's input act)
+  uint32_t* mask1_out;            // forward: ReLU bits of the intermediate activation
+  const uint32_t* mask2_in;       // backward: gates the output gradient (null for the first block)
+  uint32_t* mask2_out;            // forward: ReLU bits of the block output
+  long long mask_pixels;          // N * H * W
+  const void* res;                // bf16 NHWC [N,H,W,256]: residual (forward) / skip gradient (backward)
+  void* out;                      // bf16 NHWC [N,H,W,256]
+  int stages;                     // halo ring depth (launcher-filled)
+};
+struct FusedBlockMaps {
+  CUtensorMap a;      // [N,H,W,64] input of the 3x3, box (64, 10, 18, 1)
+  CUtensorMap w1;     // packed 3x3 weights [(tap, n) rows][64], box (64, 64)
+  CUtensorMap w2;     // packed pointwise weights [256 rows][64], box (64, 256)
+  CUtensorMap res;    // residual / skip gradient [N,H,W,256], box (64, 8, 16, 1)
+  CUtensorMap out;    // output [N,H,W,256], same box
+};
+int launch_fused_block(const FusedBlockMaps& maps, FusedBlockParams& p, cudaStream_t stream);
+
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda needed).
 // dims/strides innermost-first; strides in BYTES for dims 1..rank-1; bf16 elements; 128B swizzle.
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
