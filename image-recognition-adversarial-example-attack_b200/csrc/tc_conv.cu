@@ -763,6 +763,22 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
       const bool has_mask_in = p.mask_in != nullptr;
       const bool has_mask_out = relu && p.mask_out != nullptr;
       int oslot = 0;            // output staging slot of the sub-tile being produced
+      // ReLU gate words (backward) are fetched ONE TILE AHEAD: with the accumulator usually ready when the epilogue
+      // gets to it, a load issued in the same tile would expose its whole DRAM latency (ncu: 22 % of the samples).
+      auto load_gate = [&](int tile_, uint32_t (&mw)[kSub]) {
+        const TileCoord t2 = tile_coord<kPair>(p, tile_, BN, rank);
+        const int w2 = t2.w0 + wi, h2 = t2.h0 + hi, n2 = t2.n0 + ni;
+        const bool ok = (w2 < p.out_w) && (h2 < p.out_h) && (n2 < p.out_n);
+        const int ph2 = p.nclass > 1 ? p.cls_ph[t2.cls] : p.pix_ph, pw2 = p.nclass > 1 ? p.cls_pw[t2.cls] : p.pix_pw;
+        const long long px2 = ((long long)n2 * p.full_h + (h2 * p.pix_sub + ph2)) * p.full_w + (w2 * p.pix_sub + pw2);
+        const long long m0 = ((long long)(t2.c0 >> 6) * p.mask_pixels + px2) * 2 + half;
+#pragma unroll
+        for (int j = 0; j < kSub; ++j) mw[j] = ok ? __ldg(p.mask_in + m0 + (long long)j * p.mask_pixels * 2) : 0u;
+      };
+      uint32_t mnext[kSub];
+#pragma unroll
+      for (int j = 0; j < kSub; ++j) mnext[j] = 0xffffffffu;
+      if (has_mask_in && tile0 < total_tiles) load_gate(tile0, mnext);
 
       for (int tile = tile0; tile < total_tiles; tile += tile_step) {
         const TileCoord tc = tile_coord<kPair>(p, tile, BN, rank);
@@ -781,8 +797,8 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           bias_smem[(acc ^ 1) * 256 + etid] = __ldg(p.bias + tile_coord<kPair>(p, tile + tile_step, BN, rank).c0 + etid);
         uint32_t mword[kSub];
 #pragma unroll
-        for (int j = 0; j < kSub; ++j)
-          mword[j] = (has_mask_in && valid) ? __ldg(p.mask_in + mword0 + (long long)j * p.mask_pixels * 2) : 0xffffffffu;
+        for (int j = 0; j < kSub; ++j) mword[j] = mnext[j];
+        if (has_mask_in && tile + tile_step < total_tiles) load_gate(tile + tile_step, mnext);
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + half * 32);
@@ -1204,17 +1220,27 @@ fused_block_kernel(const __grid_constant__ FusedBlockMaps maps, const __grid_con
     int rs = 0, prev_rs = -1;
     uint32_t rphase = 0;
     uint32_t par = 0;
+    uint32_t m2n[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+    auto load_gate2 = [&](int tile_) {
+      const FbCoord t2 = fb_coord(p, tile_);
+      const int w2 = t2.w0 + wi, h2 = t2.h0 + hi;
+      const bool ok = w2 < p.img_w && h2 < p.img_h && t2.n < p.img_n;
+      const long long px2 = ((long long)t2.n * p.img_h + h2) * p.img_w + w2;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) m2n[j] = ok ? __ldg(p.mask2_in + ((long long)j * p.mask_pixels + px2) * 2 + half) : 0u;
+    };
     pdl_wait();
+    if (p.mask2_in && (int)blockIdx.x < total_tiles) load_gate2(blockIdx.x);
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const FbCoord tc = fb_coord(p, tile);
       const int w = tc.w0 + wi, h = tc.h0 + hi;
       const bool valid = w < p.img_w && h < p.img_h && tc.n < p.img_n;
       const long long pixel = ((long long)tc.n * p.img_h + h) * p.img_w + w;
-      // gate words of this thread's pixel for the four output sub-tiles (backward)
+      // gate words of this thread's pixel for the four output sub-tiles (backward), fetched one tile ahead
       uint32_t m2[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
-        m2[j] = (p.mask2_in && valid) ? __ldg(p.mask2_in + ((long long)j * p.mask_pixels + pixel) * 2 + half) : 0xffffffffu;
+      for (int j = 0; j < 4; ++j) m2[j] = m2n[j];
+      if (p.mask2_in && tile + (int)gridDim.x < total_tiles) load_gate2(tile + (int)gridDim.x);
       // ---- second epilogue: D2 + residual + shift -> output.  The residual sub-tile arrives by TMA in a ring slot;
       // each thread reads its row's 64 bytes from it, writes the result back IN PLACE, and the slot is TMA-stored.
       mbar_wait(d2_full, par);
