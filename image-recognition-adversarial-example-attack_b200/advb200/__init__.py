@@ -8,5 +8,5 @@ from .defenses import (  # noqa: F401
     calibrate_threshold_from_scores, defend_input, evaluate_defenses, evaluate_defenses_batched,
     is_adversarial_by_feature, run_attack, COUNTER_KEYS,
 )
-from .model import NativeResNet50, get_default_precision, native_model, set_default_precision  # noqa: F401
+from .model import NativeResNet50, NativeResNet50Module, get_default_precision, native_model, set_default_precision  # noqa: F401
 from .pipeline import HostBatchPipeline  # noqa: F401

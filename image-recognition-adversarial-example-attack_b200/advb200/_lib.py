@@ -36,6 +36,7 @@ SIGNATURES = {
     "advb200_input_grad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float,
                                    c_float, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_int64, c_void_p]),
+    "advb200_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_void_p]),
     "advb200_attack_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_float,
                                     c_float, c_float, c_void_p, c_void_p, c_int64, c_void_p]),
     "advb200_linf_step_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_float, c_int64, c_int, c_void_p]),

@@ -99,6 +99,7 @@ class NativeResNet50:
         self._ws = {}   # n -> (raw tensor, aligned ptr, bytes)
         self._finalizer = weakref.finalize(self, self.lib.advb200_model_destroy, handle)
         self.max_chunk = _MAX_CHUNK
+        self._gen = 0   # bumped by every native call: tells the autograd wrapper whether its forward state survives
 
     # -- workspace ---------------------------------------------------------------------------
     def _workspace(self, n: int):
@@ -140,6 +141,7 @@ class NativeResNet50:
         x = self._check_x(x)
         mean, std = self._vec3(mean, x.device), self._vec3(std, x.device)
         n = x.shape[0]
+        self._gen += 1
         out = {}
         if want_logits and not stop_at_layer3:
             out["logits"] = torch.empty((n, 1000), dtype=torch.float32, device=x.device)
@@ -165,6 +167,7 @@ class NativeResNet50:
         x = self._check_x(x)
         mean, std = self._vec3(mean, x.device), self._vec3(std, x.device)
         n = x.shape[0]
+        self._gen += 1
         y_cmp = y_cmp.detach().to(device=x.device, dtype=torch.int64).contiguous()
         if y_cmp.shape != (n,):
             raise ValueError("labels must have shape [N]")
@@ -199,6 +202,25 @@ class NativeResNet50:
         return out
 
 
+    # -- backward for a caller-supplied dlogits ------------------------------------------------
+    def backward(self, dlogits, std, n: int, grad_out=None):
+        """Input gradient [n,3,224,224] for dlogits [n,1000], through the state the immediately preceding
+        full `forward` of the same (single-chunk) batch left in the workspace (advb200_backward)."""
+        if n > self.max_chunk:
+            raise ValueError("backward works on one chunk: n <= max_chunk")
+        dl = dlogits.detach().to(device=self.device, dtype=torch.float32).contiguous()
+        if dl.shape != (n, 1000):
+            raise ValueError("dlogits must have shape [N, 1000]")
+        std = self._vec3(std, self.device)
+        self._gen += 1
+        grad = grad_out if grad_out is not None else torch.empty((n, 3, 224, 224), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            _, ws, nbytes = self._workspace(n)
+            rc = self.lib.advb200_backward(self.handle, _lib.ptr(dl), _lib.ptr(std), n, _lib.ptr(grad), c_void_p(ws),
+                                           nbytes, _lib.stream_ptr())
+            _lib.check(rc, "advb200_backward")
+        return grad
+
     # -- one fused attack step (bf16 mode) ----------------------------------------------------
     def attack_step(self, x_adv, x_orig, mean, std, y_true, *, alpha, eps, inv_n_global=None):
         """x_adv <- clamp(project(x_adv + alpha*sign(grad CE(x_adv)))) in place (attack.py:61-63; x_orig=None:
@@ -209,6 +231,7 @@ class NativeResNet50:
         if x_adv.dtype != torch.float32 or not x_adv.is_contiguous() or not x_adv.is_cuda:
             raise ValueError("x_adv must be a contiguous fp32 CUDA tensor (it is updated in place)")
         self._check_x(x_adv)
+        self._gen += 1
         mean, std = self._vec3(mean, x_adv.device), self._vec3(std, x_adv.device)
         n = x_adv.shape[0]
         y = y_true.detach().to(device=x_adv.device, dtype=torch.int64).contiguous()
@@ -258,3 +281,66 @@ def native_model(model, precision: Optional[str] = None) -> NativeResNet50:
         nm = NativeResNet50(model, precision=precision, device=dev)
         per[precision] = nm
     return nm
+
+
+class _LogitsFn(torch.autograd.Function):
+    """logits = native_forward(x) with x already normalised by the caller; backward = advb200_backward.  The
+    workspace holds the state of ONE forward: if another native call ran in between, the forward of the chunk is
+    run again before its backward (cheaper than keeping 5.7 GB of state per outstanding graph)."""
+
+    @staticmethod
+    def forward(ctx, x, owner):
+        nm = owner.native
+        xin = nm._check_x(x)
+        ctx.owner = owner
+        ctx.save_for_backward(xin)
+        out = nm.forward(xin, owner._zero, owner._one)["logits"]
+        ctx.gen = nm._gen
+        ctx.in_dtype = x.dtype
+        return out
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        owner = ctx.owner
+        nm = owner.native
+        (xin,) = ctx.saved_tensors
+        n = xin.shape[0]
+        grad = torch.empty_like(xin)
+        dlogits = dlogits.contiguous()
+        single = n <= nm.max_chunk
+        for lo in range(0, n, nm.max_chunk):
+            hi = min(n, lo + nm.max_chunk)
+            if not (single and ctx.gen == nm._gen):
+                nm.forward(xin[lo:hi], owner._zero, owner._one, want_logits=False, want_preds=True)
+            nm.backward(dlogits[lo:hi], owner._one, hi - lo, grad_out=grad[lo:hi])   # bumps _gen: state consumed
+        return grad.to(ctx.in_dtype), None
+
+
+class NativeResNet50Module(torch.nn.Module):
+    """`nn.Module` face of the native model for UNMODIFIED callers that write
+    `logits = model(normalize_batch(x, mean, std)); g = torch.autograd.grad(loss, x)` themselves
+    (visualized_attacks.py:337-358, defense_experiments.py:458-479).
+
+    Takes the normalised batch [N,3,224,224] (the normalisation stays in the caller's autograd graph), returns
+    fp32 logits [N,1000]; differentiable with respect to its input only (frozen weights).
+    There is no CPU fallback: inputs must be CUDA tensors."""
+
+    def __init__(self, model, precision: Optional[str] = None):
+        super().__init__()
+        self.native = native_model(model, precision)
+        dev = self.native.device
+        self._zero = torch.zeros(3, dtype=torch.float32, device=dev)
+        self._one = torch.ones(3, dtype=torch.float32, device=dev)
+        self.training = False
+
+    def train(self, mode: bool = True):
+        if mode:
+            raise RuntimeError("the native model is an eval-mode, frozen-weight classifier")
+        return self
+
+    def forward(self, x_normalised: torch.Tensor) -> torch.Tensor:
+        if x_normalised.ndim != 4:
+            raise ValueError("x must be a 4D tensor with shape [N, C, H, W]")
+        if torch.is_grad_enabled() and x_normalised.requires_grad:
+            return _LogitsFn.apply(x_normalised, self)
+        return self.native.forward(x_normalised, self._zero, self._one)["logits"]

@@ -651,6 +651,7 @@ struct advb200_model {
 
   // ---- plan (per batch size + workspace) ----
   int plan_n = -1;
+  int fwd_state_n = -1;         // batch whose full-forward state (masks, pool indices, layer4 output) the workspace holds
   bool hcol16 = true;           // stem operand layout of the current plan
   void* plan_ws = nullptr;
   size_t esz = 2;
@@ -1146,6 +1147,7 @@ int ensure_plan(advb200_model* m, int n, void* ws, int64_t ws_bytes, cudaStream_
   if (ws_bytes < need) return fail(ADVB200_ERR_ARG, "workspace too small: need " + std::to_string(need));
   int rc = ADVB200_OK;
   plan(m, n, ws, &rc, st, true);
+  m->fwd_state_n = -1;
   if (rc) { m->plan_n = -1; return rc; }
   m->plan_n = n; m->plan_ws = ws;
   return ADVB200_OK;
@@ -1169,13 +1171,16 @@ int forward_impl(advb200_model* m, const float* x, const float* mean3, const flo
     else rc = launch_detector_score<float>((const float*)m->l3out.p, score_out, n, 196, 1024, st);
     if (rc) return rc;
   }
+  m->fwd_state_n = -1;
   if (stop_at_layer3) return ADVB200_OK;
   if ((rc = run_ops(m->ops_l4, st))) return rc;
   if (tc) rc = launch_avgpool_fwd<bf16>((const bf16*)m->l4out.p, m->feat, n, 49, kFeat, st);
   else rc = launch_avgpool_fwd<float>((const float*)m->l4out.p, m->feat, n, 49, kFeat, st);
   if (rc) return rc;
   // fc forward: logits = feat * W^T + b   (fp32 in both modes)
-  return launch_fc_nt(m->feat, m->fc_w, m->fc_b, m->logits, m->fc_part, n, kClasses, kFeat, st);
+  rc = launch_fc_nt(m->feat, m->fc_w, m->fc_b, m->logits, m->fc_part, n, kClasses, kFeat, st);
+  if (!rc) m->fwd_state_n = n;
+  return rc;
 }
 
 }  // namespace
@@ -1354,6 +1359,18 @@ static int input_grad_impl(advb200_model* m, const float* x, const float* mean3,
                            float* logits_out, int64_t* preds_out, float* loss_out, uint8_t* success_out,
                            float* grad_x_out, float* upd_x, const float* upd_x0, float upd_alpha, float upd_eps,
                            void* workspace, int64_t workspace_bytes, void* stream);
+static int backward_impl(advb200_model* m, const float* dlogits, const float* std3, int n, float* grad_x_out,
+                         float* upd_x, const float* upd_x0, float upd_alpha, float upd_eps, cudaStream_t st);
+
+int advb200_backward(advb200_model* m, const float* dlogits, const float* std3, int n, float* grad_x_out,
+                     void* workspace, int64_t workspace_bytes, void* stream) {
+  ADV_CHECK_ARG(m && dlogits && std3 && grad_x_out && workspace, "backward: null argument");
+  (void)workspace_bytes;
+  if (m->plan_n != n || m->plan_ws != workspace || m->fwd_state_n != n)
+    return fail(ADVB200_ERR_ARG, "backward: the workspace does not hold the state of an advb200_forward of this batch "
+                                 "(call advb200_forward with the same n and workspace first)");
+  return backward_impl(m, dlogits, std3, n, grad_x_out, nullptr, nullptr, 0.f, 0.f, as_stream(stream));
+}
 
 int advb200_input_grad(advb200_model* m, const float* x, const float* mean3, const float* std3,
                        const int64_t* y_cmp, int n, int loss_kind, float c, float kappa, float inv_n_global,
@@ -1386,7 +1403,6 @@ static int input_grad_impl(advb200_model* m, const float* x, const float* mean3,
   cudaStream_t st = as_stream(stream);
   int rc = ensure_plan(m, n, workspace, workspace_bytes, st);
   if (rc) return rc;
-  const bool tc = m->precision == ADVB200_PREC_BF16;
   if ((rc = forward_impl(m, x, mean3, std3, n, false, nullptr, st))) return rc;
   if (logits_out)
     ADV_CHECK_CUDA(cudaMemcpyAsync(logits_out, m->logits, (size_t)n * kClasses * 4, cudaMemcpyDeviceToDevice, st));
@@ -1394,8 +1410,17 @@ static int input_grad_impl(advb200_model* m, const float* x, const float* mean3,
   if ((rc = launch_loss_grad(m->logits, y_cmp, n, kClasses, loss_kind, c, kappa, scale, m->dlogits, preds_out,
                              loss_out, success_out, st)))
     return rc;
+  return backward_impl(m, m->dlogits, std3, n, grad_x_out, upd_x, upd_x0, upd_alpha, upd_eps, st);
+}
+
+// dlogits [n,1000] fp32 -> input gradient, through the state the last full forward left in the workspace
+static int backward_impl(advb200_model* m, const float* dlogits, const float* std3, int n, float* grad_x_out,
+                         float* upd_x, const float* upd_x0, float upd_alpha, float upd_eps, cudaStream_t st) {
+  const bool tc = m->precision == ADVB200_PREC_BF16;
+  int rc;
+  m->fwd_state_n = -1;   // gradient buffers may reuse activation space: one backward per forward
   // fc input gradient: dfeat = dlogits * W
-  if ((rc = launch_fc_nt(m->dlogits, m->fc_wt, nullptr, m->dfeat, m->fc_part, n, kFeat, kClasses, st))) return rc;
+  if ((rc = launch_fc_nt(dlogits, m->fc_wt, nullptr, m->dfeat, m->fc_part, n, kFeat, kClasses, st))) return rc;
   if (tc) rc = launch_avgpool_bwd<bf16>(m->dfeat, (const bf16*)m->l4out.p, (bf16*)m->g_top, n, 49, kFeat, st);
   else rc = launch_avgpool_bwd<float>(m->dfeat, (const float*)m->l4out.p, (float*)m->g_top, n, 49, kFeat, st);
   if (rc) return rc;

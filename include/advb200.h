@@ -110,6 +110,15 @@ int advb200_cw_init_f32(const float* x, float* x0, float* w, float* m, float* v,
                         float* best_adv, float* best_l2, uint8_t* best_success, float* l2_partials,
                         int n_img, int64_t elems_per_img, void* stream);
 
+/* Input gradient for a caller-supplied dlogits [N,1000] fp32 (the backward half of advb200_input_grad, for callers
+ * that compute their own loss on the logits: visualized_attacks.py:337-358, defense_experiments.py:458-479 run
+ * `autograd.grad(loss, x)` through `model(normalize_batch(x))` themselves).  Uses the ReLU bit masks, pool indices
+ * and layer4 output that the immediately preceding advb200_forward(n, same workspace, full depth) left in the
+ * workspace; ADVB200_ERR_ARG if there is no such state.  One backward per forward (the gradient buffers may reuse
+ * activation space).  grad_x_out [N,3,224,224] fp32 = d(sum(dlogits*logits))/dx, already divided by std3. */
+int advb200_backward(advb200_model* m, const float* dlogits, const float* std3, int n, float* grad_x_out,
+                     void* workspace, int64_t workspace_bytes, void* stream);
+
 /* One fused attack step (bf16 mode): forward + CE input gradient as advb200_input_grad(CE_MEAN), with the sign
  * step, eps-ball projection and [0,1] clamp of attack.py:61-63 (x_orig != NULL) or attack.py:33-34
  * (x_orig == NULL: FGSM, no projection) applied to x_adv IN PLACE by the epilogue of the stem's input-gradient
