@@ -29,9 +29,12 @@ def quantize(x: np.ndarray, levels: int = 16) -> np.ndarray:
     return (np.rint((np.clip(x, 0.0, 1.0) * lm1).astype(np.float32)) / lm1).astype(np.float32)
 
 
-def defend_input(x: np.ndarray) -> np.ndarray:
-    """defense_experiments.py:210-217 with the JPEG branch off (its default, :173)."""
+def defend_input(x: np.ndarray, use_jpeg: bool = False, jpeg_quality: int = 75) -> np.ndarray:
+    """defense_experiments.py:210-217; the JPEG branch (:215-216) is off by default (:173)."""
     y = quantize(smooth3x3(np.clip(np.asarray(x, dtype=np.float32), 0.0, 1.0)), 16)
+    if use_jpeg:
+        from . import jpeg_ref
+        y = jpeg_ref.jpeg_compress_batch(y, jpeg_quality)
     return np.clip(y, 0.0, 1.0)
 
 

@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 import torch
 
-from oracle import attacks_ref, defenses_ref, resnet50_ref, weights
+from oracle import attacks_ref, defenses_ref, jpeg_ref, resnet50_ref, weights
 
 
 def _tiny(golden_dir):
@@ -47,6 +47,47 @@ def test_defenses_match_reference_bitwise(golden_dir):
     assert np.array_equal(defenses_ref.quantize(g["x"], 16), g["quant16"])
     assert np.array_equal(defenses_ref.quantize(g["x"], 4), g["quant4"])
     assert np.array_equal(defenses_ref.defend_input(g["x"]), g["defend"])
+
+
+JPEG_CASES = ["img224", "odd37x51", "rand17x16", "one_pixel", "q30_64x48", "q95_40x40", "saturated32", "q50_30x23"]
+
+
+def jpeg_case(g, name):
+    x = g["img224_u8"].astype(np.float32) / np.float32(255) if name == "img224" else g[name + "_x"]
+    return x, int(g[name + "_q"]), g[name + "_out_u8"]
+
+
+@pytest.mark.parametrize("name", JPEG_CASES)
+def test_jpeg_roundtrip_matches_reference_bitwise(golden_dir, name):
+    """The libjpeg pipeline restated in oracle/jpeg_ref.py against the reference's _jpeg_compress_batch on PIL
+    (tests/golden/jpeg_cases.npz, oracle/gen_golden_jpeg.py): every decoded byte identical, all sizes / qualities."""
+    x, q, want = jpeg_case(np.load(golden_dir / "jpeg_cases.npz"), name)
+    got = jpeg_ref.jpeg_compress_batch(x, q)
+    assert np.array_equal(got, want.astype(np.float32) / np.float32(255))
+
+
+def test_defend_input_with_jpeg_matches_reference_bitwise(golden_dir):
+    g = np.load(golden_dir / "jpeg_cases.npz")
+    assert np.array_equal(defenses_ref.defend_input(g["defend_x"], use_jpeg=True, jpeg_quality=75), g["defend_jpeg_out"])
+
+
+def test_jpeg_building_blocks():
+    qy, qc = jpeg_ref.quant_tables(75)
+    assert qy[0, 0] == 8 and qy[7, 7] == 50 and qc[0, 0] == 9 and qc[7, 7] == 50      # Annex K scaled by 50 %
+    assert jpeg_ref.quant_tables(100)[0].max() == 1 and jpeg_ref.quant_tables(1)[0].max() == 255
+    # a flat block survives the codec exactly (DC only), and the DCT pair is near-inverse without quantisation
+    flat = np.full((1, 1, 8, 8), 77, dtype=np.int64)
+    assert np.array_equal(jpeg_ref.idct_islow(jpeg_ref.fdct_islow(flat - 128) // 8), flat)
+    rng = np.random.default_rng(0)
+    blk = rng.integers(0, 256, size=(4, 4, 8, 8))
+    rec = jpeg_ref.idct_islow(np.round(jpeg_ref.fdct_islow(blk - 128) / 8).astype(np.int64))
+    assert np.abs(rec - blk).max() <= 2
+    # fancy upsampling of a constant plane is the constant; grey RGB maps to Y = v, Cb = Cr = 128 and back
+    assert np.array_equal(jpeg_ref.h2v2_fancy_upsample(np.full((3, 5), 9)), np.full((6, 10), 9))
+    grey = np.repeat(np.arange(256, dtype=np.uint8)[:, None, None], 3, axis=2)
+    y, cb, cr = jpeg_ref.rgb_to_ycc(grey)
+    assert np.array_equal(y[:, 0], np.arange(256)) and (cb == 128).all() and (cr == 128).all()
+    assert np.array_equal(jpeg_ref.ycc_to_rgb(y, cb, cr), grey)
 
 
 @pytest.fixture(scope="module")
