@@ -21,8 +21,7 @@ from . import _lib
 from .attack import cw_l2_attack, fgsm_attack, pgd_linf_attack
 from .model import native_model
 
-# module-level JPEG switches kept for interface parity (defense_experiments.py:173-174); the JPEG
-# branch itself (PIL round trip on the host) is outside the hot path and not provided natively.
+# module-level JPEG switches, as in the reference (defense_experiments.py:173-174; set by --use_jpeg / --jpeg_quality)
 _DEFENSE_USE_JPEG = False
 _DEFENSE_JPEG_QUALITY = 75
 
@@ -61,15 +60,37 @@ def _defense_quantization(x: torch.Tensor, levels: int = 16) -> torch.Tensor:
     return out
 
 
+def _jpeg_compress_batch(x: torch.Tensor, quality: int) -> torch.Tensor:
+    """defense_experiments.py:188-207 without the host round trip: the PIL/libjpeg sample pipeline (4:2:0, islow
+    DCT, quality-scaled tables, fancy upsampling) runs on the device, bit-exact with the reference's PIL path."""
+    if x.ndim != 4 or x.shape[1] != 3:
+        raise ValueError("x must be a 4D RGB tensor with shape [N, 3, H, W]")
+    if not x.is_cuda:
+        raise ValueError("x must be a CUDA tensor (no CPU fallback)")
+    xc = x.detach().to(torch.float32).contiguous()
+    n, _, h, w = xc.shape
+    out = torch.empty_like(xc)
+    if n == 0 or h == 0 or w == 0:
+        return out.to(x.dtype)
+    lib = _lib.load()
+    with torch.cuda.device(xc.device):
+        nbytes = int(lib.advb200_jpeg_scratch_bytes(n, h, w))
+        scratch = torch.empty(nbytes, dtype=torch.uint8, device=xc.device)
+        rc = lib.advb200_jpeg_roundtrip_f32(_lib.ptr(xc), _lib.ptr(out), n, h, w, int(quality), _lib.ptr(scratch),
+                                            nbytes, _lib.stream_ptr())
+    _lib.check(rc, "advb200_jpeg_roundtrip_f32")
+    return out.to(x.dtype)
+
+
 def defend_input(x: torch.Tensor) -> torch.Tensor:
-    if _DEFENSE_USE_JPEG:
-        raise NotImplementedError("the JPEG branch (defense_experiments.py:188-207) is outside the native hot path")
     xc, planes, h, w = _as_planes(x)
     out = torch.empty_like(xc)
     with torch.cuda.device(xc.device):
         rc = _lib.load().advb200_defend_input_f32(_lib.ptr(xc), _lib.ptr(out), planes, h, w, 16,
                                                   _lib.stream_ptr())
     _lib.check(rc, "advb200_defend_input_f32")
+    if _DEFENSE_USE_JPEG:                      # defense_experiments.py:215-216 (the trailing clamp is a no-op)
+        out = _jpeg_compress_batch(out, _DEFENSE_JPEG_QUALITY)
     return out
 
 

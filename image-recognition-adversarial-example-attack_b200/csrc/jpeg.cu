@@ -1,0 +1,299 @@
+// JPEG defense on the GPU (defense_experiments.py:188-207 `_jpeg_compress_batch`).
+//
+// The reference round-trips every image through PIL's JPEG encoder and decoder on the host.  Entropy coding is
+// lossless, so the pixels that come back are a pure function of the baseline-JPEG SAMPLE pipeline of libjpeg
+// (4:2:0, quality-scaled Annex-K tables, jfdctint / jidctint "islow" integer DCTs, triangle chroma upsampling).
+// That pipeline is restated here in integer arithmetic, bit for bit (oracle/jpeg_ref.py is the checker, pinned
+// against PIL by tests/golden/jpeg_cases.npz):
+//
+//   kernel 1 (jpeg_codec_kernel): one CTA per strip of 16 rows x 256 columns (16 MCUs) of one image:
+//     fp32 NCHW -> uint8 (x*255 truncated) -> YCbCr -> smem; 2x2 chroma box filter; then ONE THREAD PER 8x8 BLOCK
+//     keeps the block in registers through fdct -> quantise -> dequantise -> idct -> range limit and writes the
+//     decoded bytes back; decoded Y (full size) and Cb/Cr (half size) go to a uint8 scratch (1.5 B/pixel).
+//   kernel 2 (jpeg_upsample_rgb_kernel): "fancy" h2v2 upsampling of the decoded chroma (needs the neighbouring
+//     blocks' samples, hence the second pass), YCbCr -> RGB, /255 -> fp32 NCHW.
+//
+// HBM-bound integer/byte work: 12 B/pixel read + 12 B/pixel written + 3 B/pixel of scratch traffic = 27 B/pixel
+// algorithmic (24 if the scratch stays in L2, which it does at 224x224: 19 MB per 256 images).
+#include "common.cuh"
+
+namespace advb200 {
+namespace {
+
+constexpr int kStripW = 256;          // pixels per strip (16 MCUs)
+constexpr int kCodecThreads = 128;
+
+struct JpegTables {
+  uint32_t recip[2][64];   // ceil(2^32 / (q << 3)): exact division of the (< 2^16) magnitudes by umulhi
+  uint16_t q[2][64];       // quantisation step (luma, chroma), natural (row-major) order
+};
+
+__device__ __forceinline__ int descale(int x, int n) { return (x + (1 << (n - 1))) >> n; }
+
+constexpr int F_0_298 = 2446, F_0_390 = 3196, F_0_541 = 4433, F_0_765 = 6270, F_0_899 = 7373, F_1_175 = 9633,
+              F_1_501 = 12299, F_1_847 = 15137, F_1_961 = 16069, F_2_053 = 16819, F_2_562 = 20995, F_3_072 = 25172;
+
+// jfdctint.c, one 1-D pass over d[0], d[S], ..., d[7S].  kFirst: row pass (results scaled up by 4).
+template <int S, bool kFirst>
+__device__ __forceinline__ void fdct8(int* d) {
+  const int t0 = d[0] + d[7 * S], t7 = d[0] - d[7 * S], t1 = d[S] + d[6 * S], t6 = d[S] - d[6 * S];
+  const int t2 = d[2 * S] + d[5 * S], t5 = d[2 * S] - d[5 * S], t3 = d[3 * S] + d[4 * S], t4 = d[3 * S] - d[4 * S];
+  const int t10 = t0 + t3, t13 = t0 - t3, t11 = t1 + t2, t12 = t1 - t2;
+  constexpr int sh = kFirst ? 13 - 2 : 13 + 2;
+  if (kFirst) { d[0] = (t10 + t11) << 2; d[4 * S] = (t10 - t11) << 2; }
+  else { d[0] = descale(t10 + t11, 2); d[4 * S] = descale(t10 - t11, 2); }
+  int z1 = (t12 + t13) * F_0_541;
+  d[2 * S] = descale(z1 + t13 * F_0_765, sh);
+  d[6 * S] = descale(z1 - t12 * F_1_847, sh);
+  z1 = t4 + t7;
+  int z2 = t5 + t6, z3 = t4 + t6, z4 = t5 + t7;
+  const int z5 = (z3 + z4) * F_1_175;
+  const int a4 = t4 * F_0_298, a5 = t5 * F_2_053, a6 = t6 * F_3_072, a7 = t7 * F_1_501;
+  z1 = -z1 * F_0_899; z2 = -z2 * F_2_562; z3 = -z3 * F_1_961 + z5; z4 = -z4 * F_0_390 + z5;
+  d[7 * S] = descale(a4 + z1 + z3, sh);
+  d[5 * S] = descale(a5 + z2 + z4, sh);
+  d[3 * S] = descale(a6 + z2 + z3, sh);
+  d[S] = descale(a7 + z1 + z4, sh);
+}
+
+// jidctint.c, one 1-D pass.  kFirst: column pass into the workspace; second pass descales by 18 bits.
+template <int S, bool kFirst>
+__device__ __forceinline__ void idct8(int* d) {
+  int z2 = d[2 * S], z3 = d[6 * S];
+  int z1 = (z2 + z3) * F_0_541;
+  int t2 = z1 - z3 * F_1_847, t3 = z1 + z2 * F_0_765;
+  int t0 = (d[0] + d[4 * S]) << 13, t1 = (d[0] - d[4 * S]) << 13;
+  const int t10 = t0 + t3, t13 = t0 - t3, t11 = t1 + t2, t12 = t1 - t2;
+  t0 = d[7 * S]; t1 = d[5 * S]; t2 = d[3 * S]; t3 = d[S];
+  z1 = t0 + t3; z2 = t1 + t2; z3 = t0 + t2;
+  int z4 = t1 + t3;
+  const int z5 = (z3 + z4) * F_1_175;
+  t0 *= F_0_298; t1 *= F_2_053; t2 *= F_3_072; t3 *= F_1_501;
+  z1 = -z1 * F_0_899; z2 = -z2 * F_2_562; z3 = -z3 * F_1_961 + z5; z4 = -z4 * F_0_390 + z5;
+  t0 += z1 + z3; t1 += z2 + z4; t2 += z2 + z3; t3 += z1 + z4;
+  constexpr int sh = kFirst ? 13 - 2 : 13 + 2 + 3;
+  d[0] = descale(t10 + t3, sh); d[7 * S] = descale(t10 - t3, sh);
+  d[S] = descale(t11 + t2, sh); d[6 * S] = descale(t11 - t2, sh);
+  d[2 * S] = descale(t12 + t1, sh); d[5 * S] = descale(t12 - t1, sh);
+  d[3 * S] = descale(t13 + t0, sh); d[4 * S] = descale(t13 - t0, sh);
+}
+
+// one 8x8 block, in place in shared memory (rows `pitch` bytes apart): the whole codec in registers
+__device__ __forceinline__ void codec_block(uint8_t* blk, int pitch, const JpegTables& tb, int comp) {
+  int d[64];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    const uint2 v = *reinterpret_cast<const uint2*>(blk + r * pitch);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      d[r * 8 + k] = (int)((v.x >> (8 * k)) & 0xffu) - 128;
+      d[r * 8 + 4 + k] = (int)((v.y >> (8 * k)) & 0xffu) - 128;
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < 8; ++r) fdct8<1, true>(d + r * 8);
+#pragma unroll
+  for (int c = 0; c < 8; ++c) fdct8<8, false>(d + c);
+  // jcdctmgr.c: divisor q<<3 (the islow DCT leaves a factor 8), round half away from zero; then dequantise
+#pragma unroll
+  for (int i = 0; i < 64; ++i) {
+    const int q = tb.q[comp][i];
+    const int v = d[i];
+    const uint32_t a = (uint32_t)(v < 0 ? -v : v) + (uint32_t)(q << 2);
+    const int mag = (int)__umulhi(a, tb.recip[comp][i]);
+    d[i] = (v < 0 ? -mag : mag) * q;
+  }
+#pragma unroll
+  for (int c = 0; c < 8; ++c) idct8<8, true>(d + c);
+#pragma unroll
+  for (int r = 0; r < 8; ++r) idct8<1, false>(d + r * 8);
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    uint2 v = make_uint2(0u, 0u);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      v.x |= (uint32_t)min(max(d[r * 8 + k] + 128, 0), 255) << (8 * k);
+      v.y |= (uint32_t)min(max(d[r * 8 + 4 + k] + 128, 0), 255) << (8 * k);
+    }
+    *reinterpret_cast<uint2*>(blk + r * pitch) = v;
+  }
+}
+
+__device__ __forceinline__ int to_u8(float x) {
+  // ToPILImage on a float tensor: clamp (done by the caller of the reference function), mul(255), .byte() = truncation
+  return (int)(fminf(fmaxf(x, 0.f), 1.f) * 255.f);
+}
+
+__global__ void __launch_bounds__(kCodecThreads)
+jpeg_codec_kernel(const float* __restrict__ x, uint8_t* __restrict__ ydec, uint8_t* __restrict__ cbdec,
+                  uint8_t* __restrict__ crdec, int h, int w, int strips, int mcu_rows, const JpegTables tb) {
+  __shared__ __align__(16) uint8_t sY[16][kStripW];
+  __shared__ __align__(16) uint8_t sCbF[16][kStripW];     // full-resolution chroma of the strip
+  __shared__ __align__(16) uint8_t sCrF[16][kStripW];
+  __shared__ __align__(16) uint8_t sC[2][8][kStripW / 2];  // downsampled, then decoded in place
+  const int strip = blockIdx.x % strips;
+  const int mr = (blockIdx.x / strips) % mcu_rows;
+  const long long img = blockIdx.x / (strips * mcu_rows);
+  const int col0 = strip * kStripW, row0 = mr * 16;
+  const int hc = (h + 1) >> 1, wc = (w + 1) >> 1;
+  const float* xr = x + img * 3 * (long long)h * w;
+  const float* xg = xr + (long long)h * w;
+  const float* xb = xg + (long long)h * w;
+
+  // ---- load, quantise to bytes, colour-convert (jccolor.c); rows / columns past the image replicate its edge
+  for (int i = threadIdx.x; i < 16 * kStripW; i += kCodecThreads) {
+    const int r = i / kStripW, c = i % kStripW;
+    const int gr = min(row0 + r, h - 1), gc = min(col0 + c, w - 1);
+    const long long o = (long long)gr * w + gc;
+    const int R = to_u8(__ldg(xr + o)), G = to_u8(__ldg(xg + o)), B = to_u8(__ldg(xb + o));
+    sY[r][c] = (uint8_t)((19595 * R + 38470 * G + 7471 * B + 32768) >> 16);
+    sCbF[r][c] = (uint8_t)((-11059 * R - 21709 * G + 32768 * B + (128 << 16) + 32767) >> 16);
+    sCrF[r][c] = (uint8_t)((32768 * R - 27439 * G - 5329 * B + (128 << 16) + 32767) >> 16);
+  }
+  __syncthreads();
+  // ---- h2v2 box filter with the alternating 1,2 bias (jcsample.c); chroma rows past the real chroma height
+  //      replicate the last real chroma row (jcprepct.c pads AFTER downsampling)
+  for (int i = threadIdx.x; i < 2 * 8 * (kStripW / 2); i += kCodecThreads) {
+    const int comp = i / (8 * (kStripW / 2)), rr = (i / (kStripW / 2)) % 8, cc = i % (kStripW / 2);
+    const int cr_real = min(mr * 8 + rr, hc - 1) - mr * 8;
+    const uint8_t(*f)[kStripW] = comp ? sCrF : sCbF;
+    const int s = f[2 * cr_real][2 * cc] + f[2 * cr_real][2 * cc + 1] + f[2 * cr_real + 1][2 * cc] +
+                  f[2 * cr_real + 1][2 * cc + 1] + 1 + (cc & 1);
+    sC[comp][rr][cc] = (uint8_t)(s >> 2);
+  }
+  __syncthreads();
+  // ---- one thread per 8x8 block: 64 luma blocks, 16 + 16 chroma blocks
+  {
+    const int t = threadIdx.x;
+    if (t < 64) {
+      const int by = t >> 5, bx = t & 31;
+      if (col0 + bx * 8 < w && row0 + by * 8 < h) codec_block(&sY[by * 8][bx * 8], kStripW, tb, 0);
+    } else if (t < 96) {
+      const int comp = (t - 64) >> 4, bx = t & 15;
+      if ((col0 >> 1) + bx * 8 < wc) codec_block(&sC[comp][0][bx * 8], kStripW / 2, tb, 1);
+    }
+  }
+  __syncthreads();
+  // ---- decoded bytes -> scratch (real pixels only)
+  uint8_t* yo = ydec + img * (long long)h * w;
+  for (int i = threadIdx.x; i < 16 * kStripW; i += kCodecThreads) {
+    const int r = i / kStripW, c = i % kStripW;
+    if (row0 + r < h && col0 + c < w) yo[(long long)(row0 + r) * w + col0 + c] = sY[r][c];
+  }
+  for (int i = threadIdx.x; i < 2 * 8 * (kStripW / 2); i += kCodecThreads) {
+    const int comp = i / (8 * (kStripW / 2)), rr = (i / (kStripW / 2)) % 8, cc = i % (kStripW / 2);
+    const int gr = mr * 8 + rr, gc = (col0 >> 1) + cc;
+    if (gr < hc && gc < wc) (comp ? crdec : cbdec)[img * (long long)hc * wc + (long long)gr * wc + gc] = sC[comp][rr][cc];
+  }
+}
+
+// colsum of jdsample.c h2v2_fancy_upsample: 3 * nearer row + farther row, at chroma column j (clamped = the
+// source's special first / last column cases, where the neighbour term degenerates to the column itself)
+__device__ __forceinline__ int colsum(const uint8_t* near, const uint8_t* far, int j) { return 3 * near[j] + far[j]; }
+
+__global__ void __launch_bounds__(256)
+jpeg_upsample_rgb_kernel(const uint8_t* __restrict__ ydec, const uint8_t* __restrict__ cbdec,
+                         const uint8_t* __restrict__ crdec, float* __restrict__ out, long long n_img, int h, int w) {
+  const int hc = (h + 1) >> 1, wc = (w + 1) >> 1;
+  const long long total = n_img * h * wc;                  // one thread per horizontal output pair
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int j = (int)(i % wc);
+    const int r = (int)((i / wc) % h);
+    const long long img = i / ((long long)wc * h);
+    const int rc = r >> 1;
+    const int rfar = (r & 1) ? min(rc + 1, hc - 1) : max(rc - 1, 0);   // context rows replicate at the edges
+    const int jl = max(j - 1, 0), jr = min(j + 1, wc - 1);
+    int up[2][2];
+#pragma unroll
+    for (int comp = 0; comp < 2; ++comp) {
+      const uint8_t* base = (comp ? crdec : cbdec) + img * (long long)hc * wc;
+      const uint8_t* near = base + (long long)rc * wc;
+      const uint8_t* far = base + (long long)rfar * wc;
+      const int s = colsum(near, far, j);
+      up[comp][0] = (3 * s + colsum(near, far, jl) + 8) >> 4;
+      up[comp][1] = (3 * s + colsum(near, far, jr) + 7) >> 4;
+    }
+    const uint8_t* yrow = ydec + (img * h + r) * (long long)w;
+    float* o = out + img * 3 * (long long)h * w + (long long)r * w;
+    const long long plane = (long long)h * w;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int c = 2 * j + k;
+      if (c >= w) break;
+      const int y = yrow[c], xb = up[0][k] - 128, xr = up[1][k] - 128;
+      // jdcolor.c build_ycc_rgb_table / ycc_rgb_convert
+      const int R = y + ((91881 * xr + 32768) >> 16);
+      const int B = y + ((116130 * xb + 32768) >> 16);
+      const int G = y + ((-22554 * xb + 32768 - 46802 * xr) >> 16);
+      o[c] = __fdiv_rn((float)min(max(R, 0), 255), 255.f);              // ToTensor: div(255)
+      o[plane + c] = __fdiv_rn((float)min(max(G, 0), 255), 255.f);
+      o[2 * plane + c] = __fdiv_rn((float)min(max(B, 0), 255), 255.f);
+    }
+  }
+}
+
+int build_tables(int quality, JpegTables* tb) {
+  static const uint8_t kLuma[64] = {16, 11, 10, 16, 24,  40,  51,  61,  12, 12, 14, 19, 26,  58,  60,  55,
+                                    14, 13, 16, 24, 40,  57,  69,  56,  14, 17, 22, 29, 51,  87,  80,  62,
+                                    18, 22, 37, 56, 68,  109, 103, 77,  24, 35, 55, 64, 81,  104, 113, 92,
+                                    49, 64, 78, 87, 103, 121, 120, 101, 72, 92, 95, 98, 112, 100, 103, 99};
+  static const uint8_t kChroma[64] = {17, 18, 24, 47, 99, 99, 99, 99, 18, 21, 26, 66, 99, 99, 99, 99,
+                                      24, 26, 56, 99, 99, 99, 99, 99, 47, 66, 99, 99, 99, 99, 99, 99,
+                                      99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99,
+                                      99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99};
+  // jcparam.c jpeg_quality_scaling + jpeg_add_quant_table(force_baseline)
+  const int q = quality < 1 ? 1 : (quality > 100 ? 100 : quality);
+  const int scale = q < 50 ? 5000 / q : 200 - 2 * q;
+  for (int comp = 0; comp < 2; ++comp)
+    for (int i = 0; i < 64; ++i) {
+      long v = ((long)(comp ? kChroma[i] : kLuma[i]) * scale + 50) / 100;
+      v = v < 1 ? 1 : (v > 255 ? 255 : v);
+      tb->q[comp][i] = (uint16_t)v;
+      const uint64_t d = (uint64_t)v << 3;
+      tb->recip[comp][i] = (uint32_t)(((1ull << 32) + d - 1) / d);   // exact for numerators < 2^21
+    }
+  return 0;
+}
+
+}  // namespace
+}  // namespace advb200
+
+using namespace advb200;
+
+extern "C" {
+
+int64_t advb200_jpeg_scratch_bytes(int n_img, int h, int w) {
+  if (n_img < 0 || h <= 0 || w <= 0) return -1;
+  const int64_t hc = (h + 1) / 2, wc = (w + 1) / 2;
+  return (int64_t)n_img * ((int64_t)h * w + 2 * hc * wc) + 256;
+}
+
+int advb200_jpeg_roundtrip_f32(const float* x, float* out, int n_img, int h, int w, int quality, void* scratch,
+                               int64_t scratch_bytes, void* stream) {
+  ADV_CHECK_ARG(n_img >= 0 && h > 0 && w > 0, "jpeg: bad sizes");
+  ADV_CHECK_ARG(quality >= 1 && quality <= 100, "jpeg: quality must be in 1..100");
+  if (n_img == 0) return ADVB200_OK;
+  ADV_CHECK_ARG(x && out && scratch, "jpeg: null pointer");
+  ADV_CHECK_ARG(scratch_bytes >= advb200_jpeg_scratch_bytes(n_img, h, w), "jpeg: scratch too small");
+  JpegTables tb;
+  build_tables(quality, &tb);
+  const int64_t hc = (h + 1) / 2, wc = (w + 1) / 2;
+  uint8_t* ydec = static_cast<uint8_t*>(scratch);
+  uint8_t* cbdec = ydec + (int64_t)n_img * h * w;
+  uint8_t* crdec = cbdec + (int64_t)n_img * hc * wc;
+  const int strips = (w + kStripW - 1) / kStripW, mcu_rows = (h + 15) / 16;
+  const int64_t ctas = (int64_t)n_img * strips * mcu_rows;
+  ADV_CHECK_ARG(ctas < (1ll << 31), "jpeg: batch too large for one launch");
+  cudaStream_t st = as_stream(stream);
+  jpeg_codec_kernel<<<(unsigned)ctas, kCodecThreads, 0, st>>>(x, ydec, cbdec, crdec, h, w, strips, mcu_rows, tb);
+  ADV_LAUNCHED();
+  const int64_t pairs = (int64_t)n_img * h * wc;
+  int64_t grid = (pairs + 255) / 256;
+  const int64_t cap = (int64_t)kNumSMs * 32;
+  if (grid > cap) grid = cap;
+  jpeg_upsample_rgb_kernel<<<(unsigned)grid, 256, 0, st>>>(ydec, cbdec, crdec, out, n_img, h, w);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+
+}  // extern "C"

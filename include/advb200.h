@@ -157,6 +157,15 @@ int advb200_quantize_f32(const float* x, float* out, int64_t n_elems, int levels
 int advb200_defend_input_f32(const float* x, float* out, int64_t planes, int h, int w, int levels,
                              void* stream);
 
+/* JPEG defense (defense_experiments.py:188-207 _jpeg_compress_batch: ToPILImage -> PIL save(JPEG, quality) -> open ->
+ * ToTensor).  The baseline-JPEG sample pipeline of PIL's libjpeg (4:2:0, Annex-K tables scaled for `quality`, islow
+ * integer DCTs, fancy chroma upsampling) computed on the device, bit-exact with the host round trip; any h, w >= 1
+ * (edges replicated as the encoder does).  x, out: fp32 [n_img,3,h,w] (may alias); scratch: caller-owned device
+ * buffer of advb200_jpeg_scratch_bytes(n_img,h,w) bytes (decoded Y + half-size Cb, Cr as uint8). */
+int64_t advb200_jpeg_scratch_bytes(int n_img, int h, int w);
+int advb200_jpeg_roundtrip_f32(const float* x, float* out, int n_img, int h, int w, int quality, void* scratch,
+                               int64_t scratch_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Evaluation counters (defense_experiments.py:597-637, 809-832)
  * counters int64 [7] += {clean_correct, attack_success, defense_preproc_success,

@@ -52,12 +52,22 @@ def rec(name, ms, bytes_per_elem):
     out["kernels"][name] = {"ms": ms, "bytes_per_elem": bytes_per_elem, "gbs": gbs, "frac_of_hbm_peak": gbs / PBW}
 
 
-# the three rotating input sets keep every launch's working set (> 450 MB) out of the 126 MB L2
-rec("linf_step(project)", timed(lambda: advb200.attack._linf_step(xa, x0, g, 2 / 255, 8 / 255, True)), 16)
-rec("linf_step(fgsm)", timed(lambda: advb200.attack._linf_step(xa, x0, g, 8 / 255, 8 / 255, False)), 12)
-rec("smooth3x3", timed(lambda: defenses._defense_smoothing(x)), 8)
-rec("quantize16", timed(lambda: defenses._defense_quantization(x)), 8)
-rec("defend_input", timed(lambda: defenses.defend_input(x)), 8)
+# every kernel is called through the C ABI on preallocated buffers (the Python wrappers' allocation + context-manager
+# overhead is comparable to these 50-100 us kernels and would make the loop host-bound); each working set (> 300 MB)
+# is larger than the 126 MB L2
+from ctypes import c_void_p  # noqa: E402
+P, S = _lib.ptr, _lib.stream_ptr
+out_buf = torch.empty_like(x)
+planes, H, W = n * 3, x.shape[2], x.shape[3]
+rec("linf_step(project)", timed(lambda: lib.advb200_linf_step_f32(P(xa), P(x0), P(g), 2 / 255, 8 / 255, elems, 1, S())), 16)
+rec("linf_step(fgsm)", timed(lambda: lib.advb200_linf_step_f32(P(xa), None, P(g), 8 / 255, 8 / 255, elems, 0, S())), 12)
+rec("smooth3x3", timed(lambda: lib.advb200_smooth3x3_f32(P(x), P(out_buf), planes, H, W, S())), 8)
+rec("quantize16", timed(lambda: lib.advb200_quantize_f32(P(x), P(out_buf), elems, 16, S())), 8)
+rec("defend_input", timed(lambda: lib.advb200_defend_input_f32(P(x), P(out_buf), planes, H, W, 16, S())), 8)
+# JPEG round trip: 12 B/pixel in + 12 B/pixel out + 3 B/pixel of uint8 scratch (written, then read) = 27 B/pixel = 9 B/elem
+jbytes = int(lib.advb200_jpeg_scratch_bytes(n, H, W))
+jscratch = torch.empty(jbytes, dtype=torch.uint8, device=dev)
+rec("jpeg_q75", timed(lambda: lib.advb200_jpeg_roundtrip_f32(P(x), P(out_buf), n, H, W, 75, P(jscratch), jbytes, S())), 9)
 
 model = weights.seeded_resnet50(0).to(dev)
 mean, std = weights.mean_std()
