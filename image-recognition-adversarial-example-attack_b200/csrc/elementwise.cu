@@ -85,35 +85,96 @@ __device__ __forceinline__ float quant_one(float x, float lm1) {
   return __fdiv_rn(rintf(__fmul_rn(c, lm1)), lm1);  // round-half-even, true division
 }
 
+// The quotient k / (levels-1) takes only `levels` values: a shared-memory table filled with the same true division
+// replaces the ~12-instruction IEEE division sequence per element by one conversion and one LDS (the kernels were
+// issue-bound on it).  Bit-identical by construction; levels > kQuantTab falls back to dividing.
+constexpr int kQuantTab = 256;
+__device__ __forceinline__ void quant_table_init(float* tab, float lm1) {
+  for (int k = threadIdx.x; k < kQuantTab; k += blockDim.x) tab[k] = __fdiv_rn((float)k, lm1);
+  __syncthreads();
+}
+__device__ __forceinline__ float quant_one_tab(float x, float lm1, const float* tab, bool use_tab) {
+  const float c = fminf(fmaxf(x, 0.f), 1.f);
+  if (!use_tab) return __fdiv_rn(rintf(__fmul_rn(c, lm1)), lm1);
+  return tab[__float2int_rn(__fmul_rn(c, lm1))];     // cvt.rni = rintf (half to even); the product is in [0, lm1]
+}
+
 __global__ void __launch_bounds__(kThreads)
 quantize_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n4, int64_t n, float lm1,
                 int vec) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ float tab[kQuantTab];
+  const bool use_tab = lm1 < (float)kQuantTab;
+  quant_table_init(tab, lm1);
   if (vec) {
     const float4* xi = reinterpret_cast<const float4*>(x);
     float4* oo = reinterpret_cast<float4*>(out);
+    // four independent 16-byte loads in flight per thread: one load per iteration leaves ~32 KB per SM in flight,
+    // about half of what the HBM latency needs (measured 3.6 TB/s; the 3-operand linf step reaches 6.6 TB/s)
+    for (; i + 3 * stride < n4; i += 4 * stride) {
+      float4 a[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) a[k] = __ldg(xi + i + k * stride);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        a[k].x = quant_one_tab(a[k].x, lm1, tab, use_tab); a[k].y = quant_one_tab(a[k].y, lm1, tab, use_tab);
+        a[k].z = quant_one_tab(a[k].z, lm1, tab, use_tab); a[k].w = quant_one_tab(a[k].w, lm1, tab, use_tab);
+        oo[i + k * stride] = a[k];
+      }
+    }
     for (; i < n4; i += stride) {
       float4 a = __ldg(xi + i);
-      a.x = quant_one(a.x, lm1); a.y = quant_one(a.y, lm1);
-      a.z = quant_one(a.z, lm1); a.w = quant_one(a.w, lm1);
+      a.x = quant_one_tab(a.x, lm1, tab, use_tab); a.y = quant_one_tab(a.y, lm1, tab, use_tab);
+      a.z = quant_one_tab(a.z, lm1, tab, use_tab); a.w = quant_one_tab(a.w, lm1, tab, use_tab);
       oo[i] = a;
     }
     for (int64_t j = n4 * 4 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += stride)
-      out[j] = quant_one(x[j], lm1);
+      out[j] = quant_one_tab(x[j], lm1, tab, use_tab);
   } else {
-    for (; i < n; i += stride) out[i] = quant_one(x[i], lm1);
+    for (; i < n; i += stride) out[i] = quant_one_tab(x[i], lm1, tab, use_tab);
   }
 }
 
+// s / 9 with IEEE round-to-nearest, by Markstein's correction instead of the generic division sequence: with
+// y = RN(1/9), q0 = RN(s*y), the remainder r = s - 9*q0 is exact in one FMA and RN(q0 + r*y) is the correctly rounded
+// quotient.  The argument needs no under/overflow in q0 and r, hence the exponent guard (everything else, including
+// inf/nan, takes the generic path; +-0 returns q0 = +-0).  Verified EXHAUSTIVELY over all 2^32 bit patterns against
+// __fdiv_rn on the device (advb200_test_div9, tests/test_gpu_parity.py).
+__device__ __forceinline__ float div9(float s) {
+  const float y = 0.111111112f;
+  const float q0 = __fmul_rn(s, y);
+  const float r = __fmaf_rn(-9.0f, q0, s);
+  const float q1 = __fmaf_rn(r, y, q0);
+  const float a = fabsf(s);
+  if (a > 1e-30f && a < 1e30f) return q1;
+  if (a == 0.f) return q0;
+  return __fdiv_rn(s, 9.0f);
+}
+
+__global__ void div9_check_kernel(unsigned long long* mismatches, unsigned int* first_bad) {
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  unsigned long long bad = 0;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < (1ull << 32); i += stride) {
+    const float s = __uint_as_float((unsigned int)i);
+    const float want = __fdiv_rn(s, 9.0f), got = div9(s);
+    const bool same = (__float_as_uint(want) == __float_as_uint(got)) || (want != want && got != got);
+    if (!same) { ++bad; atomicMin(first_bad, (unsigned int)i); }
+  }
+  if (bad) atomicAdd(mismatches, bad);
+}
+
 // 3x3 mean (zero pad, divisor 9) with optional clamp-in / quantise-out (defend_input fusion).
-// One thread produces a 4-wide strip of kRows output rows, sliding a 3-row register window so
+// One thread produces a 4-wide strip of kSmoothRows output rows from a (kSmoothRows + 2)-row register window, so
 // every input element is fetched from L1/L2 about 1.5x and from HBM once.
-constexpr int kSmoothRows = 8;
+constexpr int kSmoothRows = 4;
 template <bool kDefend>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 smooth3x3_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t planes, int h, int w,
                  float lm1) {
+  __shared__ float tab[kQuantTab];
+  const bool use_tab = kDefend && lm1 < (float)kQuantTab;
+  if (kDefend) quant_table_init(tab, lm1);
   const int groups = (w + 3) >> 2;                         // 4-wide column groups
   const int row_chunks = (h + kSmoothRows - 1) / kSmoothRows;
   const int64_t total = planes * row_chunks * (int64_t)groups;
@@ -126,43 +187,62 @@ smooth3x3_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t p
     float* dst = out + p * (int64_t)h * w;
     const int c0 = gx * 4;
     const int r0 = rc * kSmoothRows;
-    float win[3][6];
+    // the whole (kSmoothRows + 2)-row window is fetched before any arithmetic: 10 rows of independent loads in
+    // flight per thread instead of one (the sliding 3-row window left the kernel latency-bound at 0.48 of HBM peak)
+    float win[kSmoothRows + 2][6];
+    const bool vec = ((w & 3) == 0) && ((reinterpret_cast<uintptr_t>(src) & 15u) == 0);
     auto load_row = [&](int r, float* v) {
+      if (r < 0 || r >= h) {
 #pragma unroll
-      for (int j = 0; j < 6; ++j) {
-        const int c = c0 - 1 + j;
-        float val = 0.f;
-        if (r >= 0 && r < h && c >= 0 && c < w) {
-          val = __ldg(src + (int64_t)r * w + c);
-          if (kDefend) val = fminf(fmaxf(val, 0.f), 1.f);
+        for (int j = 0; j < 6; ++j) v[j] = 0.f;
+        return;
+      }
+      const float* row = src + (int64_t)r * w;
+      if (vec) {
+        const float4 m = __ldg(reinterpret_cast<const float4*>(row + c0));
+        v[0] = c0 > 0 ? __ldg(row + c0 - 1) : 0.f;
+        v[1] = m.x; v[2] = m.y; v[3] = m.z; v[4] = m.w;
+        v[5] = c0 + 4 < w ? __ldg(row + c0 + 4) : 0.f;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+          const int c = c0 - 1 + j;
+          v[j] = (c >= 0 && c < w) ? __ldg(row + c) : 0.f;
         }
-        v[j] = val;
+      }
+      if (kDefend) {
+#pragma unroll
+        for (int j = 0; j < 6; ++j) v[j] = fminf(fmaxf(v[j], 0.f), 1.f);   // clamp(0) = 0: the zero padding survives
       }
     };
-    load_row(r0 - 1, win[0]);
-    load_row(r0, win[1]);
+#pragma unroll
+    for (int k = 0; k < kSmoothRows + 2; ++k) load_row(r0 - 1 + k, win[k]);
 #pragma unroll
     for (int dr = 0; dr < kSmoothRows; ++dr) {
       const int r = r0 + dr;
       if (r >= h) break;
-      load_row(r + 1, win[(dr + 2) % 3]);
-      const float* a = win[dr % 3];
-      const float* b = win[(dr + 1) % 3];
-      const float* c = win[(dr + 2) % 3];
+      const float* a = win[dr];
+      const float* b = win[dr + 1];
+      const float* c = win[dr + 2];
+      float o4[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        if (c0 + j >= w) break;
         // row-major accumulation of the nine taps, exactly F.avg_pool2d's order
         float s = a[j];
         s = __fadd_rn(s, a[j + 1]); s = __fadd_rn(s, a[j + 2]);
         s = __fadd_rn(s, b[j]); s = __fadd_rn(s, b[j + 1]); s = __fadd_rn(s, b[j + 2]);
         s = __fadd_rn(s, c[j]); s = __fadd_rn(s, c[j + 1]); s = __fadd_rn(s, c[j + 2]);
-        float o = __fdiv_rn(s, 9.0f);
-        if (kDefend) {
-          o = quant_one(o, lm1);
-          o = fminf(fmaxf(o, 0.f), 1.f);
-        }
-        dst[(int64_t)r * w + c0 + j] = o;
+        float o = div9(s);
+        // (the reference's trailing clamp, defense_experiments.py:217, is the identity on k/(levels-1), k <= levels-1)
+        if (kDefend) o = quant_one_tab(o, lm1, tab, use_tab);
+        o4[j] = o;
+      }
+      if (vec && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0)) {
+        *reinterpret_cast<float4*>(dst + (int64_t)r * w + c0) = make_float4(o4[0], o4[1], o4[2], o4[3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (c0 + j < w) dst[(int64_t)r * w + c0 + j] = o4[j];
       }
     }
   }
@@ -413,6 +493,25 @@ static int smooth_launch(const float* x, float* out, int64_t planes, int h, int 
 
 int advb200_smooth3x3_f32(const float* x, float* out, int64_t planes, int h, int w, void* stream) {
   return smooth_launch(x, out, planes, h, w, 2, false, stream);
+}
+
+int advb200_test_div9(uint64_t* mismatches_host, uint32_t* first_bad_host) {
+  // test hook: the constant-divisor shortcut of the smoothing kernels against __fdiv_rn, all 2^32 inputs
+  ADV_CHECK_ARG(mismatches_host && first_bad_host, "test_div9: null pointer");
+  unsigned long long* d_bad = nullptr;
+  unsigned int* d_first = nullptr;
+  ADV_CHECK_CUDA(cudaMalloc(&d_bad, 8));
+  ADV_CHECK_CUDA(cudaMalloc(&d_first, 4));
+  ADV_CHECK_CUDA(cudaMemset(d_bad, 0, 8));
+  ADV_CHECK_CUDA(cudaMemset(d_first, 0xff, 4));
+  div9_check_kernel<<<kNumSMs * 16, 256>>>(d_bad, d_first);
+  ADV_LAUNCHED();
+  unsigned long long bad = 0;
+  ADV_CHECK_CUDA(cudaMemcpy(&bad, d_bad, 8, cudaMemcpyDeviceToHost));
+  ADV_CHECK_CUDA(cudaMemcpy(first_bad_host, d_first, 4, cudaMemcpyDeviceToHost));
+  *mismatches_host = bad;
+  cudaFree(d_bad); cudaFree(d_first);
+  return ADVB200_OK;
 }
 
 int advb200_defend_input_f32(const float* x, float* out, int64_t planes, int h, int w, int levels,

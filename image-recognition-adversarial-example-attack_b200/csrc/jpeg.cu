@@ -141,14 +141,53 @@ jpeg_codec_kernel(const float* __restrict__ x, uint8_t* __restrict__ ydec, uint8
   const float* xb = xg + (long long)h * w;
 
   // ---- load, quantise to bytes, colour-convert (jccolor.c); rows / columns past the image replicate its edge
-  for (int i = threadIdx.x; i < 16 * kStripW; i += kCodecThreads) {
-    const int r = i / kStripW, c = i % kStripW;
-    const int gr = min(row0 + r, h - 1), gc = min(col0 + c, w - 1);
-    const long long o = (long long)gr * w + gc;
-    const int R = to_u8(__ldg(xr + o)), G = to_u8(__ldg(xg + o)), B = to_u8(__ldg(xb + o));
+  auto convert = [&](int r, int c, float fr, float fg, float fb) {
+    const int R = to_u8(fr), G = to_u8(fg), B = to_u8(fb);
     sY[r][c] = (uint8_t)((19595 * R + 38470 * G + 7471 * B + 32768) >> 16);
     sCbF[r][c] = (uint8_t)((-11059 * R - 21709 * G + 32768 * B + (128 << 16) + 32767) >> 16);
     sCrF[r][c] = (uint8_t)((32768 * R - 27439 * G - 5329 * B + (128 << 16) + 32767) >> 16);
+  };
+  const bool vec = ((w & 3) == 0) && ((reinterpret_cast<uintptr_t>(x) & 15u) == 0);
+  if (vec) {
+    // 16-byte loads, two groups (six loads) in flight per thread; groups wholly past the right edge replicate the
+    // last pixel, which the scalar tail below fills in
+    const int gw = min(kStripW, w - col0) >> 2;                  // whole 4-pixel groups of this strip inside the image
+    for (int i0 = threadIdx.x; i0 < 16 * gw; i0 += 2 * kCodecThreads) {
+      float4 v[2][3];
+      int rr[2], cc[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int i = i0 + u * kCodecThreads;
+        rr[u] = -1;
+        if (i < 16 * gw) {
+          rr[u] = i / gw; cc[u] = (i % gw) * 4;
+          const long long o = (long long)min(row0 + rr[u], h - 1) * w + col0 + cc[u];
+          v[u][0] = __ldg(reinterpret_cast<const float4*>(xr + o));
+          v[u][1] = __ldg(reinterpret_cast<const float4*>(xg + o));
+          v[u][2] = __ldg(reinterpret_cast<const float4*>(xb + o));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u)
+        if (rr[u] >= 0) {
+          convert(rr[u], cc[u], v[u][0].x, v[u][1].x, v[u][2].x);
+          convert(rr[u], cc[u] + 1, v[u][0].y, v[u][1].y, v[u][2].y);
+          convert(rr[u], cc[u] + 2, v[u][0].z, v[u][1].z, v[u][2].z);
+          convert(rr[u], cc[u] + 3, v[u][0].w, v[u][1].w, v[u][2].w);
+        }
+    }
+    const int done = gw * 4, rest = kStripW - done;              // columns past the image edge (replicated)
+    for (int i = threadIdx.x; i < 16 * rest; i += kCodecThreads) {
+      const int r = i / rest, c = done + i % rest;
+      const long long o = (long long)min(row0 + r, h - 1) * w + (w - 1);
+      convert(r, c, __ldg(xr + o), __ldg(xg + o), __ldg(xb + o));
+    }
+  } else {
+    for (int i = threadIdx.x; i < 16 * kStripW; i += kCodecThreads) {
+      const int r = i / kStripW, c = i % kStripW;
+      const long long o = (long long)min(row0 + r, h - 1) * w + min(col0 + c, w - 1);
+      convert(r, c, __ldg(xr + o), __ldg(xg + o), __ldg(xb + o));
+    }
   }
   __syncthreads();
   // ---- h2v2 box filter with the alternating 1,2 bias (jcsample.c); chroma rows past the real chroma height
@@ -174,16 +213,30 @@ jpeg_codec_kernel(const float* __restrict__ x, uint8_t* __restrict__ ydec, uint8
     }
   }
   __syncthreads();
-  // ---- decoded bytes -> scratch (real pixels only)
+  // ---- decoded bytes -> scratch (real pixels only); 4 bytes per store when the rows are 4-byte aligned
   uint8_t* yo = ydec + img * (long long)h * w;
-  for (int i = threadIdx.x; i < 16 * kStripW; i += kCodecThreads) {
-    const int r = i / kStripW, c = i % kStripW;
-    if (row0 + r < h && col0 + c < w) yo[(long long)(row0 + r) * w + col0 + c] = sY[r][c];
+  if ((w & 3) == 0) {
+    for (int i = threadIdx.x; i < 16 * (kStripW / 4); i += kCodecThreads) {
+      const int r = i / (kStripW / 4), c = (i % (kStripW / 4)) * 4;
+      if (row0 + r < h && col0 + c < w)
+        *reinterpret_cast<uint32_t*>(yo + (long long)(row0 + r) * w + col0 + c) = *reinterpret_cast<const uint32_t*>(&sY[r][c]);
+    }
+  } else {
+    for (int i = threadIdx.x; i < 16 * kStripW; i += kCodecThreads) {
+      const int r = i / kStripW, c = i % kStripW;
+      if (row0 + r < h && col0 + c < w) yo[(long long)(row0 + r) * w + col0 + c] = sY[r][c];
+    }
   }
-  for (int i = threadIdx.x; i < 2 * 8 * (kStripW / 2); i += kCodecThreads) {
-    const int comp = i / (8 * (kStripW / 2)), rr = (i / (kStripW / 2)) % 8, cc = i % (kStripW / 2);
+  const bool cvec = ((wc & 3) == 0) && (((reinterpret_cast<uintptr_t>(cbdec) | reinterpret_cast<uintptr_t>(crdec)) & 3u) == 0);
+  for (int i = threadIdx.x; i < 2 * 8 * (kStripW / 2) / (cvec ? 4 : 1); i += kCodecThreads) {
+    const int e = cvec ? i * 4 : i;
+    const int comp = e / (8 * (kStripW / 2)), rr = (e / (kStripW / 2)) % 8, cc = e % (kStripW / 2);
     const int gr = mr * 8 + rr, gc = (col0 >> 1) + cc;
-    if (gr < hc && gc < wc) (comp ? crdec : cbdec)[img * (long long)hc * wc + (long long)gr * wc + gc] = sC[comp][rr][cc];
+    if (gr < hc && gc < wc) {
+      uint8_t* dst = (comp ? crdec : cbdec) + img * (long long)hc * wc + (long long)gr * wc + gc;
+      if (cvec) *reinterpret_cast<uint32_t*>(dst) = *reinterpret_cast<const uint32_t*>(&sC[comp][rr][cc]);
+      else *dst = sC[comp][rr][cc];
+    }
   }
 }
 
@@ -194,40 +247,67 @@ __device__ __forceinline__ int colsum(const uint8_t* near, const uint8_t* far, i
 __global__ void __launch_bounds__(256)
 jpeg_upsample_rgb_kernel(const uint8_t* __restrict__ ydec, const uint8_t* __restrict__ cbdec,
                          const uint8_t* __restrict__ crdec, float* __restrict__ out, long long n_img, int h, int w) {
-  const int hc = (h + 1) >> 1, wc = (w + 1) >> 1;
-  const long long total = n_img * h * wc;                  // one thread per horizontal output pair
+  const int hc = (h + 1) >> 1, wc = (w + 1) >> 1, wq = (w + 3) >> 2;
+  const long long total = n_img * h * wq;                  // one thread per four horizontal output pixels
+  const bool vec = ((w & 3) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15u) == 0) &&
+                   ((reinterpret_cast<uintptr_t>(ydec) & 3u) == 0);
   for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
-    const int j = (int)(i % wc);
-    const int r = (int)((i / wc) % h);
-    const long long img = i / ((long long)wc * h);
+    const int q = (int)(i % wq);
+    const int r = (int)((i / wq) % h);
+    const long long img = i / ((long long)wq * h);
     const int rc = r >> 1;
     const int rfar = (r & 1) ? min(rc + 1, hc - 1) : max(rc - 1, 0);   // context rows replicate at the edges
-    const int jl = max(j - 1, 0), jr = min(j + 1, wc - 1);
-    int up[2][2];
+    const int j0 = 2 * q;                                               // chroma columns j0, j0 + 1
+    int up[2][4];
 #pragma unroll
     for (int comp = 0; comp < 2; ++comp) {
       const uint8_t* base = (comp ? crdec : cbdec) + img * (long long)hc * wc;
       const uint8_t* near = base + (long long)rc * wc;
       const uint8_t* far = base + (long long)rfar * wc;
-      const int s = colsum(near, far, j);
-      up[comp][0] = (3 * s + colsum(near, far, jl) + 8) >> 4;
-      up[comp][1] = (3 * s + colsum(near, far, jr) + 7) >> 4;
+      int s[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) s[k] = colsum(near, far, min(max(j0 - 1 + k, 0), wc - 1));
+      up[comp][0] = (3 * s[1] + s[0] + 8) >> 4;
+      up[comp][1] = (3 * s[1] + s[2] + 7) >> 4;
+      // second chroma column (absent when w % 4 is 1 or 2): its "next" neighbour clamps to itself at the edge
+      const int s3 = (j0 + 1 <= wc - 1) ? s[3] : s[2];
+      up[comp][2] = (3 * s[2] + s[1] + 8) >> 4;
+      up[comp][3] = (3 * s[2] + s3 + 7) >> 4;
     }
     const uint8_t* yrow = ydec + (img * h + r) * (long long)w;
     float* o = out + img * 3 * (long long)h * w + (long long)r * w;
     const long long plane = (long long)h * w;
+    const int c0 = 4 * q;
+    int yv[4];
+    if (vec) {
+      const uint32_t y4 = *reinterpret_cast<const uint32_t*>(yrow + c0);
 #pragma unroll
-    for (int k = 0; k < 2; ++k) {
-      const int c = 2 * j + k;
-      if (c >= w) break;
-      const int y = yrow[c], xb = up[0][k] - 128, xr = up[1][k] - 128;
+      for (int k = 0; k < 4; ++k) yv[k] = (y4 >> (8 * k)) & 0xff;
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) yv[k] = c0 + k < w ? yrow[c0 + k] : 0;
+    }
+    float rgb[3][4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int y = yv[k], xb = up[0][k] - 128, xr = up[1][k] - 128;
       // jdcolor.c build_ycc_rgb_table / ycc_rgb_convert
       const int R = y + ((91881 * xr + 32768) >> 16);
       const int B = y + ((116130 * xb + 32768) >> 16);
       const int G = y + ((-22554 * xb + 32768 - 46802 * xr) >> 16);
-      o[c] = __fdiv_rn((float)min(max(R, 0), 255), 255.f);              // ToTensor: div(255)
-      o[plane + c] = __fdiv_rn((float)min(max(G, 0), 255), 255.f);
-      o[2 * plane + c] = __fdiv_rn((float)min(max(B, 0), 255), 255.f);
+      rgb[0][k] = __fdiv_rn((float)min(max(R, 0), 255), 255.f);         // ToTensor: div(255)
+      rgb[1][k] = __fdiv_rn((float)min(max(G, 0), 255), 255.f);
+      rgb[2][k] = __fdiv_rn((float)min(max(B, 0), 255), 255.f);
+    }
+#pragma unroll
+    for (int p = 0; p < 3; ++p) {
+      if (vec) {
+        *reinterpret_cast<float4*>(o + p * plane + c0) = make_float4(rgb[p][0], rgb[p][1], rgb[p][2], rgb[p][3]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (c0 + k < w) o[p * plane + c0 + k] = rgb[p][k];
+      }
     }
   }
 }
@@ -287,8 +367,8 @@ int advb200_jpeg_roundtrip_f32(const float* x, float* out, int n_img, int h, int
   cudaStream_t st = as_stream(stream);
   jpeg_codec_kernel<<<(unsigned)ctas, kCodecThreads, 0, st>>>(x, ydec, cbdec, crdec, h, w, strips, mcu_rows, tb);
   ADV_LAUNCHED();
-  const int64_t pairs = (int64_t)n_img * h * wc;
-  int64_t grid = (pairs + 255) / 256;
+  const int64_t quads = (int64_t)n_img * h * ((w + 3) / 4);
+  int64_t grid = (quads + 255) / 256;
   const int64_t cap = (int64_t)kNumSMs * 32;
   if (grid > cap) grid = cap;
   jpeg_upsample_rgb_kernel<<<(unsigned)grid, 256, 0, st>>>(ydec, cbdec, crdec, out, n_img, h, w);

@@ -157,6 +157,10 @@ int advb200_quantize_f32(const float* x, float* out, int64_t n_elems, int levels
 int advb200_defend_input_f32(const float* x, float* out, int64_t planes, int h, int w, int levels,
                              void* stream);
 
+/* Test hook: compares the constant-divisor shortcut the smoothing kernels use for s/9 with the IEEE division, for all
+ * 2^32 float bit patterns, on the device; *mismatches must come back 0. */
+int advb200_test_div9(uint64_t* mismatches, uint32_t* first_bad_bits);
+
 /* JPEG defense (defense_experiments.py:188-207 _jpeg_compress_batch: ToPILImage -> PIL save(JPEG, quality) -> open ->
  * ToTensor).  The baseline-JPEG sample pipeline of PIL's libjpeg (4:2:0, Annex-K tables scaled for `quality`, islow
  * integer DCTs, fancy chroma upsampling) computed on the device, bit-exact with the host round trip; any h, w >= 1

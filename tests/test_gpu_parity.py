@@ -113,6 +113,16 @@ def test_defenses_bit_exact_vs_golden_and_oracle(advb200_mod, dev, golden_dir):
     assert float(s[0, 0, 5, 5]) == 1.0 and float(s[0, 0, 0, 0]) == np.float32(4.0) / np.float32(9.0)
 
 
+def test_divide_by_nine_shortcut_is_exact_for_every_float(advb200_mod):
+    """The smoothing kernels divide by 9 with one multiply and two FMAs instead of the generic division sequence;
+    the device checks it against __fdiv_rn for all 2^32 bit patterns."""
+    import ctypes
+    from advb200 import _lib
+    bad, first = ctypes.c_uint64(123), ctypes.c_uint32(0)
+    _lib.check(_lib.load().advb200_test_div9(ctypes.byref(bad), ctypes.byref(first)), "advb200_test_div9")
+    assert bad.value == 0, f"{bad.value} mismatches, first at bits 0x{first.value:08x}"
+
+
 def test_defense_edge_shapes(advb200_mod, dev):
     for shape in [(1, 1, 1, 1), (2, 3, 1, 5), (1, 2, 3, 1), (0, 3, 8, 8), (1, 3, 33, 17)]:
         x = torch.rand(shape, generator=torch.Generator().manual_seed(1)) * 1.4 - 0.2
