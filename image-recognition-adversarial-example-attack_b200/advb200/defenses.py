@@ -3,7 +3,8 @@
     reference (defense_experiments.py)                 here
     :177-179 _defense_smoothing                         advb200_smooth3x3_f32   (bit-exact)
     :182-185 _defense_quantization                      advb200_quantize_f32    (bit-exact)
-    :210-217 defend_input (JPEG off, the default)       advb200_defend_input_f32 (one fused pass)
+    :188-207 _jpeg_compress_batch                       advb200_jpeg_roundtrip_f32 (libjpeg sample pipeline on the device)
+    :210-217 defend_input                               advb200_defend_input_f32 (one fused pass) [+ the JPEG stage if switched on]
     :221-257 _layer3_features                           advb200_forward(stop_at_layer3, score_out)
     :273-285 is_adversarial_by_feature                  score > threshold
     :288-345 calibrate_feature_threshold                quantile tail on native scores

@@ -67,8 +67,9 @@ def main(argv=None) -> None:
     say = print if rank == 0 else (lambda *a, **k: None)
     if args.model_type == "robust":
         raise SystemExit("the RobustBench checkpoint (defense_experiments.py:676) is not available offline")
-    if args.use_jpeg:
-        raise SystemExit("--use_jpeg (PIL round trip, defense_experiments.py:188-207) is outside the native hot path")
+    # defense_experiments.py:770-772: the JPEG stage of defend_input (run on the device here, bit-exact with PIL's)
+    defenses._DEFENSE_USE_JPEG = bool(args.use_jpeg)
+    defenses._DEFENSE_JPEG_QUALITY = int(args.jpeg_quality)
     advb200.set_default_precision(args.precision)
     if args.weights == "random":
         torch.manual_seed(args.seed)

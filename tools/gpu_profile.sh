@@ -7,7 +7,7 @@ timeout 600 python bench.py --steps 8 --warmup 3 > gpurun_out/bench.json 2> gpur
 timeout 300 python tools/layer_profile.py 256 3 > gpurun_out/layers_256.csv 2> gpurun_out/layers.err; tail -n 1 gpurun_out/layers_256.csv
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv \
   --log-file gpurun_out/launches_pgd2.csv python tools/one_pass.py 256 pgd > gpurun_out/ncu_list.log 2>&1; echo "ncu list rc=$?"
-timeout 1500 ncu --set full --clock-control none --profile-from-start off -k regex:conv_gemm \
+timeout 1500 ncu --set full --clock-control none --profile-from-start off -k 'regex:conv_gemm|fused_block' \
   -f -o /tmp/conv_raw python tools/one_pass.py 256 grad > gpurun_out/ncu_raw.log 2>&1; echo "ncu raw rc=$?"
 ncu -i /tmp/conv_raw.ncu-rep --page raw --csv > gpurun_out/conv_raw.csv 2>/dev/null
 timeout 900 ncu --set full --clock-control none --profile-from-start off --import-source on \
