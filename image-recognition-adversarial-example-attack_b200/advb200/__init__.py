@@ -10,3 +10,5 @@ from .defenses import (  # noqa: F401
 )
 from .model import NativeResNet50, NativeResNet50Module, get_default_precision, native_model, set_default_precision  # noqa: F401
 from .pipeline import HostBatchPipeline  # noqa: F401
+from . import preprocess  # noqa: F401
+from .preprocess import get_transform, load_image  # noqa: F401

@@ -38,6 +38,9 @@ SIGNATURES = {
                                    c_int64, c_void_p]),
     "advb200_jpeg_scratch_bytes": (c_int64, [c_int, c_int, c_int]),
     "advb200_jpeg_roundtrip_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p]),
+    "advb200_preprocess_scratch_bytes": (c_int64, [c_int, c_int, c_int, c_int]),
+    "advb200_preprocess_u8": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int64, c_void_p]),
+    "advb200_to_u8_hwc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "advb200_test_div9": (c_int, [c_void_p, c_void_p]),
     "advb200_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_void_p]),
     "advb200_attack_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_float,

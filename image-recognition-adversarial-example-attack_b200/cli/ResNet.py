@@ -21,7 +21,7 @@ import torchvision.models as models  # noqa: E402
 import torchvision.transforms as transforms  # noqa: E402
 from PIL import Image  # noqa: E402
 
-from advb200 import cw_l2_attack, fgsm_attack, native_model, pgd_linf_attack, set_default_precision  # noqa: E402
+from advb200 import cw_l2_attack, fgsm_attack, native_model, pgd_linf_attack, preprocess, set_default_precision  # noqa: E402
 
 
 def build_parser() -> argparse.ArgumentParser:
@@ -66,7 +66,7 @@ def main(argv=None) -> None:
     nm = native_model(model)
     mean = torch.tensor([0.485, 0.456, 0.406])
     std = torch.tensor([0.229, 0.224, 0.225])
-    transform = transforms.Compose([transforms.Resize(256), transforms.CenterCrop(224), transforms.ToTensor()])
+    transform = preprocess.get_transform(device)      # Resize(256) -> CenterCrop(224) -> ToTensor, on the device
     categories = None
     try:
         categories = models.ResNet50_Weights.DEFAULT.meta.get("categories")
@@ -84,7 +84,7 @@ def main(argv=None) -> None:
         if not image_path.is_file():
             print(f"Image file not found: {image_path}")
             return
-        x = transform(Image.open(image_path).convert("RGB")).unsqueeze(0).to(device)
+        x = transform(Image.open(image_path).convert("RGB")).unsqueeze(0)
         logits = nm.forward(x, mean, std)["logits"]
         pred = logits.argmax(dim=1)
         topk = max(1, int(args.topk))
@@ -111,7 +111,7 @@ def main(argv=None) -> None:
             out_path = Path(args.save_adv)
             if out_path.parent:
                 out_path.parent.mkdir(parents=True, exist_ok=True)
-            transforms.ToPILImage()(x_adv[0].detach().cpu()).save(out_path)
+            preprocess.to_pil_image(x_adv[0].detach()).save(out_path)
 
     image_path = Path(args.image)
     if image_path.is_dir():

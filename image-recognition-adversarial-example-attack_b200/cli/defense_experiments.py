@@ -19,7 +19,7 @@ import torchvision.models as models  # noqa: E402
 import torchvision.transforms as transforms  # noqa: E402
 
 import advb200  # noqa: E402
-from advb200 import defenses, dist as adist  # noqa: E402
+from advb200 import defenses, dist as adist, preprocess  # noqa: E402
 
 
 def build_parser() -> argparse.ArgumentParser:
@@ -54,7 +54,7 @@ def build_parser() -> argparse.ArgumentParser:
 
 def load_images(paths, transform, device):
     from PIL import Image
-    return torch.stack([transform(Image.open(p).convert("RGB")) for p in paths]).to(device)
+    return torch.stack([transform(Image.open(p).convert("RGB")) for p in paths]).to(device)   # transform runs on the device
 
 
 def main(argv=None) -> None:
@@ -82,7 +82,7 @@ def main(argv=None) -> None:
     nm = advb200.native_model(model.to(device))
     mean = torch.tensor([0.485, 0.456, 0.406])
     std = torch.tensor([0.229, 0.224, 0.225])
-    transform = transforms.Compose([transforms.Resize(256), transforms.CenterCrop(224), transforms.ToTensor()])
+    transform = preprocess.get_transform(device)      # Resize(256) -> CenterCrop(224) -> ToTensor, on the device
 
     # ---- images: the whole list is known to every rank; each rank materialises only its shard
     if args.synthetic > 0:

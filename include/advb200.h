@@ -170,6 +170,17 @@ int64_t advb200_jpeg_scratch_bytes(int n_img, int h, int w);
 int advb200_jpeg_roundtrip_f32(const float* x, float* out, int n_img, int h, int w, int quality, void* scratch,
                                int64_t scratch_bytes, void* stream);
 
+/* Image preprocessing of `load_image` (ResNet.py:27-31, defense_experiments.py:649-662) for one decoded image:
+ * Resize(size) [shorter side -> size; PIL's antialiased bilinear ImagingResample in 22-bit fixed point on uint8] ->
+ * CenterCrop(crop) -> ToTensor (/255).  img_hwc: uint8 [h,w,3] on the device; out_chw: fp32 [3,crop,crop].
+ * Bit-exact with torchvision + PIL.  scratch: advb200_preprocess_scratch_bytes(...) bytes, 256-byte aligned.
+ * ADVB200_ERR_UNSUPPORTED when the resized image is smaller than the crop (the reference would zero-pad). */
+int64_t advb200_preprocess_scratch_bytes(int h, int w, int size, int crop);
+int advb200_preprocess_u8(const uint8_t* img_hwc, int h, int w, int size, int crop, float* out_chw, void* scratch,
+                          int64_t scratch_bytes, void* stream);
+/* ToPILImage of --save_adv (ResNet.py:121-126): fp32 [3,h,w] in [0,1] -> uint8 [h,w,3], x*255 truncated. */
+int advb200_to_u8_hwc(const float* x_chw, uint8_t* out_hwc, int h, int w, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Evaluation counters (defense_experiments.py:597-637, 809-832)
  * counters int64 [7] += {clean_correct, attack_success, defense_preproc_success,

@@ -4,7 +4,8 @@ import numpy as np
 import pytest
 import torch
 
-from oracle import attacks_ref, defenses_ref, jpeg_ref, resnet50_ref, weights
+from oracle import attacks_ref, defenses_ref, jpeg_ref, preprocess_ref, resnet50_ref, weights
+from oracle.gen_golden_preprocess import SHAPES as PREPROCESS_SHAPES, make_image
 
 
 def _tiny(golden_dir):
@@ -88,6 +89,32 @@ def test_jpeg_building_blocks():
     y, cb, cr = jpeg_ref.rgb_to_ycc(grey)
     assert np.array_equal(y[:, 0], np.arange(256)) and (cb == 128).all() and (cr == 128).all()
     assert np.array_equal(jpeg_ref.ycc_to_rgb(y, cb, cr), grey)
+
+
+@pytest.mark.parametrize("shape", PREPROCESS_SHAPES + ["example"])
+def test_preprocess_matches_reference_bitwise(golden_dir, shape):
+    """Resize(256) -> CenterCrop(224) -> ToTensor restated (PIL's fixed-point resampling) against the reference's own
+    transform on PIL (tests/golden/preprocess_cases.npz): every byte equal, up- and down-scaling, odd sizes."""
+    g = np.load(golden_dir / "preprocess_cases.npz")
+    if shape == "example":
+        img, want = g["example_crop_in"], g["example_crop_out"]
+    else:
+        img, want = make_image(*shape), g["out_%dx%d" % shape]
+    got = preprocess_ref.load_image_tensor(img)
+    assert got.shape == (1, 3, 224, 224)
+    assert np.array_equal(got[0], want.astype(np.float32) / np.float32(255))
+
+
+def test_preprocess_geometry_and_to_pil():
+    assert preprocess_ref.resized_size(762, 1024) == (256, 344) and preprocess_ref.resized_size(500, 333) == (384, 256)
+    assert preprocess_ref.crop_offsets(256, 341) == (16, 58)          # Python round(58.5) = 58 (half to even)
+    assert preprocess_ref.crop_offsets(256, 343) == (16, 60)          # round(59.5) = 60
+    b, k = preprocess_ref.precompute_coeffs(512, 256)
+    assert k.shape[1] == 5 and int(k[7].sum()) == 1 << 22 and tuple(b[0]) == (0, 3)
+    with pytest.raises(ValueError):
+        preprocess_ref.resize_center_crop_u8(np.zeros((100, 1000, 3), np.uint8), 256, 300)
+    x = np.array([0.0, 0.5, 0.999, 1.0, 254.5 / 255], dtype=np.float32).reshape(1, 1, 5).repeat(3, 0)
+    assert preprocess_ref.to_pil_u8(x)[0, :, 0].tolist() == [0, 127, 254, 255, 254]
 
 
 @pytest.fixture(scope="module")
