@@ -258,7 +258,7 @@ def main():
         "clocks": clocks,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                      "frac": achieved / peak, "traffic": traffic,
-                     "kernel": "conv_gemm_kernel<BN> (tcgen05 implicit-GEMM conv, all fwd+dgrad launches)",
+                     "kernel": "conv_gemm_kernel<BN> + fused_block_kernel (tcgen05 implicit-GEMM convs, all fwd+dgrad launches)",
                      "peak_source": f"{peak_kind} bf16_tflops_sustained (kernel timed inside a long step)",
                      "launches_per_attack": int(conv_n.value), "conv_ms_per_attack": conv_ms.value,
                      "whole_step_tflops": step_tflops, "whole_step_frac": step_tflops / peak,

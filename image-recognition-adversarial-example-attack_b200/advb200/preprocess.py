@@ -29,7 +29,7 @@ class NativeTransform:
         else:
             if hasattr(img, "convert"):                       # PIL image
                 img = np.asarray(img.convert("RGB"))
-            u8 = torch.from_numpy(np.ascontiguousarray(img))
+            u8 = torch.from_numpy(np.array(img, copy=True))          # (PIL / npz arrays can be read-only)
         if u8.dtype != torch.uint8 or u8.ndim != 3 or u8.shape[2] != 3:
             raise ValueError("expected a decoded RGB image: uint8 [H, W, 3]")
         u8 = u8.to(self.device).contiguous()
