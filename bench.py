@@ -269,4 +269,11 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    try:
+        main()
+    finally:
+        try:
+            from advb200 import dist as _adist
+            _adist.shutdown()
+        except Exception:
+            pass

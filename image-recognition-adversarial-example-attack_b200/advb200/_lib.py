@@ -41,6 +41,10 @@ SIGNATURES = {
     "advb200_preprocess_scratch_bytes": (c_int64, [c_int, c_int, c_int, c_int]),
     "advb200_preprocess_u8": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int64, c_void_p]),
     "advb200_to_u8_hwc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "advb200_vgg19_create": (c_int, [POINTER(c_void_p)] * 4 + [c_void_p, POINTER(c_void_p)]),
+    "advb200_vgg19_destroy": (c_int, [c_void_p]),
+    "advb200_vgg19_workspace_bytes": (c_int64, [c_void_p, c_int]),
+    "advb200_vgg19_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
     "advb200_test_div9": (c_int, [c_void_p, c_void_p]),
     "advb200_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_void_p]),
     "advb200_attack_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_float,

@@ -77,3 +77,9 @@ def rates_from_counters(c) -> dict:
         "detector_adv_flag_rate": c[4] / count,
         "detector_attack_success": c[5] / count,
     }
+
+
+def shutdown() -> None:
+    """Tear the process group down (quietly a no-op for single-process runs)."""
+    if dist.is_available() and dist.is_initialized():
+        dist.destroy_process_group()

@@ -1442,6 +1442,164 @@ static int backward_impl(advb200_model* m, const float* dlogits, const float* st
   return rc;
 }
 
+// ================================================================================================================
+// Forward-only transfer target: VGG-19 (blackbox_transfer.py:25-54, 233-251).
+// 16 3x3 convs (bias + ReLU) through the same tcgen05 conv kernel, 2x2 max pools, and the three classifier layers as
+// pointwise convs over a [N, 1, 1, K] activation (bf16 operands, fp32 accumulation).  The image gets 61 zero channels
+// so the first conv runs the 64-channel halo path.  Activations ping-pong between two halves of the caller's workspace.
+// ================================================================================================================
+struct advb200_vgg19 {
+  static constexpr int kConvs = 16;
+  int device = 0;
+  bf16* wconv[kConvs] = {};
+  float* bconv[kConvs] = {};
+  bf16* wfc[3] = {};
+  float* bfc[3] = {};
+  std::vector<void*> owned;
+  // plan
+  int plan_n = -1;
+  void* plan_ws = nullptr;
+  struct Step { int kind = 0; std::vector<Op> ops; const void* in = nullptr; void* out = nullptr; int h = 0, w = 0, c = 0; };
+  std::vector<Step> steps;
+  bf16* input = nullptr;     // [N,224,224,64]
+  bf16* logits_bf16 = nullptr;   // [N,1024]
+};
+
+namespace {
+const int kVggCfg[] = {64, 64, -1, 128, 128, -1, 256, 256, 256, 256, -1, 512, 512, 512, 512, -1, 512, 512, 512, 512, -1};
+constexpr int kVggFcIn = 512 * 7 * 7, kVggFcHidden = 4096, kVggClassesPad = 1024;
+
+int64_t vgg_workspace_bytes(int n) { return 2 * (int64_t)n * kImg * kImg * 64 * 2 + 4096; }
+
+int vgg_plan(advb200_vgg19* m, int n, void* ws) {
+  m->steps.clear();
+  const int64_t half = (int64_t)n * kImg * kImg * 64 * 2;
+  char* buf[2] = {static_cast<char*>(ws), static_cast<char*>(ws) + half};
+  m->input = reinterpret_cast<bf16*>(buf[0]);
+  int cur = 0, h = kImg, c = 64, li = 0, rc = ADVB200_OK;
+  for (int v : kVggCfg) {
+    advb200_vgg19::Step st;
+    if (v < 0) {
+      st.kind = 1; st.in = buf[cur]; st.out = buf[cur ^ 1]; st.h = h; st.w = h; st.c = c;
+      h /= 2;
+    } else {
+      Act in{buf[cur], n, h, h, c}, out{buf[cur ^ 1], n, h, h, v};
+      rc = build_tc_ops(st.ops, m->wconv[li], 3, 1, false, in, out, m->bconv[li], nullptr, nullptr, 1);
+      if (rc) return rc;
+      c = v; ++li;
+    }
+    m->steps.push_back(std::move(st));
+    cur ^= 1;
+  }
+  // classifier: [N, 7*7*512] (NHWC flatten; the weights were permuted to match) -> 4096 -> 4096 -> 1000 (padded 1024)
+  const int dims[4] = {kVggFcIn, kVggFcHidden, kVggFcHidden, kVggClassesPad};
+  for (int i = 0; i < 3; ++i) {
+    advb200_vgg19::Step st;
+    Act in{buf[cur], n, 1, 1, dims[i]}, out{buf[cur ^ 1], n, 1, 1, dims[i + 1]};
+    rc = build_tc_ops(st.ops, m->wfc[i], 1, 1, false, in, out, m->bfc[i], nullptr, nullptr, i < 2 ? 1 : 0);
+    if (rc) return rc;
+    m->steps.push_back(std::move(st));
+    cur ^= 1;
+  }
+  m->logits_bf16 = reinterpret_cast<bf16*>(buf[cur]);
+  return ADVB200_OK;
+}
+}  // namespace
+
+int advb200_vgg19_create(const float* const* conv_w, const float* const* conv_b, const float* const* fc_w,
+                         const float* const* fc_b, void* stream, advb200_vgg19** out) {
+  ADV_CHECK_ARG(conv_w && conv_b && fc_w && fc_b && out, "vgg19_create: null argument");
+  int dev = 0, major = 0;
+  ADV_CHECK_CUDA(cudaGetDevice(&dev));
+  ADV_CHECK_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  if (major != 10) return fail(ADVB200_ERR_UNSUPPORTED, "libadvb200 requires an sm_100 (B200) device");
+  cudaStream_t st = as_stream(stream);
+  advb200_vgg19* m = new advb200_vgg19();
+  m->device = dev;
+  auto dalloc = [&](size_t bytes) -> void* {
+    void* p = nullptr;
+    if (cudaMalloc(&p, bytes) != cudaSuccess) return nullptr;
+    m->owned.push_back(p);
+    return p;
+  };
+  int rc = ADVB200_OK, cin = 3, li = 0;
+  float* padded = nullptr;
+  for (int v : kVggCfg) {
+    if (v < 0 || rc) continue;
+    if (!conv_w[li] || !conv_b[li]) { rc = fail(ADVB200_ERR_ARG, "vgg19_create: null weight"); break; }
+    const int cin_p = cin < 64 ? 64 : cin;
+    m->wconv[li] = (bf16*)dalloc((size_t)v * cin_p * 9 * 2);
+    m->bconv[li] = (float*)dalloc((size_t)v * 4);
+    if (!m->wconv[li] || !m->bconv[li]) { rc = fail(ADVB200_ERR_CUDA, "vgg19_create: cudaMalloc failed"); break; }
+    const float* w = conv_w[li];
+    if (cin_p != cin) {
+      padded = (float*)dalloc((size_t)v * cin_p * 9 * 4);
+      if (!padded) { rc = fail(ADVB200_ERR_CUDA, "vgg19_create: cudaMalloc failed"); break; }
+      if ((rc = launch_pad_cin(w, padded, v, cin, cin_p, 3, st))) break;
+      w = padded;
+    }
+    if ((rc = launch_pack_bf16(w, nullptr, m->wconv[li], nullptr, v, cin_p, 3, st))) break;
+    if ((rc = launch_pad_vec(conv_b[li], m->bconv[li], v, v, st))) break;
+    cin = v; ++li;
+  }
+  const int dims[4] = {kVggFcIn, kVggFcHidden, kVggFcHidden, kVggClassesPad};
+  const int real_out[3] = {kVggFcHidden, kVggFcHidden, kClasses};
+  for (int i = 0; i < 3 && !rc; ++i) {
+    if (!fc_w[i] || !fc_b[i]) { rc = fail(ADVB200_ERR_ARG, "vgg19_create: null weight"); break; }
+    m->wfc[i] = (bf16*)dalloc((size_t)dims[i + 1] * dims[i] * 2);
+    m->bfc[i] = (float*)dalloc((size_t)dims[i + 1] * 4);
+    if (!m->wfc[i] || !m->bfc[i]) { rc = fail(ADVB200_ERR_CUDA, "vgg19_create: cudaMalloc failed"); break; }
+    // fc1 consumes torch's NCHW flatten (c*49 + hw); the activations here are NHWC (hw*512 + c)
+    rc = launch_pack_fc_bf16(fc_w[i], m->wfc[i], real_out[i], dims[i + 1], i == 0 ? 512 : dims[i], i == 0 ? 49 : 1, st);
+    if (!rc) rc = launch_pad_vec(fc_b[i], m->bfc[i], real_out[i], dims[i + 1], st);
+  }
+  if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = fail(ADVB200_ERR_CUDA, "vgg19_create: packing failed");
+  if (rc) {
+    for (void* p : m->owned) cudaFree(p);
+    delete m;
+    return rc;
+  }
+  *out = m;
+  return ADVB200_OK;
+}
+
+int advb200_vgg19_destroy(advb200_vgg19* m) {
+  if (!m) return ADVB200_OK;
+  for (void* p : m->owned) cudaFree(p);
+  delete m;
+  return ADVB200_OK;
+}
+
+int64_t advb200_vgg19_workspace_bytes(const advb200_vgg19* m, int n) {
+  if (!m || n <= 0) return -1;
+  return vgg_workspace_bytes(n);
+}
+
+int advb200_vgg19_forward(advb200_vgg19* m, const float* x, const float* mean3, const float* std3, int n,
+                          float* logits_out, int64_t* preds_out, void* workspace, int64_t workspace_bytes, void* stream) {
+  ADV_CHECK_ARG(m && x && mean3 && std3 && workspace && (logits_out || preds_out), "vgg19_forward: null argument");
+  ADV_CHECK_ARG(n > 0, "vgg19_forward: batch must be positive");
+  ADV_CHECK_ARG((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, "vgg19_forward: workspace must be 1024-byte aligned");
+  ADV_CHECK_ARG(workspace_bytes >= vgg_workspace_bytes(n), "vgg19_forward: workspace too small");
+  ADV_CHECK_ARG(!preds_out || logits_out, "vgg19_forward: preds need the logits buffer");
+  cudaStream_t st = as_stream(stream);
+  int rc;
+  if (m->plan_n != n || m->plan_ws != workspace) {
+    m->plan_n = -1;
+    if ((rc = vgg_plan(m, n, workspace))) return rc;
+    m->plan_n = n; m->plan_ws = workspace;
+  }
+  if ((rc = launch_prep_nhwc64_bf16(x, mean3, std3, m->input, n, kImg, kImg, st))) return rc;
+  for (advb200_vgg19::Step& s : m->steps) {
+    if (s.kind == 1) rc = launch_maxpool2x2_bf16((const bf16*)s.in, (bf16*)s.out, n, s.h, s.w, s.c, st);
+    else rc = run_ops(s.ops, st);
+    if (rc) return rc;
+  }
+  if ((rc = launch_bf16_cols_to_f32(m->logits_bf16, kVggClassesPad, logits_out, n, kClasses, st))) return rc;
+  if (preds_out) rc = launch_argmax(logits_out, n, kClasses, preds_out, st);
+  return rc;
+}
+
 int advb200_test_force_tile(int bn, int pair, int bres, int slots) {
   // test hook: tile configuration of the next advb200_test_conv calls (-1 = default heuristic)
   g_force.bn = bn; g_force.pair = pair; g_force.bres = bres; g_force.slots = slots;

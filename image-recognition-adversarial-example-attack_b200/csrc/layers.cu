@@ -629,6 +629,89 @@ pack_mask_bits_kernel(const bf16* __restrict__ act, uint32_t* __restrict__ bits,
   bits[((long long)(c32 >> 1) * pixels + px) * 2 + (c32 & 1)] = w;
 }
 
+
+// ---- helpers of the forward-only transfer target (VGG-19, blackbox_transfer.py:25-54) -----------------------------
+// normalise fp32 NCHW [N,3,H,W] -> bf16 NHWC [N,H,W,64]: channels 0..2 carry the image, 3..63 are zero so the first
+// 3x3 conv runs through the same 64-channel tensor-core path as the rest
+__global__ void prep_nhwc64_kernel(const float* __restrict__ x, const float* __restrict__ mean3,
+                                   const float* __restrict__ std3, bf16* __restrict__ out, int h, int w, long long pixels) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;     // (pixel, 16-byte group 0..7)
+  if (t >= pixels * 8) return;
+  const long long px = t >> 3;
+  const int grp = (int)(t & 7);
+  uint4 v = make_uint4(0u, 0u, 0u, 0u);
+  if (grp == 0) {
+    const long long hw = (long long)h * w;
+    const long long n = px / hw, r = px % hw;
+    float c[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      c[k] = __fdiv_rn(__fsub_rn(__ldg(x + (n * 3 + k) * hw + r), __ldg(mean3 + k)), __ldg(std3 + k));   // attack.py:17
+    const __nv_bfloat162 a = __floats2bfloat162_rn(c[0], c[1]);
+    const __nv_bfloat162 b = __floats2bfloat162_rn(c[2], 0.f);
+    v.x = *reinterpret_cast<const uint32_t*>(&a);
+    v.y = *reinterpret_cast<const uint32_t*>(&b);
+  }
+  reinterpret_cast<uint4*>(out)[t] = v;
+}
+
+// 2x2 / stride 2 max pool, bf16 NHWC, 8 channels per thread
+__global__ void maxpool2x2_bf16x8_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, int hi, int wi, int c8,
+                                         long long total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;     // (n, ho, wo, c8)
+  if (t >= total) return;
+  const int ho_n = hi / 2, wo_n = wi / 2;
+  const int cg = (int)(t % c8);
+  const int wo = (int)((t / c8) % wo_n);
+  const int ho = (int)((t / ((long long)c8 * wo_n)) % ho_n);
+  const long long n = t / ((long long)c8 * wo_n * ho_n);
+  const uint4* src = reinterpret_cast<const uint4*>(in);
+  auto at = [&](int r, int q) { return __ldg(src + (((n * hi + 2 * ho + r) * wi + 2 * wo + q) * (long long)c8 + cg)); };
+  const uint4 a = at(0, 0), b = at(0, 1), c = at(1, 0), d = at(1, 1);
+  auto mx = [](uint32_t p, uint32_t q) {
+    const __nv_bfloat162 r = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&p), *reinterpret_cast<const __nv_bfloat162*>(&q));
+    return *reinterpret_cast<const uint32_t*>(&r);
+  };
+  uint4 o;
+  o.x = mx(mx(a.x, b.x), mx(c.x, d.x)); o.y = mx(mx(a.y, b.y), mx(c.y, d.y));
+  o.z = mx(mx(a.z, b.z), mx(c.z, d.z)); o.w = mx(mx(a.w, b.w), mx(c.w, d.w));
+  reinterpret_cast<uint4*>(out)[t] = o;
+}
+
+// classifier weights: fp32 [cout, C*HW] in torch's flatten order (c*HW + hw) -> bf16 [cout_pad, HW*C] in NHWC order
+// (hw*C + c); rows >= cout are zero (1000 classes padded to 1024 output channels)
+__global__ void pack_fc_bf16_kernel(const float* __restrict__ w, bf16* __restrict__ out, int cout, int cout_pad, int c,
+                                    int hw) {
+  const long long k = (long long)c * hw;
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)cout_pad * k) return;
+  const long long co = t / k, kk = t % k;
+  const int pos = (int)(kk / c), ch = (int)(kk % c);
+  out[t] = __float2bfloat16_rn(co < cout ? __ldg(w + co * k + (long long)ch * hw + pos) : 0.f);
+}
+
+__global__ void bf16_cols_to_f32_kernel(const bf16* __restrict__ in, int ld_in, float* __restrict__ out, int cols,
+                                        long long total) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  out[t] = __bfloat162float(in[(t / cols) * ld_in + t % cols]);
+}
+
+__global__ void pad_vec_kernel(const float* __restrict__ in, float* __restrict__ out, int n, int n_pad) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n_pad) out[t] = t < n ? in[t] : 0.f;
+}
+
+// first VGG conv: fp32 [cout, 3, k, k] -> fp32 [cout, 64, k, k] with zero channels 3..63
+__global__ void pad_cin_kernel(const float* __restrict__ w, float* __restrict__ out, int cout, int cin, int cin_pad, int kk) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)cout * cin_pad * kk) return;
+  const int rs = (int)(t % kk);
+  const int ci = (int)((t / kk) % cin_pad);
+  const long long co = t / ((long long)kk * cin_pad);
+  out[t] = ci < cin ? w[(co * cin + ci) * kk + rs] : 0.f;
+}
+
 }  // namespace
 
 __global__ void vec_add_kernel(const float* a, const float* b, float* out, int n) {
@@ -808,6 +891,42 @@ int launch_transpose_f32(const float* in, float* out, int rows, int cols, cudaSt
 int launch_f32_to_bf16(const float* in, bf16* out, int64_t n, cudaStream_t st) {
   if (!n) return ADVB200_OK;
   f32_to_bf16_kernel<<<nblocks(n), kT, 0, st>>>(in, out, n);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+
+int launch_prep_nhwc64_bf16(const float* x, const float* mean3, const float* std3, bf16* out, int n, int h, int w,
+                            cudaStream_t st) {
+  const long long pixels = (long long)n * h * w;
+  prep_nhwc64_kernel<<<nblocks(pixels * 8), kT, 0, st>>>(x, mean3, std3, out, h, w, pixels);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+int launch_maxpool2x2_bf16(const bf16* in, bf16* out, int n, int hi, int wi, int c, cudaStream_t st) {
+  ADV_CHECK_ARG(c % 8 == 0 && hi % 2 == 0 && wi % 2 == 0, "maxpool2x2: needs even sizes and c % 8 == 0");
+  const long long total = (long long)n * (hi / 2) * (wi / 2) * (c / 8);
+  maxpool2x2_bf16x8_kernel<<<nblocks(total), kT, 0, st>>>(in, out, hi, wi, c / 8, total);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+int launch_pack_fc_bf16(const float* w, bf16* out, int cout, int cout_pad, int c, int hw, cudaStream_t st) {
+  pack_fc_bf16_kernel<<<nblocks((long long)cout_pad * c * hw), kT, 0, st>>>(w, out, cout, cout_pad, c, hw);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+int launch_bf16_cols_to_f32(const bf16* in, int ld_in, float* out, int rows, int cols, cudaStream_t st) {
+  const long long total = (long long)rows * cols;
+  bf16_cols_to_f32_kernel<<<nblocks(total), kT, 0, st>>>(in, ld_in, out, cols, total);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+int launch_pad_vec(const float* in, float* out, int n, int n_pad, cudaStream_t st) {
+  pad_vec_kernel<<<nblocks(n_pad), kT, 0, st>>>(in, out, n, n_pad);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+int launch_pad_cin(const float* w, float* out, int cout, int cin, int cin_pad, int k, cudaStream_t st) {
+  pad_cin_kernel<<<nblocks((long long)cout * cin_pad * k * k), kT, 0, st>>>(w, out, cout, cin, cin_pad, k * k);
   ADV_LAUNCHED();
   return ADVB200_OK;
 }

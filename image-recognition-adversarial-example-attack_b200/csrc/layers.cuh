@@ -74,4 +74,13 @@ int launch_pack_mask_bits(const bf16* act, uint32_t* bits, long long pixels, int
 // dtype converters for the test hooks
 int launch_f32_to_bf16(const float* in, bf16* out, int64_t n, cudaStream_t st);
 
+// ---- forward-only transfer target (VGG-19) helpers
+int launch_prep_nhwc64_bf16(const float* x, const float* mean3, const float* std3, bf16* out, int n, int h, int w,
+                            cudaStream_t st);
+int launch_maxpool2x2_bf16(const bf16* in, bf16* out, int n, int hi, int wi, int c, cudaStream_t st);
+int launch_pack_fc_bf16(const float* w, bf16* out, int cout, int cout_pad, int c, int hw, cudaStream_t st);
+int launch_bf16_cols_to_f32(const bf16* in, int ld_in, float* out, int rows, int cols, cudaStream_t st);
+int launch_pad_vec(const float* in, float* out, int n, int n_pad, cudaStream_t st);
+int launch_pad_cin(const float* w, float* out, int cout, int cin, int cin_pad, int k, cudaStream_t st);
+
 }  // namespace advb200

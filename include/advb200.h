@@ -182,6 +182,20 @@ int advb200_preprocess_u8(const uint8_t* img_hwc, int h, int w, int size, int cr
 int advb200_to_u8_hwc(const float* x_chw, uint8_t* out_hwc, int h, int w, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Forward-only transfer target (blackbox_transfer.py:25-54, 233-251): torchvision VGG-19, eval mode.
+ * conv_w/conv_b: the 16 conv weights [cout,cin,3,3] / biases in feature order; fc_w/fc_b: classifier.0/.3/.6
+ * ([4096,25088], [4096,4096], [1000,4096]).  bf16 operands, fp32 accumulation; logits come back as fp32 [N,1000]
+ * (rounded to bf16 once, by the last layer).  workspace: advb200_vgg19_workspace_bytes(n), 1024-byte aligned.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct advb200_vgg19 advb200_vgg19;
+int advb200_vgg19_create(const float* const* conv_w, const float* const* conv_b, const float* const* fc_w,
+                         const float* const* fc_b, void* stream, advb200_vgg19** out);
+int advb200_vgg19_destroy(advb200_vgg19* m);
+int64_t advb200_vgg19_workspace_bytes(const advb200_vgg19* m, int n);
+int advb200_vgg19_forward(advb200_vgg19* m, const float* x, const float* mean3, const float* std3, int n,
+                          float* logits_out, int64_t* preds_out, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Evaluation counters (defense_experiments.py:597-637, 809-832)
  * counters int64 [7] += {clean_correct, attack_success, defense_preproc_success,
  *                        detector_flags_clean, detector_flags_adv, detector_attack_success, count}
