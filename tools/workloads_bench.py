@@ -107,4 +107,12 @@ torch.cuda.synchronize()
 sweep["ms_total"] = e0.elapsed_time(e1)
 sweep["images_per_s_per_config"] = 4 * n / (sweep["ms_total"] * 1e-3)
 out["defense_sweep_batch%d" % n] = sweep
+# transfer target: VGG-19 forward (19.63 GMAC / image), batch 128 chunks
+import torchvision  # noqa: E402
+from advb200.transfer import NativeVGG19  # noqa: E402
+torch.manual_seed(3)
+vgg = NativeVGG19(torchvision.models.vgg19(weights=None).eval().to(dev))
+xv = x[:128]
+ms = timed(lambda: vgg.forward(xv, mean, std), reps=5, warm=2)
+out["vgg19_forward_batch128"] = {"ms": ms, "images_per_s": 128 / (ms * 1e-3), "tflops": 128 * 2 * 19.63e9 / (ms * 1e-3) / 1e12}
 print(json.dumps(out, indent=1))
