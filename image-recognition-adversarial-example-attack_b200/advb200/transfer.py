@@ -106,7 +106,14 @@ class NativeVGG19:
         return self.forward(x_normalised, torch.zeros(3, device=dev), torch.ones(3, device=dev))
 
 
-def transfer_success_rate(target, x_adv: torch.Tensor, y_true: torch.Tensor, mean, std) -> float:
-    """Fraction of adversarial images the transfer target misclassifies (blackbox_transfer.py:233-251)."""
-    preds = target.forward(x_adv, mean, std).argmax(dim=1)
-    return float((preds != y_true.to(preds.device)).float().mean())
+def transfer_counts(target, x: torch.Tensor, x_adv: torch.Tensor, mean, std):
+    """(successes, total) under the reference's criterion (blackbox_transfer.py:233-251): the attack transfers to an
+    image when the target's prediction on the adversarial differs from ITS OWN prediction on the clean image."""
+    y_clean = target.forward(x, mean, std).argmax(dim=1)
+    y_adv = target.forward(x_adv, mean, std).argmax(dim=1)
+    return int((y_clean != y_adv).sum()), int(y_clean.numel())
+
+
+def transfer_success_rate(target, x: torch.Tensor, x_adv: torch.Tensor, mean, std) -> float:
+    s, t = transfer_counts(target, x, x_adv, mean, std)
+    return s / max(t, 1)

@@ -50,9 +50,10 @@ def test_vgg19_chunking_errors_and_transfer_rate(vgg):
     full = nm.forward(x, mean, std)
     nm.max_chunk = 2
     assert torch.equal(nm.forward(x, mean, std), full)
-    y = full.argmax(1)
-    assert transfer_success_rate(nm, x, y, mean, std) == 0.0
-    assert transfer_success_rate(nm, x, (y + 1) % 1000, mean, std) == 1.0
+    assert transfer_success_rate(nm, x, x, mean, std) == 0.0
+    flipped = transfer_success_rate(nm, x, 1.0 - x, mean, std)
+    want = float((full.argmax(1) != nm.forward(1.0 - x, mean, std).argmax(1)).float().mean())
+    assert flipped == want
     with pytest.raises(ValueError):
         nm.forward(x.cpu(), mean, std)
     with pytest.raises(ValueError):
@@ -61,3 +62,36 @@ def test_vgg19_chunking_errors_and_transfer_rate(vgg):
         NativeVGG19(torchvision.models.resnet18(weights=None).eval().cuda())
     with pytest.raises(ValueError):
         NativeVGG19(torchvision.models.vgg19(weights=None).cuda().train())
+
+
+def test_blackbox_transfer_cli_table(capsys):
+    """cli/blackbox_transfer.py end to end on synthetic images: the printed table has the reference's format
+    (blackbox_transfer.py:316-340) and its VGG-19 column equals the API computation."""
+    import importlib.util
+    from pathlib import Path
+
+    import advb200
+    from advb200.transfer import NativeVGG19, transfer_counts
+    root = Path(__file__).resolve().parent.parent / "image-recognition-adversarial-example-attack_b200"
+    spec = importlib.util.spec_from_file_location("advb200_cli_blackbox", root / "cli" / "blackbox_transfer.py")
+    cli = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(cli)
+    cli.main(["--synthetic", "6", "--weights", "random", "--seed", "0", "--attacks", "fgsm", "pgd", "--steps", "3",
+              "--batch", "4"])
+    lines = capsys.readouterr().out.strip().splitlines()
+    assert lines[0] == "Attack/Model\tVGG19\tViT\tSwin"
+    assert [l.split("\t")[0] for l in lines[1:]] == ["FGSM", "PGD", "CW"]
+    assert lines[3] == "CW\t0.0%\tn/a\tn/a"                       # not requested: 0 of 0, as in the reference
+
+    dev = torch.device("cuda")
+    src, vgg_m = cli.load_models("random", 0, dev)
+    source, target = advb200.native_model(src), NativeVGG19(vgg_m)
+    mean = torch.tensor([0.485, 0.456, 0.406], device=dev)
+    std = torch.tensor([0.229, 0.224, 0.225], device=dev)
+    x = torch.rand(6, 3, 224, 224, generator=torch.Generator().manual_seed(1234)).to(dev)
+    succ = 0
+    for lo in (0, 4):
+        xb = x[lo:lo + 4]
+        y = source.forward(xb, mean, std, want_logits=False, want_preds=True)["preds"]
+        succ += transfer_counts(target, xb, advb200.fgsm_attack(source, xb, y, eps=8 / 255, mean=mean, std=std), mean, std)[0]
+    assert lines[1].split("\t")[1] == f"{100.0 * succ / 6:.1f}%"
