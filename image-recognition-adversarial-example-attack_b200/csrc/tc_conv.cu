@@ -134,8 +134,13 @@ __device__ __forceinline__ uint32_t mapa_u32(const void* p, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(rank));
   return r;
 }
+// Remote arrive on the leader CTA's barrier (the follower's epilogue handing a TMEM accumulator back).  Default
+// semantics (release at CTA scope), as for the local arrive: what the leader's MMA warp must not overtake are this
+// warp's tcgen05.ld reads, and those are ordered by tcgen05.wait::ld + tcgen05.fence::before_thread_sync.  The
+// earlier `.release.cluster` form made ptxas emit MEMBAR.ALL.CTA + ERRBAR, which also waited for the warp's global
+// mask / output stores: 13-22 % of the samples of the pair-mode launches (ncu source view) sat on that fence.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA loads whose completion is signalled on the LEADER CTA's mbarrier (bar_cluster_addr)
 __device__ __forceinline__ void tma_load_4d_pair(const CUtensorMap* map, uint32_t bar_cluster_addr, void* dst, int c0,
