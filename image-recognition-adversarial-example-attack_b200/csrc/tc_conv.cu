@@ -807,10 +807,13 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + half * 32);
+        // The TMEM load of sub-tile j+1 is issued as soon as sub-tile j has been packed to bf16 (its fp32 registers
+        // are dead from there on), so it flies during the staging stores, the barrier and the TMA-store issue
+        // instead of being waited for at the top of the next sub-tile (ncu: ~6 % of the epilogue samples).
+        float f[32];
+        tmem_ld32f(taddr0, f);
 #pragma unroll
         for (int j = 0; j < kSub; ++j) {
-          float f[32];
-          tmem_ld32f(taddr0 + (uint32_t)(j * 64), f);
           const uint32_t obase = out0 + (uint32_t)(oslot * kSubTileBytes);
           tmem_ld_wait();
           if (j == kSub - 1) {
@@ -852,6 +855,7 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
               o[i].z = pack_bf16x2(f[8 * i + 4], f[8 * i + 5]); o[i].w = pack_bf16x2(f[8 * i + 6], f[8 * i + 7]);
             }
           }
+          if (j + 1 < kSub) tmem_ld32f(taddr0 + (uint32_t)((j + 1) * 64), f);
           if (n_out_slots == 0) {
             // direct mode: this thread's 32 channels (64 contiguous bytes of its pixel) go straight to global
             // memory — no staging tile, no barrier, and the smem goes to the operand ring instead
@@ -1250,10 +1254,10 @@ fused_block_kernel(const __grid_constant__ FusedBlockMaps maps, const __grid_con
       // each thread reads its row's 64 bytes from it, writes the result back IN PLACE, and the slot is TMA-stored.
       mbar_wait(d2_full, par);
       tc_fence_after();
+      float f[32];
+      tmem_ld32f(tmem_base + lane_off + (uint32_t)(64 + half * 32), f);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        float f[32];
-        tmem_ld32f(tmem_base + lane_off + (uint32_t)(64 + j * 64 + half * 32), f);
         mbar_wait(&res_full[rs], rphase);
         const uint32_t slot = res0 + (uint32_t)(rs * kSubTileBytes) + row_off;
         uint4 r[4];
@@ -1305,6 +1309,8 @@ fused_block_kernel(const __grid_constant__ FusedBlockMaps maps, const __grid_con
           }
           sts128(slot + ((((uint32_t)(half * 4 + i)) ^ sw) << 4), o);
         }
+        // next sub-tile's accumulator columns: in flight during the barrier and the store issue
+        if (j < 3) tmem_ld32f(tmem_base + lane_off + (uint32_t)(64 + (j + 1) * 64 + half * 32), f);
         fence_async_smem();
         epi_bar();
         if (etid == 0) {
