@@ -1168,10 +1168,10 @@ fused_block_kernel(const __grid_constant__ FusedBlockMaps maps, const __grid_con
       }
       mbar_wait(d1_full, par);
       tc_fence_after();
+      float f[32];
+      tmem_ld32f(tmem_base + lane_off, f);
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
-        float f[32];
-        tmem_ld32f(tmem_base + lane_off + (uint32_t)(half * 32), f);
         tmem_ld_wait();
         if (half == 1) tc_fence_before();
         if (p.bias1) {
@@ -1206,6 +1206,7 @@ fused_block_kernel(const __grid_constant__ FusedBlockMaps maps, const __grid_con
           }
           sts128(mid0 + row_off + ((((uint32_t)(half * 4 + i)) ^ sw) << 4), o);
         }
+        if (half == 0) tmem_ld32f(tmem_base + lane_off + 32u, f);   // second half in flight during the stores
       }
       fence_async_smem();                  // generic-proxy writes -> visible to the tensor core's operand reads
       asm volatile("bar.sync 2, 128;" ::: "memory");
