@@ -204,12 +204,30 @@ def main():
     for _ in pipe.run([xh, xh], itertools.cycle(outs)):
         pass
     adist.barrier(); torch.cuda.synchronize()
+    trace = os.environ.get("ADVB200_E2E_TRACE")
+    marks = []
+    if trace:                      # debug: device timeline of every step of the end-to-end loop
+        inner = pipe.fn
+
+        def traced(xd):
+            a = torch.cuda.Event(enable_timing=True); a.record()
+            r = inner(xd)
+            b = torch.cuda.Event(enable_timing=True); b.record()
+            marks.append((a, b, time.perf_counter()))
+            return r
+        pipe.fn = traced
+    t_host0 = time.perf_counter()
     e0.record()
     for _ in pipe.run((xh for _ in range(args.steps)), itertools.cycle(outs)):
         pass
     torch.cuda.current_stream().wait_stream(pipe.d2h)
     e1.record()
     torch.cuda.synchronize(); adist.barrier()
+    if trace and rank == 0:
+        print("e2e trace: total %.1f ms; attack start %s dur %s host-return %s" % (
+            e0.elapsed_time(e1), [round(e0.elapsed_time(m[0]), 1) for m in marks],
+            [round(m[0].elapsed_time(m[1]), 1) for m in marks],
+            [round((m[2] - t_host0) * 1e3, 1) for m in marks]), file=sys.stderr, flush=True)
     ms_e2e = adist.max_over_ranks(e0.elapsed_time(e1), device=dev)
     e2e = world * n * args.steps / (ms_e2e / 1e3)
     nbytes = xh.numel() * 4

@@ -49,8 +49,8 @@ class HostBatchPipeline:
 
     def run(self, batches: Iterable[torch.Tensor], outs: Optional[Iterable[torch.Tensor]] = None) -> Iterator[torch.Tensor]:
         """Yields one pinned host tensor of adversarial images per input batch, in order.  `outs` optionally
-        supplies the pinned result buffers (otherwise they are allocated).  A yielded tensor is complete when
-        this generator has advanced past it or `synchronize()` has been called."""
+        supplies the pinned result buffers (otherwise they are allocated; two buffers used in turn are enough —
+        batch i-2 is always handed out before batch i is written).  A yielded tensor is complete."""
         compute = torch.cuda.current_stream(self.device)
         it = iter(batches)
         out_it = iter(outs) if outs is not None else None
@@ -59,20 +59,27 @@ class HostBatchPipeline:
             return
         self._stage(0, nxt)
         i = 0
-        pending = None                      # (host result, its D2H event) of the previous batch
+        # Results are handed out TWO batches late: the host then never waits on a copy that finished less than a
+        # whole attack ago, and it enqueues the launches of batch i while the device is still working on batch
+        # i-1.  (Handing them out one batch late kept the host only one attack ahead of the device; an occasional
+        # host-side stall of a few tens of ms then starved the device: 1 run in 8 lost ~10 %.)
+        pending = []                        # [(host result, its D2H event)], oldest first, at most two
         while nxt is not None:
             k = i & 1
             cur = nxt
             nxt = next(it, None)
             if nxt is not None:
                 self._stage(k ^ 1, nxt)     # next batch's H2D overlaps this batch's attack
+            if len(pending) == 2:           # retire batch i-2 first: its host buffer may be the one batch i reuses
+                host_done, ev_done = pending.pop(0)
+                ev_done.synchronize()
+                yield host_done
             compute.wait_event(self._in_ready[k])
             x_adv = self.fn(self._in[k])
             # The result is copied (device to device, ~50 us) into a staging buffer this pipeline owns and the D2H
             # reads from there.  Handing the attack's own output tensor to the copy stream (record_stream) makes
             # the caching allocator wait on a cross-stream event before it can reuse the block; when that event is
-            # late it falls back to cudaMalloc, which synchronises the device — an occasional one-step bubble
-            # (measured: 1 run in 5 lost 15 %).
+            # late it falls back to cudaMalloc, which synchronises the device.
             if self._out[k] is None:
                 self._out[k] = torch.empty_like(x_adv)
             if self._out_free[k] is not None:
@@ -89,13 +96,11 @@ class HostBatchPipeline:
                 ev = torch.cuda.Event()
                 ev.record(self.d2h)
             self._out_free[k] = ev
-            if pending is not None:
-                pending[1].synchronize()
-                yield pending[0]
-            pending = (host, ev)
+            pending.append((host, ev))
             i += 1
-        pending[1].synchronize()
-        yield pending[0]
+        for host_done, ev_done in pending:
+            ev_done.synchronize()
+            yield host_done
 
     def synchronize(self) -> None:
         self.h2d.synchronize()

@@ -407,6 +407,15 @@ def test_host_batch_pipeline_equals_direct_calls(advb200_mod, native, dev):
     for b, r in zip(batches, got):
         want = fn(b.to(dev)).cpu()
         assert torch.equal(r, want)
+    # caller-supplied result buffers, two used in turn: batch i-2 is handed out before batch i overwrites its buffer
+    import itertools
+    outs = [torch.empty(3, 3, 224, 224).pin_memory() for _ in range(2)]
+    more = batches + [weights.synthetic_images(3, seed=60).pin_memory()]
+    got2 = [r.clone() for r in pipe.run(more, itertools.cycle(outs))]
+    assert len(got2) == 5
+    for b, r in zip(more, got2):
+        assert torch.equal(r, fn(b.to(dev)).cpu())
+    assert [r.clone() for r in pipe.run(batches[:1])][0].equal(got[0])          # a single batch drains correctly
     with pytest.raises(ValueError):
         list(pipe.run([torch.zeros(3, 3, 224, 224)]))
 
