@@ -38,8 +38,10 @@ def test_vgg19_logits_match_torchvision(vgg):
     assert torch.equal(nm(attacks_ref.normalize(x, mean, std)), got)
     one = nm.forward(x[4:5], mean, std)
     assert torch.equal(one, got[4:5])
-    top_w, top_g = want.topk(5, 1).indices, got.argmax(1)
-    assert all(int(top_g[i]) in top_w[i].tolist() for i in range(6))
+    # the class the native model picks is (within the bf16 error) the checker's best class
+    picked = want.gather(1, got.argmax(1, keepdim=True)).squeeze(1)
+    spread = want.max(1).values - want.min(1).values
+    assert bool((want.max(1).values - picked <= 0.05 * spread).all())
 
 
 def test_vgg19_chunking_errors_and_transfer_rate(vgg):
