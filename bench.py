@@ -90,7 +90,9 @@ def cpu_port_pgd(n_img: int, threads: int):
     noise = weights.pgd_noise(x.shape, EPS, 1)
     attacks_ref.pgd_linf(fm, x[:2], y[:2], eps=EPS, alpha=ALPHA, steps=1, mean=mean, std=std, noise=noise[:2])
     t0 = time.perf_counter()
-    attacks_ref.pgd_linf(fm, x, y, eps=EPS, alpha=ALPHA, steps=PGD_STEPS, mean=mean, std=std, noise=noise)
+    for lo in range(0, n_img, 16):     # batches of 16: the size at which the CPU path is most efficient (measured)
+        attacks_ref.pgd_linf(fm, x[lo:lo + 16], y[lo:lo + 16], eps=EPS, alpha=ALPHA, steps=PGD_STEPS, mean=mean, std=std,
+                             noise=noise[lo:lo + 16])
     dt = time.perf_counter() - t0
     return n_img / dt, dt
 
@@ -260,9 +262,9 @@ def main():
     cpu = None
     if not args.no_cpu_baseline and world == 1:
         threads = host_threads()
-        v, dt = cpu_port_pgd(16, threads)
+        v, dt = cpu_port_pgd(64, threads)
         cpu = {"value": v, "unit": "images/s", "cores": threads, "kind": "port",
-               "sample": f"oracle port of attack.pgd_linf_attack, PGD-10 on 16 of the 256 images, {dt:.1f} s"}
+               "sample": f"oracle port of attack.pgd_linf_attack, PGD-10 on 64 of the 256 images in batches of 16, {dt:.1f} s"}
     line = {
         "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": warm,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
