@@ -4,7 +4,7 @@ defense_experiments.py).  Python here is only the host-side mirror of the refere
 surface; all arithmetic runs in libadvb200.so (hand-written sm_100a CUDA behind a C ABI)."""
 from .attack import CWResult, cw_l2_attack, fgsm_attack, normalize_batch, pgd_linf_attack  # noqa: F401
 from .defenses import (  # noqa: F401
-    _defense_quantization, _defense_smoothing, _jpeg_compress_batch, _layer3_features, calibrate_feature_threshold,
+    _defense_median_smoothing, _defense_quantization, _defense_smoothing, _jpeg_compress_batch, _layer3_features, calibrate_feature_threshold,
     calibrate_threshold_from_scores, defend_input, evaluate_defenses, evaluate_defenses_batched,
     is_adversarial_by_feature, run_attack, COUNTER_KEYS,
 )

@@ -57,6 +57,7 @@ SIGNATURES = {
                                                      c_float, c_void_p]),
     "advb200_cw_finalize_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
     "advb200_smooth3x3_f32": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
+    "advb200_median3x3_f32": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     "advb200_quantize_f32": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "advb200_defend_input_f32": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
     "advb200_eval_counters": (c_int, [c_void_p] * 5 + [c_float, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),

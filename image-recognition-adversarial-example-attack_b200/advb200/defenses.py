@@ -49,6 +49,17 @@ def _defense_smoothing(x: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def _defense_median_smoothing(x: torch.Tensor) -> torch.Tensor:
+    """3x3 median smoothing (stride 1, zero pad 1) — not in the reference, whose `_defense_smoothing` is the 3x3
+    mean (defense_experiments.py:177-179); offered as an extra defense with the same calling convention."""
+    xc, planes, h, w = _as_planes(x)
+    out = torch.empty_like(xc)
+    with torch.cuda.device(xc.device):
+        rc = _lib.load().advb200_median3x3_f32(_lib.ptr(xc), _lib.ptr(out), planes, h, w, _lib.stream_ptr())
+    _lib.check(rc, "advb200_median3x3_f32")
+    return out
+
+
 def _defense_quantization(x: torch.Tensor, levels: int = 16) -> torch.Tensor:
     if not x.is_cuda:
         raise ValueError("x must be a CUDA tensor (no CPU fallback)")

@@ -422,6 +422,82 @@ __global__ void eval_counters_kernel(const int64_t* __restrict__ pred_clean,
   if (threadIdx.x < 7 && sc[threadIdx.x]) atomicAdd(&counters[threadIdx.x], (unsigned long long)sc[threadIdx.x]);
 }
 
+// 3x3 median (zero pad 1, stride 1) — the "median smoothing" defense the north star names beside the reference's
+// 3x3 mean (defense_experiments.py:177-179 keeps the mean; this is the same window and padding with the selection
+// in place of the average).  Pure selection, so the result is bit-exact whatever the order.  Same strip layout as
+// smooth3x3_kernel; the three vertical taps of every column are sorted once and shared by the three outputs that
+// use the column: median9 = med3(max of the column minima, med3 of the column medians, min of the column maxima).
+__device__ __forceinline__ float med3(float a, float b, float c) {
+  return fmaxf(fminf(a, b), fminf(fmaxf(a, b), c));
+}
+__global__ void __launch_bounds__(256, 4)
+median3x3_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t planes, int h, int w) {
+  const int groups = (w + 3) >> 2;
+  const int row_chunks = (h + kSmoothRows - 1) / kSmoothRows;
+  const int64_t total = planes * row_chunks * (int64_t)groups;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (int64_t)gridDim.x * blockDim.x) {
+    const int gx = (int)(t % groups);
+    const int rc = (int)((t / groups) % row_chunks);
+    const int64_t p = t / ((int64_t)groups * row_chunks);
+    const float* src = x + p * (int64_t)h * w;
+    float* dst = out + p * (int64_t)h * w;
+    const int c0 = gx * 4;
+    const int r0 = rc * kSmoothRows;
+    float win[kSmoothRows + 2][6];
+    const bool vec = ((w & 3) == 0) && ((reinterpret_cast<uintptr_t>(src) & 15u) == 0);
+#pragma unroll
+    for (int k = 0; k < kSmoothRows + 2; ++k) {
+      const int r = r0 - 1 + k;
+      float* v = win[k];
+      if (r < 0 || r >= h) {
+#pragma unroll
+        for (int j = 0; j < 6; ++j) v[j] = 0.f;
+      } else {
+        const float* row = src + (int64_t)r * w;
+        if (vec) {
+          const float4 m = __ldg(reinterpret_cast<const float4*>(row + c0));
+          v[0] = c0 > 0 ? __ldg(row + c0 - 1) : 0.f;
+          v[1] = m.x; v[2] = m.y; v[3] = m.z; v[4] = m.w;
+          v[5] = c0 + 4 < w ? __ldg(row + c0 + 4) : 0.f;
+        } else {
+#pragma unroll
+          for (int j = 0; j < 6; ++j) {
+            const int c = c0 - 1 + j;
+            v[j] = (c >= 0 && c < w) ? __ldg(row + c) : 0.f;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int dr = 0; dr < kSmoothRows; ++dr) {
+      const int r = r0 + dr;
+      if (r >= h) break;
+      float lo[6], mid[6], hi[6];
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        const float a = win[dr][j], b = win[dr + 1][j], c = win[dr + 2][j];
+        lo[j] = fminf(fminf(a, b), c);
+        hi[j] = fmaxf(fmaxf(a, b), c);
+        mid[j] = med3(a, b, c);
+      }
+      float o4[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        o4[j] = med3(fmaxf(fmaxf(lo[j], lo[j + 1]), lo[j + 2]), med3(mid[j], mid[j + 1], mid[j + 2]),
+                     fminf(fminf(hi[j], hi[j + 1]), hi[j + 2]));
+      float* orow = dst + (int64_t)r * w;
+      if (vec) {
+        *reinterpret_cast<float4*>(orow + c0) = make_float4(o4[0], o4[1], o4[2], o4[3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (c0 + j < w) orow[c0 + j] = o4[j];
+      }
+    }
+  }
+}
+
 }  // namespace
 }  // namespace advb200
 
@@ -493,6 +569,17 @@ static int smooth_launch(const float* x, float* out, int64_t planes, int h, int 
 
 int advb200_smooth3x3_f32(const float* x, float* out, int64_t planes, int h, int w, void* stream) {
   return smooth_launch(x, out, planes, h, w, 2, false, stream);
+}
+
+int advb200_median3x3_f32(const float* x, float* out, int64_t planes, int h, int w, void* stream) {
+  ADV_CHECK_ARG(planes >= 0 && h > 0 && w > 0, "median3x3: bad sizes");
+  if (planes == 0) return ADVB200_OK;
+  ADV_CHECK_ARG(x && out, "median3x3: null pointer");
+  ADV_CHECK_ARG(x != out, "median3x3: in-place operation is not supported");
+  const int groups = (w + 3) / 4, chunks = (h + kSmoothRows - 1) / kSmoothRows;
+  median3x3_kernel<<<grid_for(planes * (int64_t)groups * chunks), 256, 0, as_stream(stream)>>>(x, out, planes, h, w);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
 }
 
 int advb200_test_div9(uint64_t* mismatches_host, uint32_t* first_bad_host) {

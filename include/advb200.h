@@ -151,6 +151,10 @@ int advb200_cw_finalize_f32(const float* x_adv, const float* best_adv, const uin
  * ------------------------------------------------------------------------------------------ */
 /* 3x3 mean, stride 1, zero pad 1, divisor 9 (F.avg_pool2d(x,3,1,1)); bit-exact vs torch CPU */
 int advb200_smooth3x3_f32(const float* x, float* out, int64_t planes, int h, int w, void* stream);
+/* 3x3 median, stride 1, zero pad 1: the median-smoothing defense named in the build's brief; same window and padding
+ * as the reference's mean smoothing (defense_experiments.py:177-179), selection instead of average.  Exact (a
+ * selection), NaN-free inputs assumed.  x != out. */
+int advb200_median3x3_f32(const float* x, float* out, int64_t planes, int h, int w, void* stream);
 /* round(clamp(x,0,1)*(levels-1))/(levels-1), round-half-even, true division; bit-exact */
 int advb200_quantize_f32(const float* x, float* out, int64_t n_elems, int levels, void* stream);
 /* defend_input without JPEG: clamp -> smooth -> quantize(16) -> clamp, one pass */

@@ -22,6 +22,18 @@ def smooth3x3(x: np.ndarray) -> np.ndarray:
     return (s / np.float32(9.0)).astype(np.float32)
 
 
+def median3x3(x: np.ndarray) -> np.ndarray:
+    """3x3 median, stride 1, zero pad 1 (the window and padding of defense_experiments.py:177-179 with the median in
+    place of the mean).  Not a reference function: the oracle for the extra median-smoothing defense; pinned against
+    scipy.ndimage.median_filter(mode="constant") in tests/test_oracle_golden.py."""
+    x = np.asarray(x, dtype=np.float32)
+    n, c, h, w = x.shape
+    p = np.zeros((n, c, h + 2, w + 2), dtype=np.float32)
+    p[:, :, 1:-1, 1:-1] = x
+    taps = np.stack([p[:, :, dr:dr + h, dc:dc + w] for dr in range(3) for dc in range(3)])
+    return np.sort(taps, axis=0)[4]
+
+
 def quantize(x: np.ndarray, levels: int = 16) -> np.ndarray:
     """defense_experiments.py:182-185: round-half-even of clamp(x,0,1)*(levels-1), TRUE division."""
     x = np.asarray(x, dtype=np.float32)

@@ -113,6 +113,33 @@ def test_defenses_bit_exact_vs_golden_and_oracle(advb200_mod, dev, golden_dir):
     assert float(s[0, 0, 5, 5]) == 1.0 and float(s[0, 0, 0, 0]) == np.float32(4.0) / np.float32(9.0)
 
 
+def test_median_smoothing_exact_vs_oracle(advb200_mod, dev):
+    """Extra defense (3x3 median, zero pad): a selection, so bit-exact against the oracle; ragged widths take the
+    scalar path, multiples of four the 128-bit one; plus the properties a median has at any size."""
+    gen = torch.Generator().manual_seed(21)
+    for shape in ((16, 3, 224, 224), (2, 3, 17, 23), (1, 1, 1, 1), (1, 2, 1, 9), (1, 1, 6, 2), (3, 1, 5, 8)):
+        xb = torch.rand(*shape, generator=gen) * 1.2 - 0.1
+        got = advb200_mod._defense_median_smoothing(xb.to(dev)).cpu().numpy()
+        assert np.array_equal(got, defenses_ref.median3x3(xb.numpy())), shape
+    # a misaligned view (plane base not 16-byte aligned) must take the scalar path and still agree
+    buf = torch.rand(1 + 2 * 3 * 8 * 8, generator=gen)
+    xv = buf[1:].view(2, 3, 8, 8)
+    dv = buf.to(dev)[1:].view(2, 3, 8, 8)
+    from advb200 import _lib
+    out = torch.empty(2, 3, 8, 8, device=dev)
+    assert _lib.load().advb200_median3x3_f32(_lib.ptr(dv), _lib.ptr(out), 6, 8, 8, _lib.stream_ptr()) == 0
+    assert np.array_equal(out.cpu().numpy(), defenses_ref.median3x3(xv.numpy()))
+    ones = torch.ones(1, 1, 224, 224, device=dev)
+    m = advb200_mod._defense_median_smoothing(ones)
+    assert float(m[0, 0, 5, 5]) == 1.0 and float(m[0, 0, 0, 0]) == 0.0 and float(m[0, 0, 0, 5]) == 1.0
+    big = torch.rand(64, 3, 224, 224, device=dev)
+    mb = advb200_mod._defense_median_smoothing(big)
+    assert float(mb.min()) >= 0.0 and float(mb.max()) <= float(big.max())
+    assert _lib.load().advb200_median3x3_f32(_lib.ptr(big), _lib.ptr(big), 192, 224, 224, _lib.stream_ptr()) != 0
+    with pytest.raises(ValueError):
+        advb200_mod._defense_median_smoothing(torch.rand(3, 8, 8, device=dev))
+
+
 def test_divide_by_nine_shortcut_is_exact_for_every_float(advb200_mod):
     """The smoothing kernels divide by 9 with one multiply and two FMAs instead of the generic division sequence;
     the device checks it against __fdiv_rn for all 2^32 bit patterns."""

@@ -42,6 +42,17 @@ def test_cw_matches_reference(golden_dir):
         attacks_ref.cw_l2(model, x, y, mean=mean, std=std, targeted=True)
 
 
+def test_median_oracle_matches_scipy():
+    """The median-smoothing defense has no counterpart in the reference (its smoothing is the 3x3 mean), so its oracle
+    is pinned against an independent implementation: scipy's median filter with constant-zero borders."""
+    from scipy import ndimage
+    rng = np.random.default_rng(11)
+    for shape in ((2, 3, 17, 23), (1, 1, 1, 1), (1, 2, 1, 9), (1, 1, 6, 2), (1, 3, 224, 224)):
+        x = (rng.random(shape, dtype=np.float32) * 1.2 - 0.1).astype(np.float32)
+        want = ndimage.median_filter(x, size=(1, 1, 3, 3), mode="constant", cval=0.0)
+        assert np.array_equal(defenses_ref.median3x3(x), want)
+
+
 def test_defenses_match_reference_bitwise(golden_dir):
     g = np.load(golden_dir / "defense_small.npz")
     assert np.array_equal(defenses_ref.smooth3x3(g["x"]), g["smooth"])

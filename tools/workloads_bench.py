@@ -6,6 +6,7 @@
 Usage: python tools/workloads_bench.py [batch] > gpurun_out/workloads.json"""
 import ctypes
 import json
+import os
 import sys
 from pathlib import Path
 
@@ -62,12 +63,17 @@ planes, H, W = n * 3, x.shape[2], x.shape[3]
 rec("linf_step(project)", timed(lambda: lib.advb200_linf_step_f32(P(xa), P(x0), P(g), 2 / 255, 8 / 255, elems, 1, S())), 16)
 rec("linf_step(fgsm)", timed(lambda: lib.advb200_linf_step_f32(P(xa), None, P(g), 8 / 255, 8 / 255, elems, 0, S())), 12)
 rec("smooth3x3", timed(lambda: lib.advb200_smooth3x3_f32(P(x), P(out_buf), planes, H, W, S())), 8)
+rec("median3x3", timed(lambda: lib.advb200_median3x3_f32(P(x), P(out_buf), planes, H, W, S())), 8)
 rec("quantize16", timed(lambda: lib.advb200_quantize_f32(P(x), P(out_buf), elems, 16, S())), 8)
 rec("defend_input", timed(lambda: lib.advb200_defend_input_f32(P(x), P(out_buf), planes, H, W, 16, S())), 8)
 # JPEG round trip: 12 B/pixel in + 12 B/pixel out + 3 B/pixel of uint8 scratch (written, then read) = 27 B/pixel = 9 B/elem
 jbytes = int(lib.advb200_jpeg_scratch_bytes(n, H, W))
 jscratch = torch.empty(jbytes, dtype=torch.uint8, device=dev)
 rec("jpeg_q75", timed(lambda: lib.advb200_jpeg_roundtrip_f32(P(x), P(out_buf), n, H, W, 75, P(jscratch), jbytes, S())), 9)
+
+if os.environ.get("ADVB200_WORKLOADS_KERNELS_ONLY") == "1":       # just the HBM-bound kernels (seconds)
+    print(json.dumps(out))
+    sys.exit(0)
 
 model = weights.seeded_resnet50(0).to(dev)
 mean, std = weights.mean_std()
