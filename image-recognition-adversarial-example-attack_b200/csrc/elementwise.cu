@@ -469,30 +469,42 @@ median3x3_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t p
         }
       }
     }
+    // two output rows share the ordered pair of their two common input rows (per column: 2 + 2 x 4 operations instead
+    // of 2 x 6), and two neighbouring outputs share the ordered pair of their two common column medians
 #pragma unroll
-    for (int dr = 0; dr < kSmoothRows; ++dr) {
-      const int r = r0 + dr;
-      if (r >= h) break;
-      float lo[6], mid[6], hi[6];
+    for (int dp = 0; dp < kSmoothRows; dp += 2) {
+      float lo[2][6], mid[2][6], hi[2][6];
 #pragma unroll
       for (int j = 0; j < 6; ++j) {
-        const float a = win[dr][j], b = win[dr + 1][j], c = win[dr + 2][j];
-        lo[j] = fminf(fminf(a, b), c);
-        hi[j] = fmaxf(fmaxf(a, b), c);
-        mid[j] = med3(a, b, c);
+        const float plo = fminf(win[dp + 1][j], win[dp + 2][j]), phi = fmaxf(win[dp + 1][j], win[dp + 2][j]);
+        const float a = win[dp][j], c = win[dp + 3][j];
+        lo[0][j] = fminf(a, plo); hi[0][j] = fmaxf(a, phi); mid[0][j] = fmaxf(plo, fminf(a, phi));
+        lo[1][j] = fminf(c, plo); hi[1][j] = fmaxf(c, phi); mid[1][j] = fmaxf(plo, fminf(c, phi));
       }
-      float o4[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
-        o4[j] = med3(fmaxf(fmaxf(lo[j], lo[j + 1]), lo[j + 2]), med3(mid[j], mid[j + 1], mid[j + 2]),
-                     fminf(fminf(hi[j], hi[j + 1]), hi[j + 2]));
-      float* orow = dst + (int64_t)r * w;
-      if (vec) {
-        *reinterpret_cast<float4*>(orow + c0) = make_float4(o4[0], o4[1], o4[2], o4[3]);
-      } else {
+      for (int q = 0; q < 2; ++q) {
+        const int dr = dp + q;
+        const int r = r0 + dr;
+        if (r >= h) break;
+        float o4[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (c0 + j < w) orow[c0 + j] = o4[j];
+        for (int j = 0; j < 4; j += 2) {
+          const float mlo = fminf(mid[q][j + 1], mid[q][j + 2]), mhi = fmaxf(mid[q][j + 1], mid[q][j + 2]);
+          const float m0 = fmaxf(mlo, fminf(mid[q][j], mhi));
+          const float m1 = fmaxf(mlo, fminf(mid[q][j + 3], mhi));
+          o4[j] = med3(fmaxf(fmaxf(lo[q][j], lo[q][j + 1]), lo[q][j + 2]), m0,
+                       fminf(fminf(hi[q][j], hi[q][j + 1]), hi[q][j + 2]));
+          o4[j + 1] = med3(fmaxf(fmaxf(lo[q][j + 1], lo[q][j + 2]), lo[q][j + 3]), m1,
+                           fminf(fminf(hi[q][j + 1], hi[q][j + 2]), hi[q][j + 3]));
+        }
+        float* orow = dst + (int64_t)r * w;
+        if (vec) {
+          *reinterpret_cast<float4*>(orow + c0) = make_float4(o4[0], o4[1], o4[2], o4[3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (c0 + j < w) orow[c0 + j] = o4[j];
+        }
       }
     }
   }
