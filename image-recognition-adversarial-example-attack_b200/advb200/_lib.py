@@ -7,7 +7,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import POINTER, c_char_p, c_float, c_int, c_int64, c_uint8, c_void_p
+from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int64, c_uint8, c_void_p
 from pathlib import Path
 
 _PKG_DIR = Path(__file__).resolve().parent.parent
@@ -53,8 +53,8 @@ SIGNATURES = {
     "advb200_random_start_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
     "advb200_cw_parts": (c_int, [c_int64]),
     "advb200_cw_init_f32": (c_int, [c_void_p] * 10 + [c_int, c_int64, c_void_p]),
-    "advb200_cw_step_f32": (c_int, [c_void_p] * 13 + [c_int, c_int64, c_float, c_float, c_float, c_float,
-                                                     c_float, c_void_p]),
+    "advb200_cw_step_f32": (c_int, [c_void_p] * 13 + [c_int, c_int64, c_float, c_float, c_double, c_double,
+                                                     c_double, c_void_p]),
     "advb200_cw_finalize_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
     "advb200_smooth3x3_f32": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     "advb200_median3x3_f32": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
@@ -63,6 +63,8 @@ SIGNATURES = {
     "advb200_eval_counters": (c_int, [c_void_p] * 5 + [c_float, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "advb200_test_conv": (c_int, [c_int] + [c_void_p] * 6 + [c_int] * 9 + [c_void_p]),
     "advb200_test_force_tile": (c_int, [c_int, c_int, c_int, c_int]),
+    "advb200_debug_trace": (c_int, [c_void_p, c_int64]),
+    "advb200_debug_trace_index": (c_int64, [c_char_p, c_int64]),
     "advb200_launch_count": (c_int64, []),
     "advb200_profile_enable": (c_int, [c_int]),
     "advb200_profile_read": (c_int, [POINTER(ctypes.c_double), POINTER(c_int64)]),

@@ -47,6 +47,21 @@ def _check_common(x, mean, std):
         raise ValueError("x must be a 4D tensor with shape [N, C, H, W]")
 
 
+def _check_labels(y: torch.Tensor, n: int, classes: int = 1000) -> torch.Tensor:
+    """int64 [N] labels on the host's word: F.cross_entropy / one_hot raise on a label outside [0, classes) in the
+    reference (attack.py:31,114); here the check runs once per attack call (one tiny device read), not per step."""
+    if y.ndim != 1 or y.shape[0] != n:
+        raise ValueError("labels must have shape [N]")
+    if n and bool(((y < 0) | (y >= classes)).any()):
+        raise ValueError(f"labels must lie in [0, {classes})")
+    return y
+
+
+def _dev_vec(t: torch.Tensor, device) -> torch.Tensor:
+    """mean / std moved to the device ONCE per attack call (the per-step calls then reuse the device tensor)."""
+    return t.detach().to(device=device, dtype=torch.float32).contiguous() if t.ndim == 1 else t
+
+
 def _linf_step(x_adv, x_orig, grad, alpha, eps, project):
     lib = _lib.load()
     rc = lib.advb200_linf_step_f32(_lib.ptr(x_adv), _lib.ptr(x_orig), _lib.ptr(grad), float(alpha), float(eps),
@@ -62,6 +77,8 @@ def fgsm_attack(model, x: torch.Tensor, y_true: torch.Tensor, *, eps: float, mea
         x_adv = x.detach().to(torch.float32).clone().contiguous()
         if x_adv.shape[0] == 0:
             return x_adv
+        _check_labels(y_true, x_adv.shape[0])
+        mean, std = _dev_vec(mean, x.device), _dev_vec(std, x.device)
         if nm.precision == "bf16" and _FUSED_STEP:
             nm.attack_step(x_adv, None, mean, std, y_true, alpha=eps, eps=eps, inv_n_global=inv_n_global)
         else:
@@ -72,8 +89,13 @@ def fgsm_attack(model, x: torch.Tensor, y_true: torch.Tensor, *, eps: float, mea
 
 def pgd_linf_attack(model, x: torch.Tensor, y_true: torch.Tensor, *, eps: float, alpha: float, steps: int,
                     mean: torch.Tensor, std: torch.Tensor, random_start: bool = True,
-                    inv_n_global: Optional[float] = None) -> torch.Tensor:
+                    inv_n_global: Optional[float] = None, noise: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """attack.py:37-65.  Extras beyond the reference signature (both optional): `inv_n_global` (gradient scale of a
+    sharded batch) and `noise`, a caller-drawn U(-eps,eps) start tensor used instead of drawing one here — the parity
+    harness injects the tensor the reference drew (CPU generator != CUDA Philox stream)."""
     _check_common(x, mean, std)
+    if noise is not None and tuple(noise.shape) != tuple(x.shape):
+        raise ValueError("noise must have the shape of x")
     nm = native_model(model)
     lib = _lib.load()
     with torch.cuda.device(x.device):
@@ -81,22 +103,33 @@ def pgd_linf_attack(model, x: torch.Tensor, y_true: torch.Tensor, *, eps: float,
         x_adv = torch.empty_like(x_orig)
         if x_orig.shape[0] == 0:
             return x_adv
-        if random_start:
-            noise = torch.empty_like(x_orig).uniform_(-eps, eps)      # attack.py:51, torch's generator
+        if random_start or noise is not None:
+            if noise is None:
+                noise = torch.empty_like(x_orig).uniform_(-eps, eps)      # attack.py:51, torch's generator
+            noise = noise.detach().to(device=x_orig.device, dtype=torch.float32).contiguous()
             rc = lib.advb200_random_start_f32(_lib.ptr(x_adv), _lib.ptr(x_orig), _lib.ptr(noise),
                                               x_adv.numel(), _lib.stream_ptr())
             _lib.check(rc, "advb200_random_start_f32")
         else:
             x_adv.copy_(x_orig)
-        if nm.precision == "bf16" and _FUSED_STEP:
-            # fused step: the sign step / projection / clamp run in the stem input-gradient kernel's epilogue
+        n = x_orig.shape[0]
+        _check_labels(y_true, n)
+        mean, std = _dev_vec(mean, x.device), _dev_vec(std, x.device)
+        y_dev = y_true.detach().to(device=x.device, dtype=torch.int64).contiguous()
+        inv = 1.0 / n if inv_n_global is None else inv_n_global        # CE is a mean over the WHOLE batch (attack.py:58)
+        # images are independent, so a batch larger than one workspace chunk runs all its steps chunk by chunk: the
+        # engine keeps one launch plan per (batch size, workspace) and is not re-planned between steps
+        grad = torch.empty((min(n, nm.max_chunk),) + tuple(x_orig.shape[1:]), dtype=torch.float32, device=x.device)
+        for lo in range(0, n, nm.max_chunk):
+            hi = min(n, lo + nm.max_chunk)
+            xa, xo, yy, g = x_adv[lo:hi], x_orig[lo:hi], y_dev[lo:hi], grad[:hi - lo]
             for _ in range(int(steps)):
-                nm.attack_step(x_adv, x_orig, mean, std, y_true, alpha=alpha, eps=eps, inv_n_global=inv_n_global)
-        else:
-            grad = torch.empty_like(x_orig)
-            for _ in range(int(steps)):
-                nm.input_grad(x_adv, mean, std, y_true, loss="ce", inv_n_global=inv_n_global, grad_out=grad)
-                _linf_step(x_adv, x_orig, grad, alpha, eps, project=True)
+                if nm.precision == "bf16" and _FUSED_STEP:
+                    # fused step: the sign step / projection / clamp run in the stem input-gradient kernel's epilogue
+                    nm.attack_step(xa, xo, mean, std, yy, alpha=alpha, eps=eps, inv_n_global=inv)
+                else:
+                    nm.input_grad(xa, mean, std, yy, loss="ce", inv_n_global=inv, grad_out=g)
+                    _linf_step(xa, xo, g, alpha, eps, project=True)
     return x_adv
 
 
@@ -124,39 +157,48 @@ def cw_l2_attack(model, x: torch.Tensor, y_true: torch.Tensor, *, mean: torch.Te
             return CWResult(x_adv=xin.clone(), success=torch.zeros((0,), dtype=torch.bool, device=dev))
         per = xin[0].numel()
         parts = int(lib.advb200_cw_parts(per))
-        x0, w, m, v, x_adv, best_adv = (torch.empty_like(xin) for _ in range(6))
+        y_cmp = y_target if targeted else y_true
+        _check_labels(y_cmp, n)
+        y_cmp = y_cmp.detach().to(device=dev, dtype=torch.int64).contiguous()
+        mean, std = _dev_vec(mean, dev), _dev_vec(std, dev)
+        loss = "cw_targeted" if targeted else "cw"
+        final = torch.empty_like(xin)
         best_l2 = torch.empty((n,), dtype=torch.float32, device=dev)
         best_success = torch.empty((n,), dtype=torch.uint8, device=dev)
-        success = torch.empty((n,), dtype=torch.uint8, device=dev)
-        l2_now = torch.empty((n,), dtype=torch.float32, device=dev)
-        # [N*parts floats] + N flag bytes (the step kernel keeps its `improved` flags in the tail)
-        pa = torch.empty((n * parts + (n + 3) // 4 + 1,), dtype=torch.float32, device=dev)
-        pb = torch.empty_like(pa)
-        grad = torch.empty_like(xin)
-        rc = lib.advb200_cw_init_f32(_lib.ptr(xin), _lib.ptr(x0), _lib.ptr(w), _lib.ptr(m), _lib.ptr(v),
-                                     _lib.ptr(x_adv), _lib.ptr(best_adv), _lib.ptr(best_l2),
-                                     _lib.ptr(best_success), _lib.ptr(pa), n, per, _lib.stream_ptr())
-        _lib.check(rc, "advb200_cw_init_f32")
-        y_cmp = y_target if targeted else y_true
-        loss = "cw_targeted" if targeted else "cw"
-        for t in range(1, int(steps) + 1):
-            # forward + margin-loss input gradient at the current iterate; success flags of attack.py:121,124
-            nm.input_grad(x_adv, mean, std, y_cmp, loss=loss, c=c, kappa=kappa, grad_out=grad,
-                          success_out=success)
-            # Adam scalars in double on the host, like torch's single-tensor path
-            step_size = lr / (1.0 - beta1 ** t)
-            bc2_sqrt = math.sqrt(1.0 - beta2 ** t)
-            rc = lib.advb200_cw_step_f32(_lib.ptr(w), _lib.ptr(m), _lib.ptr(v), _lib.ptr(x0), _lib.ptr(grad),
-                                         _lib.ptr(x_adv), _lib.ptr(best_adv), _lib.ptr(best_l2),
-                                         _lib.ptr(best_success), _lib.ptr(success), _lib.ptr(pa), _lib.ptr(pb),
-                                         _lib.ptr(l2_now), n, per, step_size, bc2_sqrt, beta1, beta2, adam_eps,
+        # CW's objective is a sum over images (attack.py:127), so chunks of the batch are independent problems: each
+        # chunk runs all its steps on one launch plan and one set of state arrays
+        chunk = min(n, nm.max_chunk)
+        x0, w, m, v, x_adv, best_adv, grad = (torch.empty((chunk,) + tuple(xin.shape[1:]), dtype=torch.float32, device=dev)
+                                              for _ in range(7))
+        success = torch.empty((chunk,), dtype=torch.uint8, device=dev)
+        l2_now = torch.empty((chunk,), dtype=torch.float32, device=dev)
+        for lo in range(0, n, chunk):
+            hi = min(n, lo + chunk)
+            k = hi - lo
+            # [k*parts floats] + k flag bytes (the step kernel keeps its `improved` flags in the tail)
+            pa = torch.empty((k * parts + (k + 3) // 4 + 1,), dtype=torch.float32, device=dev)
+            pb = torch.empty_like(pa)
+            bl2, bs = best_l2[lo:hi], best_success[lo:hi]
+            rc = lib.advb200_cw_init_f32(_lib.ptr(xin[lo:hi]), _lib.ptr(x0), _lib.ptr(w), _lib.ptr(m), _lib.ptr(v),
+                                         _lib.ptr(x_adv), _lib.ptr(best_adv), _lib.ptr(bl2), _lib.ptr(bs), _lib.ptr(pa), k, per,
                                          _lib.stream_ptr())
-            _lib.check(rc, "advb200_cw_step_f32")
-            pa, pb = pb, pa
-        final = torch.empty_like(xin)
-        rc = lib.advb200_cw_finalize_f32(_lib.ptr(x_adv), _lib.ptr(best_adv), _lib.ptr(best_success),
-                                         _lib.ptr(final), n, per, _lib.stream_ptr())
-        _lib.check(rc, "advb200_cw_finalize_f32")
+            _lib.check(rc, "advb200_cw_init_f32")
+            for t in range(1, int(steps) + 1):
+                # forward + margin-loss input gradient at the current iterate; success flags of attack.py:121,124
+                nm.input_grad(x_adv[:k], mean, std, y_cmp[lo:hi], loss=loss, c=c, kappa=kappa, grad_out=grad[:k],
+                              success_out=success[:k])
+                # Adam scalars in double on the host, like torch's single-tensor path
+                step_size = lr / (1.0 - beta1 ** t)
+                bc2_sqrt = math.sqrt(1.0 - beta2 ** t)
+                rc = lib.advb200_cw_step_f32(_lib.ptr(w), _lib.ptr(m), _lib.ptr(v), _lib.ptr(x0), _lib.ptr(grad),
+                                             _lib.ptr(x_adv), _lib.ptr(best_adv), _lib.ptr(bl2), _lib.ptr(bs),
+                                             _lib.ptr(success), _lib.ptr(pa), _lib.ptr(pb), _lib.ptr(l2_now), k, per,
+                                             step_size, bc2_sqrt, beta1, beta2, adam_eps, _lib.stream_ptr())
+                _lib.check(rc, "advb200_cw_step_f32")
+                pa, pb = pb, pa
+            rc = lib.advb200_cw_finalize_f32(_lib.ptr(x_adv), _lib.ptr(best_adv), _lib.ptr(bs), _lib.ptr(final[lo:hi]), k,
+                                             per, _lib.stream_ptr())
+            _lib.check(rc, "advb200_cw_finalize_f32")
     res = CWResult(x_adv=final, success=best_success.to(torch.bool))
     if return_l2:
         return res, best_l2

@@ -154,19 +154,20 @@ def calibrate_feature_threshold(model, images, *, mean, std, n: int = 100, quant
 
 
 def run_attack(attack_name, model, x, y_true, mean, std, eps, alpha, steps, cw_c, cw_kappa, cw_steps, cw_lr,
-               inv_n_global: Optional[float] = None):
+               inv_n_global: Optional[float] = None, pgd_noise: Optional[torch.Tensor] = None):
     if attack_name == "fgsm":
         return fgsm_attack(model, x, y_true, eps=eps, mean=mean, std=std, inv_n_global=inv_n_global)
     if attack_name == "pgd":
         return pgd_linf_attack(model, x, y_true, eps=eps, alpha=alpha, steps=steps, mean=mean, std=std,
-                               inv_n_global=inv_n_global)
+                               inv_n_global=inv_n_global, noise=pgd_noise)
     return cw_l2_attack(model, x, y_true, mean=mean, std=std, c=cw_c, kappa=cw_kappa, steps=cw_steps, lr=cw_lr,
                         targeted=False, y_target=None).x_adv
 
 
 def evaluate_defenses_batched(model, x, y_true, mean, std, attack_name, eps, alpha, steps, cw_c, cw_kappa,
                               cw_steps, cw_lr, detector_threshold, *, inv_n_global: Optional[float] = None,
-                              return_flags: bool = False, x_adv: Optional[torch.Tensor] = None):
+                              return_flags: bool = False, x_adv: Optional[torch.Tensor] = None,
+                              pgd_noise: Optional[torch.Tensor] = None, return_details: bool = False):
     """Vectorised evaluate_defenses: per-image outcomes equal the reference's batch-1 loop
     (every image is independent; CE's batch mean only rescales the gradient).  Returns the int64[7]
     counter vector {COUNTER_KEYS} on x's device (and the [N,6] per-image flags if asked).
@@ -179,12 +180,12 @@ def evaluate_defenses_batched(model, x, y_true, mean, std, attack_name, eps, alp
     clean = nm.forward(x, mean, std, want_logits=False, want_preds=True, want_score=True)
     if x_adv is None:
         x_adv = run_attack(attack_name, nm, x, y_true, mean, std, eps, alpha, steps, cw_c, cw_kappa, cw_steps,
-                           cw_lr, inv_n_global=scale)
+                           cw_lr, inv_n_global=scale, pgd_noise=pgd_noise)
     adv = nm.forward(x_adv, mean, std, want_logits=False, want_preds=True, want_score=True)
     x_def = defend_input(x_adv)
     dfd = nm.forward(x_def, mean, std, want_logits=False, want_preds=True)
     counters = torch.zeros((7,), dtype=torch.int64, device=dev)
-    flags = torch.empty((n, 6), dtype=torch.uint8, device=dev) if return_flags else None
+    flags = torch.empty((n, 6), dtype=torch.uint8, device=dev) if (return_flags or return_details) else None
     y = y_true.detach().to(device=dev, dtype=torch.int64).contiguous()
     with torch.cuda.device(dev):
         rc = lib.advb200_eval_counters(_lib.ptr(clean["preds"]), _lib.ptr(adv["preds"]), _lib.ptr(dfd["preds"]),
@@ -192,6 +193,9 @@ def evaluate_defenses_batched(model, x, y_true, mean, std, attack_name, eps, alp
                                        float(detector_threshold), _lib.ptr(y), n, _lib.ptr(counters),
                                        _lib.ptr(flags), _lib.stream_ptr())
     _lib.check(rc, "advb200_eval_counters")
+    if return_details:       # per-image evidence for the parity reports: flags, detector scores, the three predictions
+        return counters, flags, {"score_clean": clean["score"], "score_adv": adv["score"], "pred_clean": clean["preds"],
+                                 "pred_adv": adv["preds"], "pred_def": dfd["preds"]}
     if return_flags:
         return counters, flags
     return counters

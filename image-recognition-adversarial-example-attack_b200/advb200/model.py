@@ -132,6 +132,8 @@ class NativeResNet50:
             raise ValueError("advb200 handles [N,3,224,224] inputs (the reference's CenterCrop(224) pipeline)")
         if not x.is_cuda:
             raise ValueError("x must live on the CUDA device of the native model (no CPU fallback)")
+        if x.device != self.device:
+            raise ValueError(f"x is on {x.device} but the native model lives on {self.device}")
         return x.detach().to(dtype=torch.float32).contiguous()
 
     # -- forward -----------------------------------------------------------------------------

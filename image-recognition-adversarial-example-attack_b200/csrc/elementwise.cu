@@ -314,13 +314,12 @@ cw_step_kernel(float* __restrict__ w, float* __restrict__ m, float* __restrict__
                float* __restrict__ x_adv, float* __restrict__ best_adv,
                const uint8_t* __restrict__ improved, float* __restrict__ l2_partials_out, int parts,
                int64_t elems_per_img, float step_size, float bc2_sqrt, float beta1, float beta2,
-               float adam_eps) {
+               float one_m_b1, float one_m_b2, float adam_eps, bool aligned) {
   __shared__ float red[kCwThreads / 32];
   const int img = blockIdx.x / parts, part = blockIdx.x % parts;
   const int64_t base = (int64_t)img * elems_per_img + (int64_t)part * kCwChunk;
   const int64_t remain = elems_per_img - (int64_t)part * kCwChunk;
   const bool imp = improved[img] != 0;
-  const float one_m_b1 = 1.0f - beta1, one_m_b2 = 1.0f - beta2;
   float acc = 0.f;
 
   auto update = [&](float ww, float mm, float vv, float xo, float g, float& w_o, float& m_o,
@@ -340,7 +339,7 @@ cw_step_kernel(float* __restrict__ w, float* __restrict__ m, float* __restrict__
     acc += d * d;
   };
 
-  const bool vec = (remain >= kCwChunk) && ((elems_per_img & 3) == 0);
+  const bool vec = (remain >= kCwChunk) && ((elems_per_img & 3) == 0) && aligned;
   if (vec) {
     float4* w4 = reinterpret_cast<float4*>(w + base);
     float4* m4 = reinterpret_cast<float4*>(m + base);
@@ -498,7 +497,7 @@ median3x3_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t p
                            fminf(fminf(hi[q][j + 1], hi[q][j + 2]), hi[q][j + 3]));
         }
         float* orow = dst + (int64_t)r * w;
-        if (vec) {
+        if (vec && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0)) {      // (the output plane may be less aligned than the input)
           *reinterpret_cast<float4*>(orow + c0) = make_float4(o4[0], o4[1], o4[2], o4[3]);
         } else {
 #pragma unroll
@@ -642,8 +641,8 @@ int advb200_cw_init_f32(const float* x, float* x0, float* w, float* m, float* v,
 int advb200_cw_step_f32(float* w, float* m, float* v, const float* x0, const float* grad_x, float* x_adv,
                         float* best_adv, float* best_l2, uint8_t* best_success, const uint8_t* success,
                         const float* l2_partials_in, float* l2_partials_out, float* l2_out, int n_img,
-                        int64_t elems_per_img, float step_size, float bc2_sqrt, float beta1, float beta2,
-                        float adam_eps, void* stream) {
+                        int64_t elems_per_img, float step_size, float bc2_sqrt, double beta1, double beta2,
+                        double adam_eps, void* stream) {
   ADV_CHECK_ARG(w && m && v && x0 && grad_x && x_adv && best_adv && best_l2 && best_success && success &&
                     l2_partials_in && l2_partials_out,
                 "cw_step: null pointer");
@@ -659,7 +658,9 @@ int advb200_cw_step_f32(float* w, float* m, float* v, const float* x0, const flo
   ADV_LAUNCHED();
   cw_step_kernel<<<n_img * parts, kCwThreads, 0, as_stream(stream)>>>(
       w, m, v, x0, grad_x, x_adv, best_adv, improved, l2_partials_out, parts, elems_per_img, step_size,
-      bc2_sqrt, beta1, beta2, adam_eps);
+      bc2_sqrt, (float)beta1, (float)beta2, (float)(1.0 - beta1), (float)(1.0 - beta2), (float)adam_eps,   // torch: 1-beta in double
+      aligned16(w) && aligned16(m) && aligned16(v) && aligned16(x0) && aligned16(grad_x) && aligned16(x_adv) &&
+          aligned16(best_adv));
   ADV_LAUNCHED();
   return ADVB200_OK;
 }

@@ -67,7 +67,13 @@ struct Op {
   // profiling metadata (advb200_profile_dump): layer label, algorithmic flops and HBM bytes
   char name[48] = {0};
   double flops = 0, bytes = 0;
+  // debug trace (advb200_debug_trace): the tensor this launch writes
+  const void* tr_ptr = nullptr;
+  int tr_n = 0, tr_h = 0, tr_w = 0, tr_c = 0, tr_esz = 0;
 };
+inline void trace_target(Op& op, const Act& out, int esz) {
+  op.tr_ptr = out.p; op.tr_n = out.n; op.tr_h = out.h; op.tr_w = out.w; op.tr_c = out.c; op.tr_esz = esz;
+}
 
 // label given to the ops built next (set by plan(); read by build_tc_ops)
 const char* g_label = "";
@@ -184,6 +190,7 @@ int build_pw_ops(std::vector<Op>& ops, const PwSrc* src, int nsrc, Act out, int 
   const double pix = (double)out.n * lw * lh;
   label_op(op, "", 2.0 * pix * gemm_n * kin,
            in_bytes + 2.0 * pix * gemm_n * (1.0 + (mask ? 1.0 / 16 : 0) + (mask_out ? 1.0 / 16 : 0)) + 2.0 * gemm_n * kin);
+  trace_target(op, out, 2);
   ops.push_back(op);
   return ADVB200_OK;
 }
@@ -245,6 +252,7 @@ int build_pw_s2_ops(std::vector<Op>& ops, Act g_a, const bf16* w1, Act g_sum, co
   label_op(op, "", 2.0 * pix * gemm_n * (4.0 * g_a.c + g_sum.c),
            2.0 * (4.0 * pix * g_a.c + pix * g_sum.c + 4.0 * pix * gemm_n * (1.0 + (mask ? 1.0 / 16 : 0)) +
                   (double)gemm_n * (g_a.c + g_sum.c)));
+  trace_target(op, g_x, 2);
   ops.push_back(op);
   return ADVB200_OK;
 }
@@ -306,6 +314,7 @@ int build_fused_block(std::vector<Op>& ops, bool dgrad, Act in, const bf16* w1, 
   const double pix = (double)in.n * in.h * in.w;
   label_op(op, "", 2.0 * pix * (64.0 * 64 * 9 + 64.0 * 256),
            2.0 * pix * (64 + 256 + 256) + 2.0 * pix * (64 + 256) / 16 + 2.0 * (9 * 64 * 64 + 64 * 256));
+  trace_target(op, out, 2);
   ops.push_back(op);
   return ADVB200_OK;
 }
@@ -338,6 +347,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
 
   Op op;
   op.kind = Op::TC;
+  trace_target(op, out, 2);
   TcOp& t = op.tc;
   ConvGemmParams& p = t.p;
   memset(&p, 0, sizeof p);
@@ -580,6 +590,8 @@ int build_simt_op(std::vector<Op>& ops, const float* wm, int ksize, int stride, 
   s.n = in.n; s.hi = in.h; s.wi = in.w; s.ci = in.c; s.ho = out.h; s.wo = out.w; s.co = out.c;
   s.kh = s.kw = ksize; s.stride = stride; s.pad = pad >= 0 ? pad : (ksize - 1) / 2;
   s.relu = relu; s.dgrad = dgrad ? 1 : 0;
+  snprintf(op.name, sizeof op.name, "%s", g_label);
+  trace_target(op, out, 4);
   ops.push_back(op);
   return ADVB200_OK;
 }
@@ -589,6 +601,27 @@ int build_simt_op(std::vector<Op>& ops, const float* wm, int ksize, int stride, 
 bool g_prof_on = false;
 struct ProfRec { cudaEvent_t e0, e1; const Op* op; };
 std::vector<ProfRec> g_prof_events;
+
+// ---- debug trace (test hook, advb200_debug_trace): while a trace buffer is set, every tensor the forward / backward
+// passes write is copied into it (stream-ordered D2D) right after the launch that produced it, so a test can check every
+// launch of the real plan against the oracle applied to that launch's own inputs
+struct TraceRec { char name[48]; long long off; int n, h, w, c, esz; };
+uint8_t* g_trace_buf = nullptr;
+long long g_trace_cap = 0, g_trace_off = 0;
+bool g_trace_overflow = false;
+std::vector<TraceRec> g_trace;
+int trace_tensor(const char* name, const void* p, int n, int h, int w, int c, int esz, cudaStream_t st) {
+  if (!g_trace_buf || !p) return ADVB200_OK;
+  const long long bytes = (long long)n * h * w * c * esz;
+  const long long off = (g_trace_off + 255) & ~255ll;
+  if (off + bytes > g_trace_cap) { g_trace_overflow = true; return ADVB200_OK; }
+  ADV_CHECK_CUDA(cudaMemcpyAsync(g_trace_buf + off, p, (size_t)bytes, cudaMemcpyDeviceToDevice, st));
+  TraceRec r; snprintf(r.name, sizeof r.name, "%s", name);
+  r.off = off; r.n = n; r.h = h; r.w = w; r.c = c; r.esz = esz;
+  g_trace.push_back(r);
+  g_trace_off = off + bytes;
+  return ADVB200_OK;
+}
 
 // consecutive conv launches alternate their tile traversal direction, so a launch starts on the part of
 // its input that the previous launch wrote last (still in the 126 MB L2)
@@ -628,6 +661,8 @@ int run_ops(std::vector<Op>& ops, cudaStream_t st) {
       }
     }
     if (rc) return rc;
+    if (g_trace_buf && op.tr_ptr && (rc = trace_tensor(op.name, op.tr_ptr, op.tr_n, op.tr_h, op.tr_w, op.tr_c, op.tr_esz, st)))
+      return rc;
   }
   return ADVB200_OK;
 }
@@ -906,8 +941,10 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out, cudaStream_t tune_s
       }
       setl("fwd", nullptr, "conv1");
       label_op(op, "", 2.0 * n * 112 * 112 * 64 * 147, 2.0 * n * ((double)m->t_in.h * m->t_in.w * m->t_in.c + 112.0 * 112 * 64));
+      trace_target(op, m->c1, 2);
       m->ops_conv1.push_back(op);
     } else {
+      setl("fwd", nullptr, "conv1");
       rc = build_simt_op(m->ops_conv1, w0.f_fwd, 7, 2, false, m->t_in, m->c1, w0.shift, nullptr, nullptr, 1, 3);
     }
   }
@@ -967,14 +1004,18 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out, cudaStream_t tune_s
           if (!rc) rc = emit(ops, [&](std::vector<Op>& v_) { return build_tc_ops(v_, c3.b_fwd, 1, 1, false, t.b, t.out, c3.shift, res, nullptr, 1, t.mout); });
         }
       } else {
+        setl("fwd", &s, "c1");
         rc = build_simt_op(ops, c1.f_fwd, 1, 1, false, t.x, t.a, c1.shift, nullptr, nullptr, 1);
+        setl("fwd", &s, "c2");
         if (!rc) rc = build_simt_op(ops, c2.f_fwd, 3, s.stride, false, t.a, t.b, c2.shift, nullptr, nullptr, 1);
         const float* res = reinterpret_cast<const float*>(t.x.p);
         if (!rc && s.down) {
           const ConvW& cd = m->conv[s.conv_base + 3];
+          setl("fwd", &s, "ds");
           rc = build_simt_op(ops, cd.f_fwd, 1, s.stride, false, t.x, t.idn, cd.shift, nullptr, nullptr, 0);
           res = reinterpret_cast<const float*>(t.idn.p);
         }
+        setl("fwd", &s, "c3");
         if (!rc) rc = build_simt_op(ops, c3.f_fwd, 1, 1, false, t.b, t.out, c3.shift, res, nullptr, 1);
       }
     }
@@ -1010,7 +1051,9 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out, cudaStream_t tune_s
         }
       } else {
         typedef const float* F;
+        setl("bwd", &s, "c3");
         rc = build_simt_op(m->ops_bwd, c3.f_dgrad, 1, 1, true, g_sum, g_b, nullptr, nullptr, (F)t.b.p, 0);
+        setl("bwd", &s, "c2");
         if (!rc) rc = build_simt_op(m->ops_bwd, c2.f_dgrad, 3, s.stride, true, g_b, g_a, nullptr, nullptr, (F)t.a.p, 0);
       }
     }
@@ -1056,6 +1099,7 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out, cudaStream_t tune_s
           setl("bwd", &s, "ds");
           rc = emit(m->ops_bwd, [&](std::vector<Op>& v_) { return build_tc_ops(v_, cd.b_dgrad, 1, s.stride, true, g_sum, g_t, nullptr, nullptr, nullptr, 0); });
         } else {
+          setl("bwd", &s, "ds");
           rc = build_simt_op(m->ops_bwd, cd.f_dgrad, 1, s.stride, true, g_sum, g_t, nullptr, nullptr, nullptr, 0);
         }
       }
@@ -1130,6 +1174,7 @@ int64_t plan(advb200_model* m, int n, void* ws, int* rc_out, cudaStream_t tune_s
     } else {
       Act gy = m->c1; gy.p = m->g_c1;
       Act gx = m->t_in; gx.p = m->g_img_nhwc;
+      setl("bwd", nullptr, "conv1");
       rc = build_simt_op(m->ops_conv1_bwd, m->conv[0].f_dgrad, 7, 2, true, gy, gx, nullptr, nullptr, nullptr, 0, 3);
     }
   }
@@ -1165,6 +1210,7 @@ int forward_impl(advb200_model* m, const float* x, const float* mean3, const flo
   if (tc) rc = launch_maxpool_fwd<bf16>((const bf16*)m->c1.p, (bf16*)m->p1.p, m->pool_idx, n, 112, 112, 64, st);
   else rc = launch_maxpool_fwd<float>((const float*)m->c1.p, (float*)m->p1.p, m->pool_idx, n, 112, 112, 64, st);
   if (rc) return rc;
+  if ((rc = trace_tensor("p1", m->p1.p, n, 56, 56, 64, (int)m->esz, st))) return rc;
   if ((rc = run_ops(m->ops_l123, st))) return rc;
   if (score_out) {
     if (tc) rc = launch_detector_score<bf16>((const bf16*)m->l3out.p, score_out, n, 196, 1024, st);
@@ -1179,6 +1225,8 @@ int forward_impl(advb200_model* m, const float* x, const float* mean3, const flo
   if (rc) return rc;
   // fc forward: logits = feat * W^T + b   (fp32 in both modes)
   rc = launch_fc_nt(m->feat, m->fc_w, m->fc_b, m->logits, m->fc_part, n, kClasses, kFeat, st);
+  if (!rc) rc = trace_tensor("feat", m->feat, n, 1, 1, kFeat, 4, st);
+  if (!rc) rc = trace_tensor("logits", m->logits, n, 1, 1, kClasses, 4, st);
   if (!rc) m->fwd_state_n = n;
   return rc;
 }
@@ -1420,14 +1468,18 @@ static int backward_impl(advb200_model* m, const float* dlogits, const float* st
   int rc;
   m->fwd_state_n = -1;   // gradient buffers may reuse activation space: one backward per forward
   // fc input gradient: dfeat = dlogits * W
+  if ((rc = trace_tensor("dlogits", dlogits, n, 1, 1, kClasses, 4, st))) return rc;
   if ((rc = launch_fc_nt(dlogits, m->fc_wt, nullptr, m->dfeat, m->fc_part, n, kFeat, kClasses, st))) return rc;
+  if ((rc = trace_tensor("dfeat", m->dfeat, n, 1, 1, kFeat, 4, st))) return rc;
   if (tc) rc = launch_avgpool_bwd<bf16>(m->dfeat, (const bf16*)m->l4out.p, (bf16*)m->g_top, n, 49, kFeat, st);
   else rc = launch_avgpool_bwd<float>(m->dfeat, (const float*)m->l4out.p, (float*)m->g_top, n, 49, kFeat, st);
   if (rc) return rc;
+  if ((rc = trace_tensor("g_top", m->g_top, n, 7, 7, kFeat, (int)m->esz, st))) return rc;
   if ((rc = run_ops(m->ops_bwd, st))) return rc;
   if (tc) rc = launch_maxpool_bwd<bf16>((const bf16*)m->g_final, m->pool_idx, (bf16*)m->g_c1, n, 112, 112, 64, st);
   else rc = launch_maxpool_bwd<float>((const float*)m->g_final, m->pool_idx, (float*)m->g_c1, n, 112, 112, 64, st);
   if (rc) return rc;
+  if ((rc = trace_tensor("g_c1", m->g_c1, n, 112, 112, 64, (int)m->esz, st))) return rc;
   if (tc) {
     // patch the per-call output / std pointers into the conv1-dgrad epilogue (host-side only)
     Op& op = m->ops_conv1_bwd[0];
@@ -1598,6 +1650,33 @@ int advb200_vgg19_forward(advb200_vgg19* m, const float* x, const float* mean3, 
   if ((rc = launch_bf16_cols_to_f32(m->logits_bf16, kVggClassesPad, logits_out, n, kClasses, st))) return rc;
   if (preds_out) rc = launch_argmax(logits_out, n, kClasses, preds_out, st);
   return rc;
+}
+
+int advb200_debug_trace(void* buf, int64_t cap_bytes) {
+  g_trace_buf = reinterpret_cast<uint8_t*>(buf);
+  g_trace_cap = buf ? cap_bytes : 0;
+  if (buf) {            // a new trace starts; switching off (NULL) keeps the index readable
+    g_trace_off = 0; g_trace_overflow = false;
+    g_trace.clear();
+  }
+  return ADVB200_OK;
+}
+
+int64_t advb200_debug_trace_index(char* buf_host, int64_t cap) {
+  // one line per traced tensor: name|byte offset|n|h|w|c|element size ; a final line "overflow" if the buffer was too small
+  std::string out;
+  for (const TraceRec& r : g_trace) {
+    char line[160];
+    snprintf(line, sizeof line, "%s|%lld|%d|%d|%d|%d|%d\n", r.name, r.off, r.n, r.h, r.w, r.c, r.esz);
+    out += line;
+  }
+  if (g_trace_overflow) out += "overflow\n";
+  if (buf_host && cap > 0) {
+    const size_t ncopy = out.size() < (size_t)cap - 1 ? out.size() : (size_t)cap - 1;
+    memcpy(buf_host, out.data(), ncopy);
+    buf_host[ncopy] = 0;
+  }
+  return (int64_t)out.size() + 1;
 }
 
 int advb200_test_force_tile(int bn, int pair, int bres, int slots) {

@@ -436,6 +436,19 @@ loss_grad_kernel(const float* __restrict__ logits, const int64_t* __restrict__ y
   __syncthreads();
   if (tid == 0 && preds) preds[n] = amax;
 
+  if (yy < 0 || yy >= classes) {
+    // a label outside [0, classes) raises in the reference (F.cross_entropy / one_hot); the Python mirror checks labels
+    // once per attack call — a raw C-ABI caller gets a NaN row instead of an out-of-bounds read
+    const float qnan = __int_as_float(0x7fc00000);
+    if (dlogits)
+      for (int j = tid; j < classes; j += kT) dlogits[(long long)n * classes + j] = qnan;
+    if (tid == 0) {
+      if (loss) loss[n] = qnan;
+      if (success) success[n] = 0;
+    }
+    return;
+  }
+
   if (loss_kind == ADVB200_LOSS_CE_MEAN) {
     // softmax cross-entropy: d z_j = (p_j - [j==y]) * scale, with the true-class entry formed as
     // -(sum_{j!=y} p_j) to avoid the cancellation in p_y - 1

@@ -134,12 +134,14 @@ int advb200_attack_step(advb200_model* m, float* x_adv_inout, const float* x_ori
  *   improved_n = success_n && l2_n < best_l2_n  -> best_l2, best_success, best_adv updated
  *   g_w = (2*(x_adv-x0) + grad_x) * 0.5 * (1 - tanh(w)^2);  Adam(m, v, w)
  *   x_adv <- 0.5*(tanh(w)+1) for the NEXT iteration, l2_partials_out <- its distance partials.
- * step_size = lr/(1-beta1^t) and bc2_sqrt = sqrt(1-beta2^t) are computed in double by the host. */
+ * step_size = lr/(1-beta1^t) and bc2_sqrt = sqrt(1-beta2^t) are computed in double by the host; beta1, beta2 and
+ * adam_eps are doubles because torch forms 1-beta1 and 1-beta2 in double and only then rounds them to fp32
+ * (1.0f - 0.999f is 1.3e-5 away from fp32(1 - 0.999): enough to miss the reference's Adam state). */
 int advb200_cw_step_f32(float* w, float* m, float* v, const float* x0, const float* grad_x,
                         float* x_adv, float* best_adv, float* best_l2, uint8_t* best_success,
                         const uint8_t* success, const float* l2_partials_in, float* l2_partials_out,
                         float* l2_out, int n_img, int64_t elems_per_img, float step_size,
-                        float bc2_sqrt, float beta1, float beta2, float adam_eps, void* stream);
+                        float bc2_sqrt, double beta1, double beta2, double adam_eps, void* stream);
 
 /* attack.py:139: out = best_success ? best_adv : x_adv (x_adv already holds 0.5*(tanh(w)+1)
  * of the post-update w). */
@@ -228,6 +230,16 @@ int advb200_test_conv(int precision, const void* x, const float* wgt, const floa
  * heuristic) of the following advb200_test_conv calls — the candidates the plan-time autotuner chooses between;
  * the parity tests check that every candidate gives bit-identical results. */
 int advb200_test_force_tile(int bn, int pair, int bres, int slots);
+
+/* Test hook: in-situ trace of a forward / input-gradient pass.  While a device buffer is set, every tensor the passes
+ * write — each conv launch's output as the plan really runs it (fused launches, multi-class stride-2 input gradients),
+ * the pooled tensors, fc / loss tensors — is copied into the buffer right after the launch that produced it (names as in
+ * advb200_profile_dump: "fwd l2.0.c3+ds", "bwd l1.1.c2+c1", "p1", "g_top", ...).  tests/test_gpu_trace.py checks every
+ * launch against the oracle applied to that launch's OWN traced inputs (model(...) attack.py:30; autograd.grad
+ * attack.py:32).  advb200_debug_trace(NULL, 0) switches tracing off; advb200_debug_trace_index writes one line per
+ * tensor, "name|byte offset|n|h|w|c|element size" (activations NHWC), and returns the bytes needed. */
+int advb200_debug_trace(void* buf, int64_t cap_bytes);
+int64_t advb200_debug_trace_index(char* buf_host, int64_t cap);
 
 /* number of kernels launched by this library since load (bench.py's gpu_launches) */
 int64_t advb200_launch_count(void);

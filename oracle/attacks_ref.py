@@ -57,6 +57,16 @@ def pgd_linf(model, x, y, *, eps, alpha, steps, mean, std, noise: Optional[torch
     return x_adv
 
 
+def adam_update(w, m, v, g, t, lr, b1=0.9, b2=0.999, adam_eps=1e-8):
+    """torch.optim.Adam single-tensor update at step t >= 1 (betas .9/.999, eps 1e-8, no weight decay / amsgrad;
+    torch/optim/adam.py): the bias corrections are Python doubles applied as fp32 scalars."""
+    m = m + (g - m) * (1.0 - b1)
+    v = v * b2 + (1.0 - b2) * g * g
+    step_size = lr / (1.0 - b1 ** t)
+    denom = v.sqrt() / math.sqrt(1.0 - b2 ** t) + adam_eps
+    return w - step_size * (m / denom), m, v
+
+
 def cw_l2(model, x, y_true, *, mean, std, c=1.0, kappa=0.0, steps=1000, lr=1e-2, targeted=False, y_target=None):
     """attack.py:78-140 with torch.optim.Adam written out.  Returns (x_adv, success, best_l2)."""
     if targeted and y_target is None:
@@ -89,12 +99,7 @@ def cw_l2(model, x, y_true, *, mean, std, c=1.0, kappa=0.0, steps=1000, lr=1e-2,
         l2 = (x_adv - x0).view(n, -1).pow(2).sum(dim=1)                   # :126
         loss = (l2 + c * f).sum()                                         # :127
         (g,) = torch.autograd.grad(loss, wv)
-        # torch.optim.Adam single-tensor update (betas .9/.999, eps 1e-8, no weight decay / amsgrad)
-        m = m + (g - m) * (1.0 - b1)
-        v = v * b2 + (1.0 - b2) * g * g
-        step_size = lr / (1.0 - b1 ** t)
-        denom = v.sqrt() / math.sqrt(1.0 - b2 ** t) + adam_eps
-        w = w - step_size * (m / denom)
+        w, m, v = adam_update(w, m, v, g, t, lr, b1, b2, adam_eps)
         improved = success & (l2.detach() < best_l2)                      # :133-137
         best_l2 = torch.where(improved, l2.detach(), best_l2)
         best_success = best_success | improved

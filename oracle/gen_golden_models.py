@@ -1,0 +1,231 @@
+"""Generates the model-level golden fixtures by importing and running the REFERENCE ITSELF from /root/reference
+(read-only), for either fixture model of oracle/weights.py:
+
+    python oracle/gen_golden_models.py --model cond  --what quick      # ~3 min : tests/golden/{cond_resnet.npz, cond_attacks.npz, meta_cond.json}
+    python oracle/gen_golden_models.py --model seed0 --what config3    # ~5 min : CW-L2 100 steps, 16 images (BASELINE config 3 subset)
+    python oracle/gen_golden_models.py --model seed0 --what config5    # ~25 min: the reference's batch-1 evaluate_defenses loop
+                                                                       #           on the first 256 images (BASELINE config 5 subset)
+
+Runs only in the build container (the GPU box has no /root/reference); the outputs are committed so the tests can check
+both the oracle restatement and the CUDA path against them.  The seed-0 "quick" fixtures are made by oracle/gen_golden.py.
+"""
+from __future__ import annotations
+
+import argparse
+import copy
+import json
+import sys
+import time
+from pathlib import Path
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+ROOT = Path(__file__).resolve().parent.parent
+OUT = ROOT / "tests" / "golden"
+sys.path.insert(0, str(ROOT))
+sys.dont_write_bytecode = True
+
+from oracle import weights  # noqa: E402
+from oracle.gen_golden import import_reference  # noqa: E402
+
+EPS_LISTS = {          # BASELINE config 5's {4,8}/255 plus small points where the rates are strictly inside (0,1)
+    "seed0": [1 / 255, 4 / 255, 8 / 255],
+    "cond": [0.03 / 255, 0.06 / 255, 4 / 255, 8 / 255],
+}
+ALPHA, STEPS = 2 / 255, 10
+NOISE_SEED0 = 5000      # image i's PGD start noise is what attack.py:51 draws right after torch.manual_seed(NOISE_SEED0 + i)
+
+
+def images_for(tag: str, n: int) -> torch.Tensor:
+    """The image set of a fixture model: the survey's U[0,1) noise images for the mandated seed-0 model (what
+    `cli/defense_experiments.py --synthetic N` draws), structured + noise images for the conditioned one."""
+    return weights.synthetic_images(n) if tag == "seed0" else weights.mixed_images(n, seed=77)
+
+
+def threshold_for(tag: str, scores: torch.Tensor) -> float:
+    q = float(torch.quantile(scores, 0.95).item())
+    if tag == "seed0":
+        return q * 0.5 if q > 50 else max(q, 1.0)          # defense_experiments.py:338-345
+    # conditioned model: activations are O(1), scores ~0.3, and the reference's floor of 1.0 would switch the detector
+    # off altogether; the fixtures pass the raw 0.95-quantile as --detector_threshold so its flags stay informative
+    return q
+
+
+def quick(tag: str, ref_attack, ref_def):
+    model = weights.MODELS[tag](0)
+    if tag == "cond":
+        weights.save_conditioned_stats(model, 0)
+        model = weights.conditioned_resnet50(0)            # reload through the committed statistics
+    mean, std = weights.mean_std()
+    meta = {"torch": torch.__version__, "threads": torch.get_num_threads(), "model": tag}
+    xs = images_for(tag, 8)
+    x4 = xs[:4]
+    xi = x4.clone().requires_grad_(True)
+    logits = model(ref_attack.normalize_batch(xi, mean, std))
+    y4 = logits.argmax(1)
+    (grad,) = torch.autograd.grad(F.cross_entropy(logits, y4), xi)
+    m64 = copy.deepcopy(model).double()
+    xi64 = x4.double().clone().requires_grad_(True)
+    l64 = m64(ref_attack.normalize_batch(xi64, mean.double(), std.double()))
+    (g64,) = torch.autograd.grad(F.cross_entropy(l64, y4), xi64)
+    # the reference's own all-bf16 run (model.bfloat16()), the figure to read the bf16 kernels' numbers against
+    mb = copy.deepcopy(model).bfloat16()
+    xib = x4.bfloat16().clone().requires_grad_(True)
+    lb = mb(ref_attack.normalize_batch(xib, mean.bfloat16(), std.bfloat16()))
+    (gb,) = torch.autograd.grad(F.cross_entropy(lb.float(), y4), xib)
+    rel = lambda a, b: float((a.double() - b.double()).norm() / b.double().norm())
+    mask = g64.abs() > 1e-6 * g64.abs().max()
+    meta["ref_fp32_vs_fp64"] = {"logits_rel": rel(logits, l64), "grad_rel": rel(grad, g64),
+                                "sign_mismatches": int((grad.sign() != g64.sign())[mask].sum()), "masked": int(mask.sum())}
+    meta["ref_bf16_vs_fp32"] = {"logits_rel": rel(lb.float(), logits), "grad_rel": rel(gb.float(), grad),
+                                "sign_agreement": float((gb.float().sign() == grad.sign())[mask].float().mean())}
+    np.savez_compressed(OUT / f"{tag}_resnet.npz", logits=logits.detach().numpy(), logits64=l64.detach().numpy(),
+                        y=y4.numpy(), grad=grad.numpy(), grad64=g64.float().numpy())
+
+    # attacks, N = 2
+    x2, y2 = x4[:2], y4[:2]
+    eps, alpha = 8 / 255, 2 / 255
+    att = {}
+    for e_name, e in (("8", 8 / 255), ("small", EPS_LISTS[tag][0])):
+        fg = ref_attack.fgsm_attack(model, x2, y2, eps=e, mean=mean, std=std)
+        torch.manual_seed(7)
+        pg = ref_attack.pgd_linf_attack(model, x2, y2, eps=e, alpha=alpha, steps=10, mean=mean, std=std)
+        with torch.no_grad():
+            att[f"fgsm_logits_{e_name}"] = model(ref_attack.normalize_batch(fg, mean, std)).numpy()
+            att[f"pgd_logits_{e_name}"] = model(ref_attack.normalize_batch(pg, mean, std)).numpy()
+        att[f"fgsm_x_{e_name}"] = fg.numpy()
+        att[f"eps_{e_name}"] = np.float64(e)
+    cwu = ref_attack.cw_l2_attack(model, x2, y2, mean=mean, std=std, c=1.0, kappa=0.0, steps=20, lr=0.01)
+    cwt = ref_attack.cw_l2_attack(model, x2, y2, mean=mean, std=std, c=1.0, kappa=0.0, steps=20, lr=0.01,
+                                  targeted=True, y_target=torch.full((2,), 805))
+    with torch.no_grad():
+        lcu = model(ref_attack.normalize_batch(cwu.x_adv, mean, std))
+        lct = model(ref_attack.normalize_batch(cwt.x_adv, mean, std))
+    l2 = lambda a: (a - x2.clamp(0, 1)).flatten(1).pow(2).sum(1).numpy()
+    np.savez_compressed(OUT / f"{tag}_attacks.npz", cwu_success=cwu.success.numpy(), cwu_l2=l2(cwu.x_adv),
+                        cwu_logits=lcu.numpy(), cwt_success=cwt.success.numpy(), cwt_l2=l2(cwt.x_adv),
+                        cwt_logits=lct.numpy(), **att)
+
+    # detector scores / threshold / evaluate_defenses dicts (batch 1)
+    scores = torch.cat([ref_def._layer3_features(model, xs[i:i + 1], mean, std) for i in range(8)])
+    thr = threshold_for(tag, scores)
+    evals = {}
+    for attack_name in ("fgsm", "pgd"):
+        for e in EPS_LISTS[tag]:
+            rows = []
+            for i in range(2):
+                xi1 = xs[i:i + 1]
+                yi = model(ref_attack.normalize_batch(xi1, mean, std)).argmax(1)
+                torch.manual_seed(100 + i)
+                r = ref_def.evaluate_defenses(model, xi1, yi, mean, std, attack_name, float(e), alpha, 10, 1.0, 0.0, 20,
+                                              0.01, thr)
+                rows.append({k: int(v) for k, v in r.items()})
+            evals[f"{attack_name}_{e * 255:g}"] = rows
+    meta["detector"] = {"scores": scores.tolist(), "threshold": thr, "evaluate_defenses": evals}
+    (OUT / f"meta_{tag}.json").write_text(json.dumps(meta, indent=1))
+    print(json.dumps(meta, indent=1)[:2500])
+
+
+def config3(tag: str, ref_attack, ref_def, n: int = 16):
+    """BASELINE config 3 on a subset: CW-L2, 100 steps, c = 1, kappa = 0, lr = 0.01, untargeted and targeted-805."""
+    model = weights.MODELS[tag](0)
+    mean, std = weights.mean_std()
+    x = images_for(tag, n)
+    with torch.no_grad():
+        y = model(ref_attack.normalize_batch(x, mean, std)).argmax(1)
+    out = {"y": y.numpy(), "n": n}
+    for name, kw in (("cwu", {}), ("cwt", {"targeted": True, "y_target": torch.full((n,), 805)})):
+        t0 = time.time()
+        succ, l2s, logit_rows, linf = [], [], [], []
+        for lo in range(0, n, 4):          # batches of 4: CW's objective is a sum, so batching does not change any image
+            xb, yb = x[lo:lo + 4], y[lo:lo + 4]
+            kwb = dict(kw)
+            if "y_target" in kwb:
+                kwb["y_target"] = kwb["y_target"][lo:lo + 4]
+            res = ref_attack.cw_l2_attack(model, xb, yb, mean=mean, std=std, c=1.0, kappa=0.0, steps=100, lr=0.01, **kwb)
+            with torch.no_grad():
+                logit_rows.append(model(ref_attack.normalize_batch(res.x_adv, mean, std)))
+            succ.append(res.success)
+            l2s.append((res.x_adv - xb.clamp(0, 1)).flatten(1).pow(2).sum(1))
+            linf.append((res.x_adv - xb.clamp(0, 1)).flatten(1).abs().amax(1))
+        out[name + "_success"] = torch.cat(succ).numpy()
+        out[name + "_l2"] = torch.cat(l2s).numpy()
+        out[name + "_linf"] = torch.cat(linf).numpy()
+        out[name + "_logits"] = torch.cat(logit_rows).numpy()
+        print(f"[{tag}] {name}: success {int(torch.cat(succ).sum())}/{n}, l2 {torch.cat(l2s).mean():.4f}, {time.time() - t0:.0f} s",
+              flush=True)
+    np.savez_compressed(OUT / f"config3_{tag}.npz", **out)
+
+
+def config5(tag: str, ref_attack, ref_def, n: int = 256):
+    """BASELINE config 5 on the first `n` images: the reference's own batch-1 loop (defense_experiments.py:804-832),
+    threshold calibrated on the first 100 images (:775-796).  Per image and (attack, eps) it records the six booleans
+    evaluate_defenses returns, and — through recording wrappers around the reference's own functions, which are called
+    unmodified — the detector scores and the three predictions, so a flag that differs can be reported with its margin."""
+    model = weights.MODELS[tag](0)
+    mean, std = weights.mean_std()
+    x = images_for(tag, n)
+    scores_log, preds_log = [], []
+    orig_l3 = ref_def._layer3_features
+
+    def rec_l3(*a, **k):
+        s = orig_l3(*a, **k)
+        scores_log.append(float(s[0]))
+        return s
+
+    ref_def._layer3_features = rec_l3
+    model.register_forward_hook(lambda mod, inp, outp: preds_log.append(int(outp[0].argmax())))
+    calib = torch.cat([orig_l3(model, x[i:i + 1], mean, std) for i in range(min(100, n))])
+    thr = threshold_for(tag, calib)
+    out = {"n": n, "threshold": np.float64(thr), "calib_scores": calib.numpy(), "eps_list": np.array(EPS_LISTS[tag]),
+           "alpha": np.float64(ALPHA), "steps": STEPS, "noise_seed0": NOISE_SEED0}
+    keys = ("clean_correct", "attack_success", "defense_preproc_success", "detector_flags_clean", "detector_flags_adv",
+            "detector_attack_success")
+    with torch.no_grad():
+        y = torch.cat([model(ref_attack.normalize_batch(x[i:i + 32], mean, std)).argmax(1) for i in range(0, n, 32)])
+    out["y"] = y.numpy()
+    for attack_name in ("fgsm", "pgd"):
+        for ei, e in enumerate(EPS_LISTS[tag]):
+            t0 = time.time()
+            flags = np.zeros((n, 6), dtype=np.uint8)
+            sc = np.zeros((n, 2), dtype=np.float32)      # detector score of x_adv, of x
+            pr = np.zeros((n, 3), dtype=np.int64)        # predictions: clean, adversarial, defended
+            for i in range(n):
+                scores_log.clear(); preds_log.clear()
+                torch.manual_seed(NOISE_SEED0 + i)
+                r = ref_def.evaluate_defenses(model, x[i:i + 1], y[i:i + 1], mean, std, attack_name, float(e), ALPHA, STEPS,
+                                              1.0, 0.0, 100, 0.01, thr)
+                flags[i] = [int(r[k]) for k in keys]
+                sc[i] = scores_log[-2:]
+                pr[i] = [preds_log[0], preds_log[-2], preds_log[-1]]
+            out[f"{attack_name}_{ei}_flags"] = flags
+            out[f"{attack_name}_{ei}_scores"] = sc
+            out[f"{attack_name}_{ei}_preds"] = pr
+            print(f"[{tag}] {attack_name} eps={e * 255:g}/255: sums {flags.sum(0).tolist()} of {n}, {time.time() - t0:.0f} s",
+                  flush=True)
+            np.savez_compressed(OUT / f"config5_{tag}.npz", **out)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", choices=["seed0", "cond"], required=True)
+    ap.add_argument("--what", choices=["quick", "config3", "config5"], required=True)
+    ap.add_argument("--n", type=int, default=0)
+    ap.add_argument("--threads", type=int, default=0)
+    args = ap.parse_args()
+    if args.threads:
+        torch.set_num_threads(args.threads)
+    OUT.mkdir(parents=True, exist_ok=True)
+    ref_attack, ref_def = import_reference()
+    if args.what == "quick":
+        quick(args.model, ref_attack, ref_def)
+    elif args.what == "config3":
+        config3(args.model, ref_attack, ref_def, args.n or 16)
+    else:
+        config5(args.model, ref_attack, ref_def, args.n or 256)
+
+
+if __name__ == "__main__":
+    main()

@@ -163,3 +163,75 @@ def test_detector_and_evaluate_defenses_match_reference(golden_meta, fmodel):
     out, _ = defenses_ref.evaluate_defenses(fmodel, x, y, mean, std, "fgsm", 4 / 255, 2 / 255, 10, det["threshold"])
     want = det["evaluate_defenses"]["fgsm_4"][0]
     assert {k: int(v) for k, v in out.items()} == want
+
+
+# ---------------------------------------------------------------- the conditioned (non-identity BatchNorm) fixture model
+@pytest.fixture(scope="module")
+def cond_model():
+    return weights.conditioned_resnet50(0)
+
+
+def test_conditioned_model_has_nontrivial_batchnorm_everywhere(cond_model):
+    """Every one of the 53 BatchNorms folds to a non-trivial scale AND shift (the seed-0 model folds to 1/sqrt(1+eps), 0)."""
+    sd = cond_model.state_dict()
+    n = 0
+    for k in sd:
+        if k.endswith("running_var"):
+            p = k[:-len(".running_var")]
+            scale = sd[p + ".weight"] / torch.sqrt(sd[k] + 1e-5)
+            shift = sd[p + ".bias"] - sd[p + ".running_mean"] * scale
+            assert float(scale.std()) > 1e-3 and float(shift.abs().mean()) > 1e-3, p
+            n += 1
+    assert n == 53
+    # the committed statistics are what a fresh calibration pass computes (to fp32 noise)
+    fresh = weights.conditioned_resnet50(0, stats_file="/nonexistent").state_dict()
+    for k in sd:
+        if "running_" in k:
+            assert float((sd[k] - fresh[k]).abs().max() / fresh[k].abs().max()) < 1e-4, k
+
+
+def test_functional_resnet_matches_reference_on_the_conditioned_model(golden_dir, cond_model):
+    g = np.load(golden_dir / "cond_resnet.npz")
+    meta = __import__("json").loads((golden_dir / "meta_cond.json").read_text())
+    mean, std = weights.mean_std()
+    x = weights.mixed_images(8, seed=77)[:4]
+    y = torch.from_numpy(g["y"])
+    fm = resnet50_ref.FunctionalResNet50(cond_model.state_dict())
+    grad, logits = attacks_ref.ce_input_grad(fm, x, y, mean, std)
+    ref = torch.from_numpy(g["logits"])
+    assert float((logits - ref).norm() / ref.norm()) < 1e-5
+    assert torch.equal(logits.argmax(1), y) and len(set(y.tolist())) > 1          # predictions differ between images
+    gref = torch.from_numpy(g["grad"])
+    assert float((grad - gref).norm() / gref.norm()) < 3 * meta["ref_fp32_vs_fp64"]["grad_rel"] + 1e-3
+
+
+def test_bf16_emulator_without_rounding_is_the_reference_network(golden_dir, cond_model):
+    """oracle/resnet50_bf16emu.py with emulate=False == torchvision in float64 (the reference's fp64 golden)."""
+    from oracle import resnet50_bf16emu as emu
+    g = np.load(golden_dir / "cond_resnet.npz")
+    mean, std = weights.mean_std()
+    x = weights.mixed_images(8, seed=77)[:2]
+    y = torch.from_numpy(g["y"])[:2]
+    e = emu.Bf16EmuResNet50(cond_model.state_dict(), emulate=False)
+    grad, logits = e.input_grad(x, y, mean, std, inv_n=1 / 4)          # the golden gradient is the mean over 4 images
+    l64, g64 = torch.from_numpy(g["logits64"])[:2], torch.from_numpy(g["grad64"])[:2]
+    assert float((logits - l64).norm() / l64.norm()) < 2e-6            # BN folded in fp32, like the product
+    assert float((grad - g64).norm() / g64.norm()) < 2e-3
+
+
+@pytest.mark.parametrize("precision", ["bf16", "fp32"])
+def test_launch_by_launch_oracle_reproduces_the_autograd_emulator(cond_model, precision):
+    """oracle/trace_ref.py (explicit per-launch forward / input-gradient formulas, used teacher-forced against the CUDA
+    trace) chained free-running == the autograd-based emulator: same logits bit for bit, same gradient."""
+    from oracle import resnet50_bf16emu as emu, trace_ref
+    mean, std = weights.mean_std()
+    x = weights.mixed_images(2, seed=5)
+    e = emu.Bf16EmuResNet50(cond_model.state_dict(), emulate=precision == "bf16")
+    y = e(x, mean, std).argmax(1)
+    grad, logits = e.input_grad(x, y, mean, std)
+    w = trace_ref.ManualResNet50(cond_model.state_dict(), precision).walk(x, mean, std, y, 1 / 2)
+    assert float((w["logits"].flatten(1) - logits).abs().max()) < 1e-6
+    assert float((w["grad"] - grad).norm() / grad.norm()) < 1e-6
+    rel, bad = trace_ref.compare(w["grad"], grad, precision == "bf16")
+    assert bad == 0
+    assert trace_ref.canonical("bwd l2.0.c2/*") == "bwd l2.0.c2" and trace_ref.canonical("bwd l3.0.c1+ds/3") == "bwd l3.0.c1+ds"
