@@ -111,19 +111,25 @@ def quick(tag: str, ref_attack, ref_def):
     # detector scores / threshold / evaluate_defenses dicts (batch 1)
     scores = torch.cat([ref_def._layer3_features(model, xs[i:i + 1], mean, std) for i in range(8)])
     thr = threshold_for(tag, scores)
-    evals = {}
+    evals, gaps = {}, {}
+    gaps_log = []
+    hook = model.register_forward_hook(lambda mod, inp, outp: gaps_log.append(float(outp[0].detach().topk(2).values.diff().abs())))
     for attack_name in ("fgsm", "pgd"):
         for e in EPS_LISTS[tag]:
-            rows = []
+            rows, grows = [], []
             for i in range(2):
                 xi1 = xs[i:i + 1]
                 yi = model(ref_attack.normalize_batch(xi1, mean, std)).argmax(1)
                 torch.manual_seed(100 + i)
+                gaps_log.clear()
                 r = ref_def.evaluate_defenses(model, xi1, yi, mean, std, attack_name, float(e), alpha, 10, 1.0, 0.0, 20,
                                               0.01, thr)
                 rows.append({k: int(v) for k, v in r.items()})
+                grows.append([gaps_log[0], gaps_log[-2], gaps_log[-1]])     # top-1/top-2 logit gap: clean, adversarial, defended
             evals[f"{attack_name}_{e * 255:g}"] = rows
-    meta["detector"] = {"scores": scores.tolist(), "threshold": thr, "evaluate_defenses": evals}
+            gaps[f"{attack_name}_{e * 255:g}"] = grows
+    hook.remove()
+    meta["detector"] = {"scores": scores.tolist(), "threshold": thr, "evaluate_defenses": evals, "decision_gaps": gaps}
     (OUT / f"meta_{tag}.json").write_text(json.dumps(meta, indent=1))
     print(json.dumps(meta, indent=1)[:2500])
 
@@ -176,7 +182,14 @@ def config5(tag: str, ref_attack, ref_def, n: int = 256):
         return s
 
     ref_def._layer3_features = rec_l3
-    model.register_forward_hook(lambda mod, inp, outp: preds_log.append(int(outp[0].argmax())))
+    gaps_log = []
+
+    def rec_pred(mod, inp, outp):
+        top2 = outp[0].detach().topk(2).values
+        preds_log.append(int(outp[0].argmax()))
+        gaps_log.append(float(top2[0] - top2[1]))          # top-1 / top-2 logit gap: how close the decision was to a tie
+
+    model.register_forward_hook(rec_pred)
     calib = torch.cat([orig_l3(model, x[i:i + 1], mean, std) for i in range(min(100, n))])
     thr = threshold_for(tag, calib)
     out = {"n": n, "threshold": np.float64(thr), "calib_scores": calib.numpy(), "eps_list": np.array(EPS_LISTS[tag]),
@@ -192,17 +205,20 @@ def config5(tag: str, ref_attack, ref_def, n: int = 256):
             flags = np.zeros((n, 6), dtype=np.uint8)
             sc = np.zeros((n, 2), dtype=np.float32)      # detector score of x_adv, of x
             pr = np.zeros((n, 3), dtype=np.int64)        # predictions: clean, adversarial, defended
+            gp = np.zeros((n, 3), dtype=np.float32)      # their top-1 / top-2 logit gaps
             for i in range(n):
-                scores_log.clear(); preds_log.clear()
+                scores_log.clear(); preds_log.clear(); gaps_log.clear()
                 torch.manual_seed(NOISE_SEED0 + i)
                 r = ref_def.evaluate_defenses(model, x[i:i + 1], y[i:i + 1], mean, std, attack_name, float(e), ALPHA, STEPS,
                                               1.0, 0.0, 100, 0.01, thr)
                 flags[i] = [int(r[k]) for k in keys]
                 sc[i] = scores_log[-2:]
                 pr[i] = [preds_log[0], preds_log[-2], preds_log[-1]]
+                gp[i] = [gaps_log[0], gaps_log[-2], gaps_log[-1]]
             out[f"{attack_name}_{ei}_flags"] = flags
             out[f"{attack_name}_{ei}_scores"] = sc
             out[f"{attack_name}_{ei}_preds"] = pr
+            out[f"{attack_name}_{ei}_gaps"] = gp
             print(f"[{tag}] {attack_name} eps={e * 255:g}/255: sums {flags.sum(0).tolist()} of {n}, {time.time() - t0:.0f} s",
                   flush=True)
             np.savez_compressed(OUT / f"config5_{tag}.npz", **out)

@@ -122,6 +122,8 @@ def test_cw_step_full_size_vector_path_vs_oracle():
     x = torch.rand(3, 3, 224, 224, generator=gen)
     d = CwDriver(x, dev)
     succ = torch.tensor([1, 0, 1], dtype=torch.uint8, device=dev)
+    best_l2 = torch.full((3,), float("inf"), device=dev)
+    best_adv = d.x0.clone()
     for t in range(1, 4):
         gx = (torch.randn(3, 3, 224, 224, generator=gen) * 0.05).to(dev)
         w_prev, m_prev, v_prev, xa_prev = d.w.clone(), d.m.clone(), d.v.clone(), d.x_adv.clone()
@@ -133,7 +135,10 @@ def test_cw_step_full_size_vector_path_vs_oracle():
         assert float(((d.v - v_ref).abs() / v_ref.abs().clamp_min(1e-12)).max()) < 1e-5
         np.testing.assert_allclose(d.l2_now.cpu().numpy(), (xa_prev - d.x0).flatten(1).double().pow(2).sum(1).cpu().numpy(),
                                    rtol=2e-6, atol=1e-9)
-        assert torch.equal(d.best_adv[0], xa_prev[0]) and torch.equal(d.best_adv[1], d.x0[1])     # only improved images copy
+        improved = succ.bool() & (d.l2_now < best_l2)                      # attack.py:133-137
+        best_l2 = torch.where(improved, d.l2_now, best_l2)
+        best_adv = torch.where(improved.view(-1, 1, 1, 1), xa_prev, best_adv)
+        assert torch.equal(d.best_adv, best_adv) and torch.equal(d.best_l2, best_l2)     # only improved images copy
     # misaligned state arrays: same results through the scalar path
     d2 = CwDriver(x, dev)
     from advb200 import _lib
