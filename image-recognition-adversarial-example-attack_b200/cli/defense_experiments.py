@@ -65,8 +65,9 @@ def main(argv=None) -> None:
     device = torch.device("cuda", local)
     torch.cuda.set_device(device)
     say = print if rank == 0 else (lambda *a, **k: None)
-    if args.model_type == "robust":
-        raise SystemExit("the RobustBench checkpoint (defense_experiments.py:676) is not available offline")
+    if args.model_type == "robust" and args.weights != "random":
+        raise SystemExit("the RobustBench checkpoint (defense_experiments.py:676) is not available offline; "
+                         "use --model_type robust --weights random for the same code path on seeded weights")
     # defense_experiments.py:770-772: the JPEG stage of defend_input (run on the device here, bit-exact with PIL's)
     defenses._DEFENSE_USE_JPEG = bool(args.use_jpeg)
     defenses._DEFENSE_JPEG_QUALITY = int(args.jpeg_quality)
@@ -80,8 +81,13 @@ def main(argv=None) -> None:
         except Exception as e:
             raise SystemExit(f"could not load the pretrained torchvision checkpoint ({e}); use --weights random")
     nm = advb200.native_model(model.to(device))
-    mean = torch.tensor([0.485, 0.456, 0.406])
-    std = torch.tensor([0.229, 0.224, 0.225])
+    if args.model_type == "robust":
+        # defense_experiments.py:764-767: the RobustBench model normalises internally, so the attack functions get
+        # mean = 0 / std = 1 (same ResNet-50 architecture, the normalisation fused into conv1 becomes the identity)
+        mean, std = torch.zeros(3), torch.ones(3)
+    else:
+        mean = torch.tensor([0.485, 0.456, 0.406])
+        std = torch.tensor([0.229, 0.224, 0.225])
     transform = preprocess.get_transform(device)      # Resize(256) -> CenterCrop(224) -> ToTensor, on the device
 
     # ---- images: the whole list is known to every rank; each rank materialises only its shard
@@ -145,14 +151,23 @@ def main(argv=None) -> None:
             for b0 in range(0, x_shard.shape[0], args.batch):
                 xb = x_shard[b0:b0 + args.batch]
                 yb = nm.forward(xb, mean, std, want_logits=False, want_preds=True)["preds"]
+                noise = None
+                if attack_name == "pgd":
+                    # PGD's random start (attack.py:51), drawn per batch from a generator seeded by the batch's GLOBAL
+                    # image offset: the noise of an image does not depend on how the list is sharded, so the counters of
+                    # a 1-rank and an 8-rank run are bit-equal whenever the shards are whole batches
+                    gen = torch.Generator(device=device)
+                    gen.manual_seed(int(args.seed) * 1000003 + (lo + b0) * 7 + 1)
+                    noise = torch.empty_like(xb).uniform_(-float(eps), float(eps), generator=gen)
                 counters += defenses.evaluate_defenses_batched(
                     nm, xb, yb, mean, std, attack_name, float(eps), float(args.alpha), int(args.steps),
-                    float(args.cw_c), float(args.cw_kappa), int(args.cw_steps), float(args.cw_lr), thr)
+                    float(args.cw_c), float(args.cw_kappa), int(args.cw_steps), float(args.cw_lr), thr, pgd_noise=noise)
             adist.allreduce_counters(counters)
             results[(attack_name, float(eps))] = counters.cpu().tolist()
 
     say("\n" + "=" * 60)
     for (attack_name, eps), c in sorted(results.items()):
+        say(f"counters attack={attack_name} eps={eps:.5f}: {c}")
         r = adist.rates_from_counters(c)
         say(f"attack={attack_name}, eps={eps:.5f}, "
             f"attack_success={r['attack_success']:.3f}, "
