@@ -168,7 +168,50 @@ __global__ void div9_check_kernel(unsigned long long* mismatches, unsigned int* 
 // One thread produces a 4-wide strip of kSmoothRows output rows from a (kSmoothRows + 2)-row register window, so
 // every input element is fetched from L1/L2 about 1.5x and from HBM once.
 constexpr int kSmoothRows = 4;
-template <bool kDefend>
+
+// (kSmoothRows + 2) x 6 input window of a 4-wide, kSmoothRows-tall output strip, zero padded.  93 % of the strips of a
+// 224 x 224 plane are interior and 16-byte aligned: they take the branch-free path (18 unconditional loads, all issued
+// before any use); edge or unaligned strips take the bounds-checked scalar path.
+__device__ __forceinline__ void load_window(const float* __restrict__ src, int h, int w, int r0, int c0, bool vec,
+                                            float (&win)[kSmoothRows + 2][6]) {
+  const bool interior = vec && r0 > 0 && r0 + kSmoothRows < h && c0 > 0 && c0 + 4 < w;
+  if (interior) {
+    const float* row = src + (int64_t)(r0 - 1) * w + c0;
+#pragma unroll
+    for (int k = 0; k < kSmoothRows + 2; ++k, row += w) {
+      const float4 m = __ldg(reinterpret_cast<const float4*>(row));
+      win[k][0] = __ldg(row - 1);
+      win[k][1] = m.x; win[k][2] = m.y; win[k][3] = m.z; win[k][4] = m.w;
+      win[k][5] = __ldg(row + 4);
+    }
+    return;
+  }
+#pragma unroll
+  for (int k = 0; k < kSmoothRows + 2; ++k) {
+    const int r = r0 - 1 + k;
+    float* v = win[k];
+    if (r < 0 || r >= h) {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) v[j] = 0.f;
+      continue;
+    }
+    const float* row = src + (int64_t)r * w;
+    if (vec) {
+      const float4 m = __ldg(reinterpret_cast<const float4*>(row + c0));
+      v[0] = c0 > 0 ? __ldg(row + c0 - 1) : 0.f;
+      v[1] = m.x; v[2] = m.y; v[3] = m.z; v[4] = m.w;
+      v[5] = c0 + 4 < w ? __ldg(row + c0 + 4) : 0.f;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        const int c = c0 - 1 + j;
+        v[j] = (c >= 0 && c < w) ? __ldg(row + c) : 0.f;
+      }
+    }
+  }
+}
+
+template <bool kDefend, typename Idx>
 __global__ void __launch_bounds__(256, 4)
 smooth3x3_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t planes, int h, int w,
                  float lm1) {
@@ -177,12 +220,15 @@ smooth3x3_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t p
   if (kDefend) quant_table_init(tab, lm1);
   const int groups = (w + 3) >> 2;                         // 4-wide column groups
   const int row_chunks = (h + kSmoothRows - 1) / kSmoothRows;
-  const int64_t total = planes * row_chunks * (int64_t)groups;
-  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-       t += (int64_t)gridDim.x * blockDim.x) {
-    const int gx = (int)(t % groups);
-    const int rc = (int)((t / groups) % row_chunks);
-    const int64_t p = t / ((int64_t)groups * row_chunks);
+  // Idx = uint32_t whenever the strip count (+ one grid stride) fits 31 bits: two 32-bit divisions per strip instead of
+  // three 64-bit ones (about 80 of the ~620 instructions a strip costs)
+  const Idx total = (Idx)(planes * row_chunks * (int64_t)groups);
+  for (Idx t = (Idx)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (Idx)gridDim.x * blockDim.x) {
+    const Idx tq = t / (Idx)groups;
+    const int gx = (int)(t - tq * (Idx)groups);
+    const Idx tp = tq / (Idx)row_chunks;
+    const int rc = (int)(tq - tp * (Idx)row_chunks);
+    const int64_t p = (int64_t)tp;
     const float* src = x + p * (int64_t)h * w;
     float* dst = out + p * (int64_t)h * w;
     const int c0 = gx * 4;
@@ -191,32 +237,15 @@ smooth3x3_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t p
     // flight per thread instead of one (the sliding 3-row window left the kernel latency-bound at 0.48 of HBM peak)
     float win[kSmoothRows + 2][6];
     const bool vec = ((w & 3) == 0) && ((reinterpret_cast<uintptr_t>(src) & 15u) == 0);
-    auto load_row = [&](int r, float* v) {
-      if (r < 0 || r >= h) {
+    load_window(src, h, w, r0, c0, vec, win);
+    if (kDefend) {
+      // clamp AFTER every load of the window has been issued: clamping inside load_row made each row's loads wait for
+      // the previous row's first use (ncu: long-scoreboard 6.1 stalls per issue, 0.49 of the HBM rate)
 #pragma unroll
-        for (int j = 0; j < 6; ++j) v[j] = 0.f;
-        return;
-      }
-      const float* row = src + (int64_t)r * w;
-      if (vec) {
-        const float4 m = __ldg(reinterpret_cast<const float4*>(row + c0));
-        v[0] = c0 > 0 ? __ldg(row + c0 - 1) : 0.f;
-        v[1] = m.x; v[2] = m.y; v[3] = m.z; v[4] = m.w;
-        v[5] = c0 + 4 < w ? __ldg(row + c0 + 4) : 0.f;
-      } else {
+      for (int k = 0; k < kSmoothRows + 2; ++k)
 #pragma unroll
-        for (int j = 0; j < 6; ++j) {
-          const int c = c0 - 1 + j;
-          v[j] = (c >= 0 && c < w) ? __ldg(row + c) : 0.f;
-        }
-      }
-      if (kDefend) {
-#pragma unroll
-        for (int j = 0; j < 6; ++j) v[j] = fminf(fmaxf(v[j], 0.f), 1.f);   // clamp(0) = 0: the zero padding survives
-      }
-    };
-#pragma unroll
-    for (int k = 0; k < kSmoothRows + 2; ++k) load_row(r0 - 1 + k, win[k]);
+        for (int j = 0; j < 6; ++j) win[k][j] = fminf(fmaxf(win[k][j], 0.f), 1.f);   // clamp(0) = 0: the zero padding survives
+    }
 #pragma unroll
     for (int dr = 0; dr < kSmoothRows; ++dr) {
       const int r = r0 + dr;
@@ -431,45 +460,25 @@ __global__ void eval_counters_kernel(const int64_t* __restrict__ pred_clean,
 __device__ __forceinline__ float med3(float a, float b, float c) {
   return fmaxf(fminf(a, b), fminf(fmaxf(a, b), c));
 }
+template <typename Idx>
 __global__ void __launch_bounds__(256, 4)
 median3x3_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t planes, int h, int w) {
   const int groups = (w + 3) >> 2;
   const int row_chunks = (h + kSmoothRows - 1) / kSmoothRows;
-  const int64_t total = planes * row_chunks * (int64_t)groups;
-  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-       t += (int64_t)gridDim.x * blockDim.x) {
-    const int gx = (int)(t % groups);
-    const int rc = (int)((t / groups) % row_chunks);
-    const int64_t p = t / ((int64_t)groups * row_chunks);
+  const Idx total = (Idx)(planes * row_chunks * (int64_t)groups);      // (32-bit strip index when it fits: see smooth3x3_kernel)
+  for (Idx t = (Idx)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (Idx)gridDim.x * blockDim.x) {
+    const Idx tq = t / (Idx)groups;
+    const int gx = (int)(t - tq * (Idx)groups);
+    const Idx tp = tq / (Idx)row_chunks;
+    const int rc = (int)(tq - tp * (Idx)row_chunks);
+    const int64_t p = (int64_t)tp;
     const float* src = x + p * (int64_t)h * w;
     float* dst = out + p * (int64_t)h * w;
     const int c0 = gx * 4;
     const int r0 = rc * kSmoothRows;
     float win[kSmoothRows + 2][6];
     const bool vec = ((w & 3) == 0) && ((reinterpret_cast<uintptr_t>(src) & 15u) == 0);
-#pragma unroll
-    for (int k = 0; k < kSmoothRows + 2; ++k) {
-      const int r = r0 - 1 + k;
-      float* v = win[k];
-      if (r < 0 || r >= h) {
-#pragma unroll
-        for (int j = 0; j < 6; ++j) v[j] = 0.f;
-      } else {
-        const float* row = src + (int64_t)r * w;
-        if (vec) {
-          const float4 m = __ldg(reinterpret_cast<const float4*>(row + c0));
-          v[0] = c0 > 0 ? __ldg(row + c0 - 1) : 0.f;
-          v[1] = m.x; v[2] = m.y; v[3] = m.z; v[4] = m.w;
-          v[5] = c0 + 4 < w ? __ldg(row + c0 + 4) : 0.f;
-        } else {
-#pragma unroll
-          for (int j = 0; j < 6; ++j) {
-            const int c = c0 - 1 + j;
-            v[j] = (c >= 0 && c < w) ? __ldg(row + c) : 0.f;
-          }
-        }
-      }
-    }
+    load_window(src, h, w, r0, c0, vec, win);
     // two output rows share the ordered pair of their two common input rows (per column: 2 + 2 x 4 operations instead
     // of 2 x 6), and two neighbouring outputs share the ordered pair of their two common column medians
 #pragma unroll
@@ -572,10 +581,15 @@ static int smooth_launch(const float* x, float* out, int64_t planes, int h, int 
   const int groups = (w + 3) / 4, chunks = (h + kSmoothRows - 1) / kSmoothRows;
   const int64_t total = planes * (int64_t)groups * chunks;
   const int grid = grid_for(total);
-  if (defend)
-    smooth3x3_kernel<true><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, (float)(levels - 1));
+  const bool small = total + (int64_t)grid * 256 < (int64_t(1) << 31);
+  if (defend && small)
+    smooth3x3_kernel<true, uint32_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, (float)(levels - 1));
+  else if (defend)
+    smooth3x3_kernel<true, int64_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, (float)(levels - 1));
+  else if (small)
+    smooth3x3_kernel<false, uint32_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, 0.f);
   else
-    smooth3x3_kernel<false><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, 0.f);
+    smooth3x3_kernel<false, int64_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, 0.f);
   ADV_LAUNCHED();
   return ADVB200_OK;
 }
@@ -590,7 +604,12 @@ int advb200_median3x3_f32(const float* x, float* out, int64_t planes, int h, int
   ADV_CHECK_ARG(x && out, "median3x3: null pointer");
   ADV_CHECK_ARG(x != out, "median3x3: in-place operation is not supported");
   const int groups = (w + 3) / 4, chunks = (h + kSmoothRows - 1) / kSmoothRows;
-  median3x3_kernel<<<grid_for(planes * (int64_t)groups * chunks), 256, 0, as_stream(stream)>>>(x, out, planes, h, w);
+  const int64_t total = planes * (int64_t)groups * chunks;
+  const int grid = grid_for(total);
+  if (total + (int64_t)grid * 256 < (int64_t(1) << 31))
+    median3x3_kernel<uint32_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w);
+  else
+    median3x3_kernel<int64_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w);
   ADV_LAUNCHED();
   return ADVB200_OK;
 }

@@ -7,9 +7,10 @@
 // against PIL by tests/golden/jpeg_cases.npz):
 //
 //   kernel 1 (jpeg_codec_kernel): one CTA per strip of 16 rows x 256 columns (16 MCUs) of one image:
-//     fp32 NCHW -> uint8 (x*255 truncated) -> YCbCr -> smem; 2x2 chroma box filter; then ONE THREAD PER 8x8 BLOCK
-//     keeps the block in registers through fdct -> quantise -> dequantise -> idct -> range limit and writes the
-//     decoded bytes back; decoded Y (full size) and Cb/Cr (half size) go to a uint8 scratch (1.5 B/pixel).
+//     fp32 NCHW -> uint8 (x*255 truncated) -> YCbCr -> smem; 2x2 chroma box filter; then EIGHT LANES PER 8x8 BLOCK
+//     take it through fdct -> quantise -> dequantise -> idct -> range limit (row / column passes exchanged through
+//     shared memory) and write the decoded bytes back; decoded Y (full size) and Cb/Cr (half size) go to a uint8
+//     scratch (1.5 B/pixel).
 //   kernel 2 (jpeg_upsample_rgb_kernel): "fancy" h2v2 upsampling of the decoded chroma (needs the neighbouring
 //     blocks' samples, hence the second pass), YCbCr -> RGB, /255 -> fp32 NCHW.
 //
@@ -78,44 +79,58 @@ __device__ __forceinline__ void idct8(int* d) {
   d[3 * S] = descale(t13 + t0, sh); d[4 * S] = descale(t13 - t0, sh);
 }
 
-// one 8x8 block, in place in shared memory (rows `pitch` bytes apart): the whole codec in registers
-__device__ __forceinline__ void codec_block(uint8_t* blk, int pitch, const JpegTables& tb, int comp) {
-  int d[64];
-#pragma unroll
-  for (int r = 0; r < 8; ++r) {
-    const uint2 v = *reinterpret_cast<const uint2*>(blk + r * pitch);
+// One 8x8 block by EIGHT lanes of a warp (lane l owns row l in the row passes and column l in the column passes), in
+// place in shared memory (rows `pitch` bytes apart).  The two DCTs are separable, so the block goes
+//   rows: fdct  ->  [exchange]  ->  columns: fdct, quantise, dequantise, idct  ->  [exchange]  ->  rows: idct, range limit
+// with the 64 intermediate ints exchanged through `ws` (block stride 72 ints: the four blocks a warp works on fall on
+// different banks).  One thread per block (the first version) left 32 of 128 threads idle and every busy thread with a
+// ~2500-instruction dependent chain; here every lane has four 8-point passes (~220 instructions) and all lanes work.
+// Same integer arithmetic in the same order per 1-D pass, hence the same bits.
+constexpr int kWsStride = 72;
+__device__ __forceinline__ void codec_block8(uint8_t* blk, int pitch, int* ws, const uint16_t* q, const uint32_t* recip,
+                                             int l, bool active) {
+  int d[8];
+  if (active) {
+    const uint2 v = *reinterpret_cast<const uint2*>(blk + l * pitch);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      d[r * 8 + k] = (int)((v.x >> (8 * k)) & 0xffu) - 128;
-      d[r * 8 + 4 + k] = (int)((v.y >> (8 * k)) & 0xffu) - 128;
+      d[k] = (int)((v.x >> (8 * k)) & 0xffu) - 128;
+      d[4 + k] = (int)((v.y >> (8 * k)) & 0xffu) - 128;
     }
+    fdct8<1, true>(d);
+    *reinterpret_cast<int4*>(ws + l * 8) = make_int4(d[0], d[1], d[2], d[3]);
+    *reinterpret_cast<int4*>(ws + l * 8 + 4) = make_int4(d[4], d[5], d[6], d[7]);
   }
+  __syncwarp();
+  if (active) {
 #pragma unroll
-  for (int r = 0; r < 8; ++r) fdct8<1, true>(d + r * 8);
+    for (int r = 0; r < 8; ++r) d[r] = ws[r * 8 + l];
+    fdct8<1, false>(d);
+    // jcdctmgr.c: divisor q<<3 (the islow DCT leaves a factor 8), round half away from zero; then dequantise
 #pragma unroll
-  for (int c = 0; c < 8; ++c) fdct8<8, false>(d + c);
-  // jcdctmgr.c: divisor q<<3 (the islow DCT leaves a factor 8), round half away from zero; then dequantise
+    for (int r = 0; r < 8; ++r) {
+      const int qq = q[r * 8 + l];
+      const int v = d[r];
+      const uint32_t a = (uint32_t)(v < 0 ? -v : v) + (uint32_t)(qq << 2);
+      const int mag = (int)__umulhi(a, recip[r * 8 + l]);
+      d[r] = (v < 0 ? -mag : mag) * qq;
+    }
+    idct8<1, true>(d);
 #pragma unroll
-  for (int i = 0; i < 64; ++i) {
-    const int q = tb.q[comp][i];
-    const int v = d[i];
-    const uint32_t a = (uint32_t)(v < 0 ? -v : v) + (uint32_t)(q << 2);
-    const int mag = (int)__umulhi(a, tb.recip[comp][i]);
-    d[i] = (v < 0 ? -mag : mag) * q;
+    for (int r = 0; r < 8; ++r) ws[r * 8 + l] = d[r];
   }
-#pragma unroll
-  for (int c = 0; c < 8; ++c) idct8<8, true>(d + c);
-#pragma unroll
-  for (int r = 0; r < 8; ++r) idct8<1, false>(d + r * 8);
-#pragma unroll
-  for (int r = 0; r < 8; ++r) {
+  __syncwarp();
+  if (active) {
+    const int4 a = *reinterpret_cast<const int4*>(ws + l * 8), b = *reinterpret_cast<const int4*>(ws + l * 8 + 4);
+    d[0] = a.x; d[1] = a.y; d[2] = a.z; d[3] = a.w; d[4] = b.x; d[5] = b.y; d[6] = b.z; d[7] = b.w;
+    idct8<1, false>(d);
     uint2 v = make_uint2(0u, 0u);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      v.x |= (uint32_t)min(max(d[r * 8 + k] + 128, 0), 255) << (8 * k);
-      v.y |= (uint32_t)min(max(d[r * 8 + 4 + k] + 128, 0), 255) << (8 * k);
+      v.x |= (uint32_t)min(max(d[k] + 128, 0), 255) << (8 * k);
+      v.y |= (uint32_t)min(max(d[4 + k] + 128, 0), 255) << (8 * k);
     }
-    *reinterpret_cast<uint2*>(blk + r * pitch) = v;
+    *reinterpret_cast<uint2*>(blk + l * pitch) = v;
   }
 }
 
@@ -131,6 +146,10 @@ jpeg_codec_kernel(const float* __restrict__ x, uint8_t* __restrict__ ydec, uint8
   __shared__ __align__(16) uint8_t sCbF[16][kStripW];     // full-resolution chroma of the strip
   __shared__ __align__(16) uint8_t sCrF[16][kStripW];
   __shared__ __align__(16) uint8_t sC[2][8][kStripW / 2];  // downsampled, then decoded in place
+  __shared__ __align__(16) int sW[(kCodecThreads / 8) * kWsStride];   // per 8-lane group: one block's 64 intermediates
+  __shared__ uint16_t sQ[2][64];                            // the tables, indexed by lane (constant memory would serialise)
+  __shared__ uint32_t sRecip[2][64];
+  for (int i = threadIdx.x; i < 128; i += kCodecThreads) { sQ[i >> 6][i & 63] = tb.q[i >> 6][i & 63]; sRecip[i >> 6][i & 63] = tb.recip[i >> 6][i & 63]; }
   const int strip = blockIdx.x % strips;
   const int mr = (blockIdx.x / strips) % mcu_rows;
   const long long img = blockIdx.x / (strips * mcu_rows);
@@ -201,15 +220,19 @@ jpeg_codec_kernel(const float* __restrict__ x, uint8_t* __restrict__ ydec, uint8
     sC[comp][rr][cc] = (uint8_t)(s >> 2);
   }
   __syncthreads();
-  // ---- one thread per 8x8 block: 64 luma blocks, 16 + 16 chroma blocks
+  // ---- eight lanes per 8x8 block: 64 luma blocks, then 16 + 16 chroma blocks (6 rounds of 16 blocks per CTA)
   {
-    const int t = threadIdx.x;
-    if (t < 64) {
-      const int by = t >> 5, bx = t & 31;
-      if (col0 + bx * 8 < w && row0 + by * 8 < h) codec_block(&sY[by * 8][bx * 8], kStripW, tb, 0);
-    } else if (t < 96) {
-      const int comp = (t - 64) >> 4, bx = t & 15;
-      if ((col0 >> 1) + bx * 8 < wc) codec_block(&sC[comp][0][bx * 8], kStripW / 2, tb, 1);
+    const int grp = threadIdx.x >> 3, l = threadIdx.x & 7;
+    int* ws = sW + grp * kWsStride;
+    for (int b = grp; b < 96; b += kCodecThreads / 8) {
+      if (b < 64) {
+        const int by = b >> 5, bx = b & 31;
+        codec_block8(&sY[by * 8][bx * 8], kStripW, ws, sQ[0], sRecip[0], l, col0 + bx * 8 < w && row0 + by * 8 < h);
+      } else {
+        const int comp = (b - 64) >> 4, bx = b & 15;
+        codec_block8(&sC[comp][0][bx * 8], kStripW / 2, ws, sQ[1], sRecip[1], l, (col0 >> 1) + bx * 8 < wc);
+      }
+      __syncwarp();                                  // the group's workspace is reused by its next block
     }
   }
   __syncthreads();
