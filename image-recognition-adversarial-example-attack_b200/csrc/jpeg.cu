@@ -267,17 +267,25 @@ jpeg_codec_kernel(const float* __restrict__ x, uint8_t* __restrict__ ydec, uint8
 // source's special first / last column cases, where the neighbour term degenerates to the column itself)
 __device__ __forceinline__ int colsum(const uint8_t* near, const uint8_t* far, int j) { return 3 * near[j] + far[j]; }
 
+template <typename Idx>
 __global__ void __launch_bounds__(256)
 jpeg_upsample_rgb_kernel(const uint8_t* __restrict__ ydec, const uint8_t* __restrict__ cbdec,
                          const uint8_t* __restrict__ crdec, float* __restrict__ out, long long n_img, int h, int w) {
+  // ToTensor's k / 255 takes 256 values: a shared-memory table filled with the same true division replaces twelve IEEE
+  // division sequences per thread (the kernel is instruction-bound: ncu issue-active 83 %); bit-identical by construction
+  __shared__ float tab255[256];
+  tab255[threadIdx.x] = __fdiv_rn((float)threadIdx.x, 255.f);
+  __syncthreads();
   const int hc = (h + 1) >> 1, wc = (w + 1) >> 1, wq = (w + 3) >> 2;
-  const long long total = n_img * h * wq;                  // one thread per four horizontal output pixels
+  const Idx total = (Idx)(n_img * h * wq);                 // one thread per four horizontal output pixels
   const bool vec = ((w & 3) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15u) == 0) &&
                    ((reinterpret_cast<uintptr_t>(ydec) & 3u) == 0);
-  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
-    const int q = (int)(i % wq);
-    const int r = (int)((i / wq) % h);
-    const long long img = i / ((long long)wq * h);
+  for (Idx i = (Idx)blockIdx.x * 256 + threadIdx.x; i < total; i += (Idx)gridDim.x * 256) {
+    const Idx iq = i / (Idx)wq;                            // (32-bit index math whenever the thread count fits 31 bits)
+    const int q = (int)(i - iq * (Idx)wq);
+    const Idx ir = iq / (Idx)h;
+    const int r = (int)(iq - ir * (Idx)h);
+    const long long img = (long long)ir;
     const int rc = r >> 1;
     const int rfar = (r & 1) ? min(rc + 1, hc - 1) : max(rc - 1, 0);   // context rows replicate at the edges
     const int j0 = 2 * q;                                               // chroma columns j0, j0 + 1
@@ -318,9 +326,9 @@ jpeg_upsample_rgb_kernel(const uint8_t* __restrict__ ydec, const uint8_t* __rest
       const int R = y + ((91881 * xr + 32768) >> 16);
       const int B = y + ((116130 * xb + 32768) >> 16);
       const int G = y + ((-22554 * xb + 32768 - 46802 * xr) >> 16);
-      rgb[0][k] = __fdiv_rn((float)min(max(R, 0), 255), 255.f);         // ToTensor: div(255)
-      rgb[1][k] = __fdiv_rn((float)min(max(G, 0), 255), 255.f);
-      rgb[2][k] = __fdiv_rn((float)min(max(B, 0), 255), 255.f);
+      rgb[0][k] = tab255[min(max(R, 0), 255)];                          // ToTensor: div(255)
+      rgb[1][k] = tab255[min(max(G, 0), 255)];
+      rgb[2][k] = tab255[min(max(B, 0), 255)];
     }
 #pragma unroll
     for (int p = 0; p < 3; ++p) {
@@ -394,7 +402,10 @@ int advb200_jpeg_roundtrip_f32(const float* x, float* out, int n_img, int h, int
   int64_t grid = (quads + 255) / 256;
   const int64_t cap = (int64_t)kNumSMs * 32;
   if (grid > cap) grid = cap;
-  jpeg_upsample_rgb_kernel<<<(unsigned)grid, 256, 0, st>>>(ydec, cbdec, crdec, out, n_img, h, w);
+  if (quads + grid * 256 < (1ll << 31))
+    jpeg_upsample_rgb_kernel<uint32_t><<<(unsigned)grid, 256, 0, st>>>(ydec, cbdec, crdec, out, n_img, h, w);
+  else
+    jpeg_upsample_rgb_kernel<long long><<<(unsigned)grid, 256, 0, st>>>(ydec, cbdec, crdec, out, n_img, h, w);
   ADV_LAUNCHED();
   return ADVB200_OK;
 }

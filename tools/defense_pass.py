@@ -21,7 +21,24 @@ jbytes = int(lib.advb200_jpeg_scratch_bytes(n, H, W))
 jscratch = torch.empty(jbytes, dtype=torch.uint8, device=dev)
 
 
+per = x[0].numel()
+parts = int(lib.advb200_cw_parts(per))
+cw_w, cw_m, cw_v, cw_x0, cw_xa, cw_best, cw_g = (torch.empty_like(x) for _ in range(7))
+cw_g.normal_(0, 1e-3)
+cw_bl2 = torch.empty(n, device=dev)
+cw_bs = torch.empty(n, dtype=torch.uint8, device=dev)
+cw_succ = torch.zeros(n, dtype=torch.uint8, device=dev)
+cw_pa = torch.empty(n * parts + (n + 3) // 4 + 1, device=dev)
+cw_pb = torch.empty_like(cw_pa)
+xa, x0 = x.clone(), x.clone()
+
+
 def one():
+    assert lib.advb200_linf_step_f32(P(xa), P(x0), P(cw_g), 2 / 255, 8 / 255, elems, 1, S()) == 0
+    assert lib.advb200_cw_init_f32(P(x), P(cw_x0), P(cw_w), P(cw_m), P(cw_v), P(cw_xa), P(cw_best), P(cw_bl2), P(cw_bs), P(cw_pa),
+                                   n, per, S()) == 0
+    assert lib.advb200_cw_step_f32(P(cw_w), P(cw_m), P(cw_v), P(cw_x0), P(cw_g), P(cw_xa), P(cw_best), P(cw_bl2), P(cw_bs),
+                                   P(cw_succ), P(cw_pa), P(cw_pb), None, n, per, 0.05, 0.0316, 0.9, 0.999, 1e-8, S()) == 0
     assert lib.advb200_smooth3x3_f32(P(x), P(out), planes, H, W, S()) == 0
     assert lib.advb200_median3x3_f32(P(x), P(out), planes, H, W, S()) == 0
     assert lib.advb200_quantize_f32(P(x), P(out), elems, 16, S()) == 0

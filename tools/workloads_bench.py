@@ -71,6 +71,23 @@ jbytes = int(lib.advb200_jpeg_scratch_bytes(n, H, W))
 jscratch = torch.empty(jbytes, dtype=torch.uint8, device=dev)
 rec("jpeg_q75", timed(lambda: lib.advb200_jpeg_roundtrip_f32(P(x), P(out_buf), n, H, W, 75, P(jscratch), jbytes, S())), 9)
 
+# CW-L2 update kernel alone (attack.py:126-137 + Adam): reads w, m, v, x0, grad_x (20 B/elem), writes w, m, v, x_adv
+# (16 B/elem) = 36 B/elem; success = 0 for every image so no best_adv copy is added (that is +4 B/elem on improving steps)
+per = x[0].numel()
+parts = int(lib.advb200_cw_parts(per))
+cw_w, cw_m, cw_v, cw_x0, cw_xa, cw_best = (torch.empty_like(x) for _ in range(6))
+cw_bl2 = torch.empty(n, device=dev)
+cw_bs = torch.empty(n, dtype=torch.uint8, device=dev)
+cw_succ = torch.zeros(n, dtype=torch.uint8, device=dev)
+cw_pa = torch.empty(n * parts + (n + 3) // 4 + 1, device=dev)
+cw_pb = torch.empty_like(cw_pa)
+rec("cw_init", timed(lambda: lib.advb200_cw_init_f32(P(x), P(cw_x0), P(cw_w), P(cw_m), P(cw_v), P(cw_xa), P(cw_best), P(cw_bl2),
+                                                     P(cw_bs), P(cw_pa), n, per, S())), 28)
+gsmall = g * 1e-3
+rec("cw_step", timed(lambda: lib.advb200_cw_step_f32(P(cw_w), P(cw_m), P(cw_v), P(cw_x0), P(gsmall), P(cw_xa), P(cw_best), P(cw_bl2),
+                                                     P(cw_bs), P(cw_succ), P(cw_pa), P(cw_pb), None, n, per, 0.05, 0.0316, 0.9, 0.999,
+                                                     1e-8, S())), 36)
+
 if os.environ.get("ADVB200_WORKLOADS_KERNELS_ONLY") == "1":       # just the HBM-bound kernels (seconds)
     print(json.dumps(out))
     sys.exit(0)
