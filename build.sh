@@ -9,7 +9,7 @@ mkdir -p "$OUT" "$OUT/obj"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 FLAGS=(-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Xptxas -v "$@")
 pids=()
-for f in elementwise jpeg preprocess layers simt_conv tc_conv engine; do
+for f in elementwise jpeg preprocess layers transformer simt_conv tc_conv engine; do
   ( "$NVCC" "${FLAGS[@]}" -c "$SRC/$f.cu" -o "$OUT/obj/$f.o" > "$OUT/obj/$f.log" 2>&1 || { cat "$OUT/obj/$f.log"; exit 1; } ) &
   pids+=($!)
 done

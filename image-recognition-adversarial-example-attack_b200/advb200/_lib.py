@@ -51,6 +51,8 @@ SIGNATURES = {
                                     c_float, c_float, c_void_p, c_void_p, c_int64, c_void_p]),
     "advb200_linf_step_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_float, c_int64, c_int, c_void_p]),
     "advb200_random_start_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
+    "advb200_pgd_steps": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_float, c_float, c_float,
+                                  c_int, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "advb200_cw_parts": (c_int, [c_int64]),
     "advb200_cw_init_f32": (c_int, [c_void_p] * 10 + [c_int, c_int64, c_void_p]),
     "advb200_cw_step_f32": (c_int, [c_void_p] * 13 + [c_int, c_int64, c_float, c_float, c_double, c_double,
@@ -63,6 +65,20 @@ SIGNATURES = {
     "advb200_eval_counters": (c_int, [c_void_p] * 5 + [c_float, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "advb200_test_conv": (c_int, [c_int] + [c_void_p] * 6 + [c_int] * 9 + [c_void_p]),
     "advb200_test_force_tile": (c_int, [c_int, c_int, c_int, c_int]),
+    "advb200_linear_create": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, POINTER(c_void_p)]),
+    "advb200_linear_destroy": (c_int, [c_void_p]),
+    "advb200_linear_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p]),
+    "advb200_fc_scratch_bytes": (c_int64, [c_int, c_int]),
+    "advb200_fc_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "advb200_patch_im2col_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "advb200_vit_tokens_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "advb200_add_layernorm": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_int64, c_int, c_int, c_int,
+                                      c_void_p]),
+    "advb200_gelu_bf16": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
+    "advb200_window_attention_bf16": (c_int, [c_void_p, c_void_p, c_void_p] + [c_int] * 13 + [c_float, c_void_p]),
+    "advb200_patch_merge_gather_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "advb200_ln_pool_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+                                    c_void_p]),
     "advb200_debug_trace": (c_int, [c_void_p, c_int64]),
     "advb200_debug_trace_index": (c_int64, [c_char_p, c_int64]),
     "advb200_launch_count": (c_int64, []),

@@ -28,6 +28,11 @@ from .model import native_model
 # but measured 3.5 % slower end to end (that epilogue is already the stem kernel's critical path), so the default
 # is gradient + the HBM-rate update kernel; ADVB200_FUSED_STEP=1 opts in.
 _FUSED_STEP = bool(os.environ.get("ADVB200_FUSED_STEP"))
+# PGD's step loop runs natively (advb200_pgd_steps): one host call per step replaying a captured CUDA graph of the ~105
+# kernel launches.  ADVB200_NO_NATIVE_LOOP=1 keeps the Python loop over input_grad + linf_step, ADVB200_NO_GRAPH=1 keeps
+# the native loop but launches the kernels one by one.  All three give the same bits (tests/test_gpu_cw_kernels.py).
+_NATIVE_LOOP = not os.environ.get("ADVB200_NO_NATIVE_LOOP")
+_USE_GRAPH = not os.environ.get("ADVB200_NO_GRAPH")
 
 
 def normalize_batch(x: torch.Tensor, mean: torch.Tensor, std: torch.Tensor) -> torch.Tensor:
@@ -119,10 +124,17 @@ def pgd_linf_attack(model, x: torch.Tensor, y_true: torch.Tensor, *, eps: float,
         inv = 1.0 / n if inv_n_global is None else inv_n_global        # CE is a mean over the WHOLE batch (attack.py:58)
         # images are independent, so a batch larger than one workspace chunk runs all its steps chunk by chunk: the
         # engine keeps one launch plan per (batch size, workspace) and is not re-planned between steps
-        grad = torch.empty((min(n, nm.max_chunk),) + tuple(x_orig.shape[1:]), dtype=torch.float32, device=x.device)
+        grad = None
         for lo in range(0, n, nm.max_chunk):
             hi = min(n, lo + nm.max_chunk)
-            xa, xo, yy, g = x_adv[lo:hi], x_orig[lo:hi], y_dev[lo:hi], grad[:hi - lo]
+            xa, xo, yy = x_adv[lo:hi], x_orig[lo:hi], y_dev[lo:hi]
+            if not (nm.precision == "bf16" and _FUSED_STEP) and _NATIVE_LOOP and tuple(xa.shape[1:]) == (3, 224, 224):
+                # the whole loop of this chunk as one native call per step (captured CUDA graph, replayed)
+                nm.pgd_steps(xa, xo, mean, std, yy, alpha=alpha, eps=eps, steps=int(steps), inv_n_global=inv, use_graph=_USE_GRAPH)
+                continue
+            if grad is None:
+                grad = torch.empty((min(n, nm.max_chunk),) + tuple(x_orig.shape[1:]), dtype=torch.float32, device=x.device)
+            g = grad[:hi - lo]
             for _ in range(int(steps)):
                 if nm.precision == "bf16" and _FUSED_STEP:
                     # fused step: the sign step / projection / clamp run in the stem input-gradient kernel's epilogue

@@ -97,6 +97,7 @@ class NativeResNet50:
             _lib.check(rc, "advb200_model_create")
         self.handle = handle
         self._ws = {}   # n -> (raw tensor, aligned ptr, bytes)
+        self._pgd_bufs = {}   # n -> persistent iterate / gradient / label buffers of pgd_steps (stable pointers for the graph)
         self._finalizer = weakref.finalize(self, self.lib.advb200_model_destroy, handle)
         self.max_chunk = _MAX_CHUNK
         self._gen = 0   # bumped by every native call: tells the autograd wrapper whether its forward state survives
@@ -222,6 +223,41 @@ class NativeResNet50:
                                            nbytes, _lib.stream_ptr())
             _lib.check(rc, "advb200_backward")
         return grad
+
+    # -- the PGD loop body, `steps` times, as one native call (CUDA-graph replay) -----------------
+    def pgd_steps(self, x_adv, x_orig, mean, std, y_true, *, alpha, eps, steps, inv_n_global, use_graph=True):
+        """x_adv <- clamp(project(x_adv + alpha*sign(grad CE(x_adv)))) `steps` times, in place (attack.py:55-63), for one
+        chunk (n <= max_chunk).  The iteration runs on buffers this object owns (so the captured CUDA graph — ~105 kernel
+        launches replayed as one host call per step — sees the same pointers on every attack); the chunk is copied in and the
+        result copied back (two 0.6 MB/image device copies per attack)."""
+        n = x_adv.shape[0]
+        if n > self.max_chunk:
+            raise ValueError("pgd_steps works on one chunk: n <= max_chunk")
+        dev = self.device
+        buf = self._pgd_bufs.get(n)
+        if buf is None:
+            while len(self._pgd_bufs) >= 2:
+                self._pgd_bufs.pop(next(iter(self._pgd_bufs)))
+            mk = lambda: torch.empty((n, 3, 224, 224), dtype=torch.float32, device=dev)
+            buf = {"x_adv": mk(), "x_orig": mk(), "grad": mk(), "y": torch.empty((n,), dtype=torch.int64, device=dev),
+                   "mean": torch.empty(3, dtype=torch.float32, device=dev), "std": torch.empty(3, dtype=torch.float32, device=dev)}
+            self._pgd_bufs[n] = buf
+        buf["x_adv"].copy_(x_adv)
+        if x_orig is not None:
+            buf["x_orig"].copy_(x_orig)
+        buf["y"].copy_(y_true)
+        buf["mean"].copy_(self._vec3(mean, dev))
+        buf["std"].copy_(self._vec3(std, dev))
+        self._gen += 1
+        with torch.cuda.device(dev):
+            _, ws, nbytes = self._workspace(n)
+            rc = self.lib.advb200_pgd_steps(self.handle, _lib.ptr(buf["x_adv"]), _lib.ptr(buf["x_orig"]) if x_orig is not None else None,
+                                            _lib.ptr(buf["mean"]), _lib.ptr(buf["std"]), _lib.ptr(buf["y"]), n, float(inv_n_global),
+                                            float(alpha), float(eps), int(steps), _lib.ptr(buf["grad"]), c_void_p(ws), nbytes,
+                                            int(bool(use_graph)), _lib.stream_ptr())
+            _lib.check(rc, "advb200_pgd_steps")
+        x_adv.copy_(buf["x_adv"])
+        return x_adv
 
     # -- one fused attack step (bf16 mode) ----------------------------------------------------
     def attack_step(self, x_adv, x_orig, mean, std, y_true, *, alpha, eps, inv_n_global=None):

@@ -3,8 +3,8 @@
 table of :316-340 is printed in the same format.  Batched (the reference loops image by image); the success
 criterion is the reference's: the target's prediction on the adversarial differs from its own on the clean image.
 
-Targets: VGG-19 runs natively (advb200.transfer.NativeVGG19).  ViT-B/16 and Swin-T are not built (attention
-kernels are outside this path): their columns print "n/a".  Plotting (--visualize_n) is out of scope.
+Targets: VGG-19 (advb200.transfer.NativeVGG19), ViT-B/16 and Swin-T (advb200.transformers) all run natively on the
+device.  Plotting (--visualize_n) is out of scope.
 
     python blackbox_transfer.py --image_dir picture --attacks fgsm pgd cw
     python blackbox_transfer.py --synthetic 64 --weights random --attacks fgsm pgd       # offline smoke run
@@ -24,6 +24,7 @@ from PIL import Image  # noqa: E402
 
 from advb200 import cw_l2_attack, fgsm_attack, native_model, pgd_linf_attack, preprocess, set_default_precision  # noqa: E402
 from advb200.transfer import NativeVGG19, transfer_counts  # noqa: E402
+from advb200.transformers import NativeSwinT, NativeViTB16  # noqa: E402
 
 
 def build_parser() -> argparse.ArgumentParser:
@@ -62,6 +63,25 @@ def load_models(kind: str, seed: int, device):
     return src.to(device), vgg.to(device)
 
 
+def load_transformers(kind: str, seed: int, device):
+    """blackbox_transfer.py:36-54 `load_vit` / `load_swin` (IMAGENET1K_V1), or seeded random init offline.  torchvision
+    zero-initialises the ViT classifier head; the random-init variant redraws it so the column is not degenerate."""
+    if kind == "random":
+        torch.manual_seed(seed + 2)
+        vit = tv_models.vit_b_16(weights=None).eval()
+        with torch.no_grad():
+            vit.heads.head.weight.normal_(std=0.02)
+        torch.manual_seed(seed + 3)
+        swin = tv_models.swin_t(weights=None).eval()
+    else:
+        try:
+            vit = tv_models.vit_b_16(weights=tv_models.ViT_B_16_Weights.IMAGENET1K_V1).eval()
+            swin = tv_models.swin_t(weights=tv_models.Swin_T_Weights.IMAGENET1K_V1).eval()
+        except Exception as e:  # offline box
+            raise SystemExit(f"could not load the pretrained torchvision checkpoints ({e}); use --weights random")
+    return vit.to(device), swin.to(device)
+
+
 def iter_images(image_dir: Path):
     exts = (".jpg", ".jpeg", ".png", ".bmp")
     for path in sorted(image_dir.iterdir()):
@@ -76,7 +96,9 @@ def main(argv=None) -> None:
     device = torch.device("cuda")
     set_default_precision(args.precision)
     src, vgg = load_models(args.weights, args.seed, device)
-    source, target = native_model(src), NativeVGG19(vgg)
+    vit, swin = load_transformers(args.weights, args.seed, device)
+    source = native_model(src)
+    targets = {"VGG19": NativeVGG19(vgg), "ViT": NativeViTB16(vit), "Swin": NativeSwinT(swin)}
     mean = torch.tensor([0.485, 0.456, 0.406], device=device)
     std = torch.tensor([0.229, 0.224, 0.225], device=device)
 
@@ -93,7 +115,7 @@ def main(argv=None) -> None:
             raise SystemExit(f"No image files found in directory: {image_dir}")
         images = torch.stack(xs)
 
-    stats = {a: {"success": 0, "total": 0} for a in ("fgsm", "pgd", "cw")}
+    stats = {a: {t: {"success": 0, "total": 0} for t in targets} for a in ("fgsm", "pgd", "cw")}
     for lo in range(0, images.shape[0], int(args.batch)):
         x = images[lo:lo + int(args.batch)]
         y_source = source.forward(x, mean, std, want_logits=False, want_preds=True)["preds"]
@@ -107,16 +129,19 @@ def main(argv=None) -> None:
                 x_adv = cw_l2_attack(source, x, y_source, mean=mean, std=std, c=float(args.cw_c),
                                      kappa=float(args.cw_kappa), steps=int(args.cw_steps), lr=float(args.cw_lr),
                                      targeted=False, y_target=None).x_adv
-            s, t = transfer_counts(target, x, x_adv, mean, std)
-            stats[name]["success"] += s
-            stats[name]["total"] += t
+            for tname, target in targets.items():
+                s, t = transfer_counts(target, x, x_adv, mean, std)
+                stats[name][tname]["success"] += s
+                stats[name][tname]["total"] += t
 
     # blackbox_transfer.py:316-340 — rows = attacks, columns = target models
     print("\t".join(["Attack/Model", "VGG19", "ViT", "Swin"]))
     for name in ("fgsm", "pgd", "cw"):
-        total, success = stats[name]["total"], stats[name]["success"]
-        asr = 0.0 if total == 0 else 100.0 * success / total
-        print("\t".join([name.upper(), f"{asr:.1f}%", "n/a", "n/a"]))
+        row = [name.upper()]
+        for tname in ("VGG19", "ViT", "Swin"):
+            total, success = stats[name][tname]["total"], stats[name][tname]["success"]
+            row.append(f"{0.0 if total == 0 else 100.0 * success / total:.1f}%")
+        print("\t".join(row))
 
 
 if __name__ == "__main__":

@@ -703,6 +703,13 @@ struct advb200_model {
   std::map<std::string, std::vector<TileForce>> tune_cache;
   double tune_ms = 0;           // wall time spent tuning (reported by advb200_tune_report)
   int tuned_ops = 0;
+  // captured attack steps (advb200_pgd_steps): one CUDA graph per distinct argument set, replayed once per step
+  struct StepGraph {
+    const void *x_adv, *x_orig, *mean3, *std3, *y, *grad, *ws;
+    int n; float inv_n, alpha, eps;
+    cudaGraphExec_t exec; long long launches;
+  };
+  std::vector<StepGraph> step_graphs;
 };
 
 namespace advb200 {
@@ -1191,6 +1198,8 @@ int ensure_plan(advb200_model* m, int n, void* ws, int64_t ws_bytes, cudaStream_
   const int64_t need = plan(m, n, nullptr, nullptr);
   if (ws_bytes < need) return fail(ADVB200_ERR_ARG, "workspace too small: need " + std::to_string(need));
   int rc = ADVB200_OK;
+  for (auto& g : m->step_graphs) cudaGraphExecDestroy(g.exec);     // captured steps refer to the previous plan's launches
+  m->step_graphs.clear();
   plan(m, n, ws, &rc, st, true);
   m->fwd_state_n = -1;
   if (rc) { m->plan_n = -1; return rc; }
@@ -1368,6 +1377,7 @@ int64_t advb200_profile_dump(char* buf_host, int64_t cap) {
 
 int advb200_model_destroy(advb200_model* m) {
   if (!m) return ADVB200_OK;
+  for (auto& g : m->step_graphs) cudaGraphExecDestroy(g.exec);
   for (void* p : m->owned) cudaFree(p);
   delete m;
   return ADVB200_OK;
@@ -1439,6 +1449,73 @@ int advb200_attack_step(advb200_model* m, float* x_adv_inout, const float* x_ori
   return input_grad_impl(m, x_adv_inout, mean3, std3, y_true, n, ADVB200_LOSS_CE_MEAN, 0.f, 0.f, inv_n_global, nullptr,
                          preds_out, nullptr, nullptr, nullptr, x_adv_inout, x_orig, alpha, eps, workspace,
                          workspace_bytes, stream);
+}
+
+// `steps` iterations of  x_adv <- clamp(project(x_adv + alpha * sign(grad CE(x_adv))))  (attack.py:55-63; x_orig == NULL:
+// no projection).  With use_graph the kernel sequence of ONE iteration (~105 launches) is captured once per argument set
+// into a CUDA graph and replayed `steps` times: one host call per iteration instead of ~105, so the launch stream never
+// depends on the host keeping ahead (eight ranks sharing one host do not always).  Same kernels, same order, same bits.
+int advb200_pgd_steps(advb200_model* m, float* x_adv_inout, const float* x_orig, const float* mean3, const float* std3,
+                      const int64_t* y_true, int n, float inv_n_global, float alpha, float eps, int steps,
+                      float* grad_scratch, void* workspace, int64_t workspace_bytes, int use_graph, void* stream) {
+  ADV_CHECK_ARG(m && x_adv_inout && mean3 && std3 && y_true && grad_scratch && workspace, "pgd_steps: null argument");
+  ADV_CHECK_ARG(steps >= 0, "pgd_steps: negative step count");
+  cudaStream_t st = as_stream(stream);
+  const int64_t elems = (int64_t)n * 3 * kImg * kImg;
+  auto one_step = [&]() -> int {
+    int rc = input_grad_impl(m, x_adv_inout, mean3, std3, y_true, n, ADVB200_LOSS_CE_MEAN, 0.f, 0.f, inv_n_global, nullptr,
+                             nullptr, nullptr, nullptr, grad_scratch, nullptr, nullptr, 0.f, 0.f, workspace, workspace_bytes, stream);
+    if (rc) return rc;
+    return advb200_linf_step_f32(x_adv_inout, x_orig, grad_scratch, alpha, eps, elems, x_orig != nullptr, stream);
+  };
+  static const bool graphs_off = getenv("ADVB200_NO_GRAPH") != nullptr;
+  if (!use_graph || graphs_off || g_prof_on || g_trace_buf || steps == 0) {
+    for (int s = 0; s < steps; ++s) {
+      const int rc = one_step();
+      if (rc) return rc;
+    }
+    return ADVB200_OK;
+  }
+  // the plan (and its one-off autotuning, which allocates and synchronises) must exist before the capture starts
+  int rc = ensure_plan(m, n, workspace, workspace_bytes, st);
+  if (rc) return rc;
+  advb200_model::StepGraph* hit = nullptr;
+  for (auto& g : m->step_graphs)
+    if (g.x_adv == x_adv_inout && g.x_orig == x_orig && g.mean3 == mean3 && g.std3 == std3 && g.y == y_true &&
+        g.grad == grad_scratch && g.ws == workspace && g.n == n && g.inv_n == inv_n_global && g.alpha == alpha && g.eps == eps)
+      hit = &g;
+  if (!hit) {
+    const long long l0 = g_launches.load();
+    cudaGraph_t graph = nullptr;
+    if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+      cudaGetLastError();
+      for (int s = 0; s < steps; ++s) if ((rc = one_step())) return rc;      // capture unavailable: plain launches
+      return ADVB200_OK;
+    }
+    rc = one_step();
+    const cudaError_t ce = cudaStreamEndCapture(st, &graph);
+    if (rc || ce != cudaSuccess || !graph) {
+      if (graph) cudaGraphDestroy(graph);
+      cudaGetLastError();
+      if (rc) return rc;
+      return fail(ADVB200_ERR_CUDA, std::string("pgd_steps: stream capture failed: ") + cudaGetErrorString(ce));
+    }
+    advb200_model::StepGraph g{x_adv_inout, x_orig, mean3, std3, y_true, grad_scratch, workspace, n, inv_n_global, alpha, eps,
+                               nullptr, g_launches.load() - l0};
+    g_launches.store(l0);                     // nothing ran during the capture; replays are counted below
+    const cudaError_t ie = cudaGraphInstantiate(&g.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ie != cudaSuccess) { cudaGetLastError(); return fail(ADVB200_ERR_CUDA, std::string("pgd_steps: cudaGraphInstantiate: ") + cudaGetErrorString(ie)); }
+    if (m->step_graphs.size() >= 8) { cudaGraphExecDestroy(m->step_graphs.front().exec); m->step_graphs.erase(m->step_graphs.begin()); }
+    m->step_graphs.push_back(g);
+    hit = &m->step_graphs.back();
+  }
+  for (int s = 0; s < steps; ++s) {
+    ADV_CHECK_CUDA(cudaGraphLaunch(hit->exec, st));
+    g_launches.fetch_add(hit->launches);
+  }
+  m->fwd_state_n = -1;
+  return ADVB200_OK;
 }
 
 static int input_grad_impl(advb200_model* m, const float* x, const float* mean3, const float* std3,
@@ -1650,6 +1727,88 @@ int advb200_vgg19_forward(advb200_vgg19* m, const float* x, const float* mean3, 
   if ((rc = launch_bf16_cols_to_f32(m->logits_bf16, kVggClassesPad, logits_out, n, kClasses, st))) return rc;
   if (preds_out) rc = launch_argmax(logits_out, n, kClasses, preds_out, st);
   return rc;
+}
+
+// ================================================================================================================
+// Linear layers of the transformer transfer targets (ViT-B/16, Swin-T: blackbox_transfer.py:36-54) on the tcgen05
+// conv kernel: y[m, cout] = x[m, cin] W^T + b (+ residual) is a pointwise conv over m "pixels".  Channel counts are
+// padded to multiples of 64 at pack time (zero weights / zero bias), so padded output channels come out as exact zeros.
+// ================================================================================================================
+struct advb200_linear {
+  int cin = 0, cout = 0, cin_pad = 0, cout_pad = 0;
+  bf16* w = nullptr;       // [cout_pad][cin_pad], K-major
+  float* b = nullptr;      // [cout_pad]
+  std::vector<void*> owned;
+  struct Built { const void* x; void* y; const void* add; long long m; int relu; std::vector<Op> ops; };
+  std::vector<Built> built;     // launch descriptors (TMA tensor maps) per distinct argument set
+};
+
+int advb200_linear_create(const float* w, const float* bias, int cin, int cout, int cin_pad, int cout_pad, void* stream,
+                          advb200_linear** out) {
+  ADV_CHECK_ARG(w && out, "linear_create: null argument");
+  ADV_CHECK_ARG(cin > 0 && cout > 0 && cin_pad >= cin && cout_pad >= cout && cin_pad % 64 == 0 && cout_pad % 64 == 0,
+                "linear_create: padded channel counts must be multiples of 64 and cover the real ones");
+  cudaStream_t st = as_stream(stream);
+  advb200_linear* l = new advb200_linear();
+  l->cin = cin; l->cout = cout; l->cin_pad = cin_pad; l->cout_pad = cout_pad;
+  auto dalloc = [&](size_t bytes) -> void* {
+    void* p = nullptr;
+    if (cudaMalloc(&p, bytes) != cudaSuccess) return nullptr;
+    l->owned.push_back(p);
+    return p;
+  };
+  int rc = ADVB200_OK;
+  float* tmp = (float*)dalloc((size_t)cout * cin_pad * 4);
+  l->w = (bf16*)dalloc((size_t)cout_pad * cin_pad * 2);
+  l->b = (float*)dalloc((size_t)cout_pad * 4);
+  if (!tmp || !l->w || !l->b) rc = fail(ADVB200_ERR_CUDA, "linear_create: cudaMalloc failed");
+  if (!rc) rc = launch_pad_cin(w, tmp, cout, cin, cin_pad, 1, st);
+  if (!rc) rc = launch_pack_fc_bf16(tmp, l->w, cout, cout_pad, cin_pad, 1, st);
+  if (!rc) {
+    if (bias) rc = launch_pad_vec(bias, l->b, cout, cout_pad, st);
+    else if (cudaMemsetAsync(l->b, 0, (size_t)cout_pad * 4, st) != cudaSuccess) rc = fail(ADVB200_ERR_CUDA, "linear_create: memset failed");
+  }
+  if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = fail(ADVB200_ERR_CUDA, "linear_create: packing failed");
+  if (rc) { for (void* p : l->owned) cudaFree(p); delete l; return rc; }
+  *out = l;
+  return ADVB200_OK;
+}
+
+int advb200_linear_destroy(advb200_linear* l) {
+  if (!l) return ADVB200_OK;
+  for (void* p : l->owned) cudaFree(p);
+  delete l;
+  return ADVB200_OK;
+}
+
+int advb200_linear_forward(advb200_linear* l, const void* x, void* y, int64_t m, int relu, const void* add, void* stream) {
+  ADV_CHECK_ARG(l && x && y, "linear_forward: null argument");
+  ADV_CHECK_ARG(m >= 0 && m < (1ll << 31), "linear_forward: bad row count");
+  if (m == 0) return ADVB200_OK;
+  advb200_linear::Built* hit = nullptr;
+  for (auto& b : l->built)
+    if (b.x == x && b.y == y && b.add == add && b.m == m && b.relu == relu) hit = &b;
+  if (!hit) {
+    advb200_linear::Built b{x, y, add, m, relu, {}};
+    Act in{const_cast<void*>(x), 1, (int)m, 1, l->cin_pad}, out{y, 1, (int)m, 1, l->cout_pad};
+    g_label = "linear";
+    g_force = TileForce{};
+    const int rc = build_tc_ops(b.ops, l->w, 1, 1, false, in, out, l->b, reinterpret_cast<const bf16*>(add), nullptr, relu ? 1 : 0);
+    if (rc) return rc;
+    if (l->built.size() >= 16) l->built.erase(l->built.begin());
+    l->built.push_back(std::move(b));
+    hit = &l->built.back();
+  }
+  return run_ops(hit->ops, as_stream(stream));
+}
+
+// fp32 classifier head: logits[n, classes] = feat[n, k] W^T + b (W [classes, k]); scratch of advb200_fc_scratch_bytes(n, classes)
+int64_t advb200_fc_scratch_bytes(int n, int classes) { return n > 0 && classes > 0 ? fc_nt_partial_bytes(n, classes) : 0; }
+int advb200_fc_f32(const float* feat, const float* w, const float* bias, float* logits, float* scratch, int n, int classes, int k,
+                   void* stream) {
+  ADV_CHECK_ARG(feat && w && logits && scratch && n >= 0 && classes > 0 && k > 0, "fc: bad argument");
+  if (n == 0) return ADVB200_OK;
+  return launch_fc_nt(feat, w, bias, logits, scratch, n, classes, k, as_stream(stream));
 }
 
 int advb200_debug_trace(void* buf, int64_t cap_bytes) {

@@ -128,6 +128,16 @@ int advb200_attack_step(advb200_model* m, float* x_adv_inout, const float* x_ori
                         const float* std3, const int64_t* y_true, int n, float inv_n_global, float alpha,
                         float eps, int64_t* preds_out, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* The PGD loop body, `steps` times (attack.py:55-63):  x_adv <- clamp(project(x_adv + alpha*sign(grad CE(x_adv)))),
+ * in place; x_orig == NULL drops the projection (attack.py:33-34).  grad_scratch: fp32 [N,3,224,224] caller-owned.
+ * use_graph != 0: the ~105 kernel launches of one iteration are captured ONCE per argument set (pointers, n, scalars)
+ * into a CUDA graph and replayed per step — one host call per iteration; same kernels in the same order, bit-identical
+ * to advb200_input_grad + advb200_linf_step_f32.  Captured graphs are dropped when the model is re-planned for
+ * another batch size / workspace. */
+int advb200_pgd_steps(advb200_model* m, float* x_adv_inout, const float* x_orig, const float* mean3, const float* std3,
+                      const int64_t* y_true, int n, float inv_n_global, float alpha, float eps, int steps,
+                      float* grad_scratch, void* workspace, int64_t workspace_bytes, int use_graph, void* stream);
+
 /* One CW iteration after advb200_input_grad(CW_*) produced grad_x and success for the current
  * x_adv (attack.py:126-137 + torch.optim.Adam single-tensor update):
  *   l2_n = sum(l2_partials_in[n,:])                     (distance of the CURRENT x_adv)
@@ -230,6 +240,51 @@ int advb200_test_conv(int precision, const void* x, const float* wgt, const floa
  * heuristic) of the following advb200_test_conv calls — the candidates the plan-time autotuner chooses between;
  * the parity tests check that every candidate gives bit-identical results. */
 int advb200_test_force_tile(int bn, int pair, int bres, int slots);
+
+/* ------------------------------------------------------------------------------------------
+ * Building blocks of the transformer transfer targets — ViT-B/16 and Swin-T, forward only
+ * (blackbox_transfer.py:36-54 load_vit / load_swin; :233-251 predict_model on the adversarial examples).
+ * The Python mirror (advb200/transformers.py) composes them exactly as torchvision composes its modules.
+ * Token matrices are [tokens, channels] row-major; bf16 unless the name says f32; channel counts seen by the GEMM kernel
+ * are padded to multiples of 64 (zero weights, zero bias, padded activations exactly zero).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct advb200_linear advb200_linear;
+/* nn.Linear(cin, cout) packed for the tcgen05 kernel: w fp32 [cout, cin], bias fp32 [cout] or NULL */
+int advb200_linear_create(const float* w, const float* bias, int cin, int cout, int cin_pad, int cout_pad, void* stream,
+                          advb200_linear** out);
+int advb200_linear_destroy(advb200_linear* l);
+/* y[m, cout_pad] = x[m, cin_pad] W^T + b (+ add[m, cout_pad]), optional ReLU; bf16 in / out, fp32 accumulation */
+int advb200_linear_forward(advb200_linear* l, const void* x, void* y, int64_t m, int relu, const void* add, void* stream);
+/* fp32 classifier head (model.heads / model.head): logits = feat W^T + b; scratch of advb200_fc_scratch_bytes(n, classes) bytes */
+int64_t advb200_fc_scratch_bytes(int n, int classes);
+int advb200_fc_f32(const float* feat, const float* w, const float* bias, float* logits, float* scratch, int n, int classes, int k,
+                   void* stream);
+/* conv_proj / patch embedding operand: normalised image (attack.py:17) -> bf16 [N*(h/patch)*(w/patch), kpad], column
+ * (c*patch + i)*patch + j = the flatten order of the Conv2d weight; columns >= 3*patch*patch are zero */
+int advb200_patch_im2col_bf16(const float* x, const float* mean3, const float* std3, void* out, int n, int h, int w, int patch,
+                              int kpad, void* stream);
+/* ViT: x32[n,0,:] = class_token + pos[0]; x32[n,1+p,:] = patch[n,p,:] + pos[1+p]   (fp32 residual stream) */
+int advb200_vit_tokens_f32(const void* patch_bf16, const float* cls, const float* pos, float* x32, int n, int tokens, int c,
+                           void* stream);
+/* residual stream update fused with LayerNorm: mode 0: x32 unchanged, 1: x32 += delta, 2: x32 = delta (delta bf16
+ * [m, c_pad]); y (bf16 [m, c_pad], may be NULL) = LayerNorm over the c_real real channels (<= 1536), pad = 0 */
+int advb200_add_layernorm(float* x32, const void* delta_bf16, const float* gamma, const float* beta, float eps, void* y_bf16,
+                          int64_t m, int c_real, int c_pad, int mode, void* stream);
+/* exact (erf) GELU, bf16 -> bf16, n % 8 == 0 */
+int advb200_gelu_bf16(const void* x, void* y, int64_t n, void* stream);
+/* multi-head attention, one window per CTA and head: softmax(q k^T * scale + bias + region mask) v.
+ * grid_h == 0: the window is the image's whole sequence of tokens_per_window tokens (ViT).  Otherwise window x window
+ * windows of a grid_h x grid_w token grid cyclically shifted by `shift` (Swin shifted-window attention, with the
+ * region mask of torchvision's implementation when shift > 0); bias fp32 [heads, T, T] (relative-position bias) or NULL.
+ * q / k / v are column blocks of `qkv` at q_off / k_off / v_off (+ head * dim); out[row, head*dim + d]. */
+int advb200_window_attention_bf16(const void* qkv, void* out, const float* bias, int n_img, int tokens_per_window, int heads, int dim,
+                                  int ld_qkv, int ld_out, int q_off, int k_off, int v_off, int grid_h, int grid_w, int window,
+                                  int shift, float scale, void* stream);
+/* Swin PatchMerging input: concat of the four 2x2 neighbours (x0, x1, x2, x3 of torchvision) of the fp32 stream */
+int advb200_patch_merge_gather_f32(const float* x32, float* out, int n, int grid_h, int grid_w, int c_real, int c_pad, void* stream);
+/* head features: mean over `count` tokens from t0 of LayerNorm(x32[n, t, :]) -> fp32 [n, c_real] (ViT: the class token) */
+int advb200_ln_pool_f32(const float* x32, const float* gamma, const float* beta, float eps, float* feat, int n, int tokens, int t0,
+                        int count, int c_real, int c_pad, void* stream);
 
 /* Test hook: in-situ trace of a forward / input-gradient pass.  While a device buffer is set, every tensor the passes
  * write — each conv launch's output as the plan really runs it (fused launches, multi-class stride-2 input gradients),

@@ -214,3 +214,33 @@ def test_median_and_smoothing_with_a_misaligned_output_plane():
     _lib.check(lib.advb200_defend_input_f32(_lib.ptr(xd), _lib.ptr(out), 6, 8, 8, 16, _lib.stream_ptr()), "defend")
     assert np.array_equal(out.cpu().numpy(), defenses_ref.defend_input(x.numpy()))
     torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("precision", ["bf16", "fp32"])
+def test_native_graph_loop_equals_python_loop(precision):
+    """advb200_pgd_steps (captured CUDA graph replayed per step; plain native loop) == the Python loop over
+    advb200_input_grad + advb200_linf_step_f32, bit for bit, for a full chunk, a tail chunk and a repeated call."""
+    import advb200
+    from advb200 import attack as A
+    dev = torch.device("cuda:0")
+    nm = advb200.NativeResNet50(weights.conditioned_resnet50(0).to(dev), precision=precision)
+    nm.max_chunk = 4
+    mean, std = weights.mean_std()
+    x = weights.mixed_images(6, seed=5).to(dev)                    # chunks of 4 + 2
+    y = nm.forward(x, mean, std, want_preds=True)["preds"]
+    eps = 4 / 255
+    noise = weights.pgd_noise(x.shape, eps, 3).to(dev)
+    kw = dict(eps=eps, alpha=2 / 255, steps=3, mean=mean, std=std, noise=noise)
+    outs = {}
+    for mode, (native, graph) in {"python": (False, False), "native": (True, False), "graph": (True, True)}.items():
+        A._NATIVE_LOOP, A._USE_GRAPH = native, graph
+        try:
+            outs[mode] = advb200.pgd_linf_attack(nm, x, y, **kw)
+            if mode == "graph":
+                again = advb200.pgd_linf_attack(nm, x, y, **kw)      # second call replays the cached graphs
+                assert torch.equal(again, outs[mode])
+        finally:
+            A._NATIVE_LOOP, A._USE_GRAPH = True, True
+    assert torch.equal(outs["native"], outs["python"]) and torch.equal(outs["graph"], outs["python"])
+    assert not torch.equal(outs["python"], x)
+    assert bool(((outs["graph"] <= x + eps) & (outs["graph"] >= x - eps)).all())

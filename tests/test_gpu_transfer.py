@@ -83,7 +83,9 @@ def test_blackbox_transfer_cli_table(capsys):
     lines = capsys.readouterr().out.strip().splitlines()
     assert lines[0] == "Attack/Model\tVGG19\tViT\tSwin"
     assert [l.split("\t")[0] for l in lines[1:]] == ["FGSM", "PGD", "CW"]
-    assert lines[3] == "CW\t0.0%\tn/a\tn/a"                       # not requested: 0 of 0, as in the reference
+    assert lines[3] == "CW\t0.0%\t0.0%\t0.0%"                   # not requested: 0 of 0, as in the reference
+    for l in lines[1:3]:
+        assert all(c.endswith("%") for c in l.split("\t")[1:])     # all three target columns are filled
 
     dev = torch.device("cuda")
     src, vgg_m = cli.load_models("random", 0, dev)
