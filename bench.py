@@ -223,10 +223,16 @@ def main():
     l0 = _lib.launch_count()
     adist.barrier(); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    prof_range = bool(os.environ.get("ADVB200_BENCH_PROFILE_RANGE"))    # ncu --profile-from-start off: only the timed steps
+    if prof_range:
+        torch.cuda.profiler.start()
     e0.record()
     for _ in range(args.steps):
         xa = attack(x)
     e1.record()
+    if prof_range:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
     torch.cuda.synchronize(); adist.barrier()
     ms = adist.max_over_ranks(e0.elapsed_time(e1), device=dev)
     launches = _lib.launch_count() - l0

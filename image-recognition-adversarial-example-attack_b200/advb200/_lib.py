@@ -76,6 +76,7 @@ SIGNATURES = {
                                       c_void_p]),
     "advb200_gelu_bf16": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "advb200_window_attention_bf16": (c_int, [c_void_p, c_void_p, c_void_p] + [c_int] * 13 + [c_float, c_void_p]),
+    "advb200_test_attention_simt": (c_int, [c_int]),
     "advb200_patch_merge_gather_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "advb200_ln_pool_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                     c_void_p]),

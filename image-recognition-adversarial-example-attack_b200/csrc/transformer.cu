@@ -8,6 +8,8 @@
 // patch merging and the pooled head features.  Tokens are rows of [tokens, channels] matrices (channels padded to a
 // multiple of 64 for the GEMM kernel; padded channels are kept at exactly zero).  The residual stream stays in fp32 so
 // twelve layers of residual adds do not accumulate bf16 rounding; GEMM operands and outputs are bf16.
+#include <cstdlib>
+
 #include "layers.cuh"
 
 namespace advb200 {
@@ -143,6 +145,7 @@ __device__ __forceinline__ long long attn_row(const AttnParams& p, long long img
 
 constexpr int kAttnWarps = 8;
 constexpr int kAttnMaxKeysPerLane = 7;          // T <= 224
+bool g_attn_force_simt = false;                 // test hook (advb200_test_attention_simt)
 
 __global__ void __launch_bounds__(kAttnWarps * 32)
 window_attention_kernel(const AttnParams p) {
@@ -223,6 +226,164 @@ window_attention_kernel(const AttnParams p) {
     if (lane + 32 < D) dst[lane + 32] = __float2bfloat16_rn(o1);
     __syncwarp();
   }
+}
+
+// ---- the same attention on the tensor cores (warp-level mma.sync m16n8k16, bf16 operands, fp32 accumulation).
+//      One CTA per (image, window, head); Q, K [token][dim] and V transposed [dim][token] sit in shared memory as bf16
+//      with row pitches (dim + 8, tokens + 8) that make every fragment load conflict-free.  A warp owns 16 query rows at
+//      a time: S = Q K^T (kTP / 8 n-tiles x kD / 16 k-steps) stays in registers, bias / region mask / padding mask are
+//      applied per accumulator element, the softmax runs on the registers (a row lives in the four lanes of a quad), the
+//      un-normalised probabilities are packed to bf16 A fragments in place (the accumulator layout of two neighbouring
+//      n-tiles IS the A layout of one k-step) and O = P V is divided by the row sum at the end.
+//      kTP = tokens padded to a multiple of 16 (208 for ViT's 197, 64 for Swin's 49), kD = head dim (64 / 32).
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&v);
+}
+
+template <int kTP, int kD, int kWarps>
+__global__ void __launch_bounds__(kWarps * 32)
+window_attention_mma_kernel(const AttnParams p) {
+  constexpr int kQP = kD + 8;            // pitch (bf16 elements) of the Q / K rows
+  constexpr int kVP = kTP + 8;           // pitch of the transposed V rows
+  constexpr int kNT = kTP / 8;           // score n-tiles (8 keys each)
+  constexpr int kKS = kD / 16;           // k-steps of Q K^T
+  constexpr int kDT = kD / 8;            // output n-tiles (8 dims each)
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  bf16* Qs = reinterpret_cast<bf16*>(smem_raw);          // [kTP][kQP]
+  bf16* Ks = Qs + kTP * kQP;                              // [kTP][kQP]
+  bf16* Vt = Ks + kTP * kQP;                              // [kD][kVP]
+  int* Rg = reinterpret_cast<int*>(Vt + kD * kVP);        // [kTP] region ids
+  const int T = p.T;
+  const int head = blockIdx.x % p.heads;
+  const int win = (blockIdx.x / p.heads) % p.wins_per_img;
+  const long long img = blockIdx.x / (p.heads * p.wins_per_img);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
+
+  // stage Q, K (rows) and V (transposed); padded token rows are zero
+  for (int i = threadIdx.x; i < kTP * (kD / 8); i += kWarps * 32) {
+    const int t = i / (kD / 8), c8 = (i % (kD / 8)) * 8;
+    uint4 q = make_uint4(0u, 0u, 0u, 0u), k = q, v = q;
+    if (t < T) {
+      const long long row = attn_row(p, img, win, t, nullptr);
+      const bf16* src = p.qkv + row * p.ld_qkv + head * kD + c8;
+      q = *reinterpret_cast<const uint4*>(src + p.q_off);
+      k = *reinterpret_cast<const uint4*>(src + p.k_off);
+      v = *reinterpret_cast<const uint4*>(src + p.v_off);
+    }
+    *reinterpret_cast<uint4*>(Qs + t * kQP + c8) = q;
+    *reinterpret_cast<uint4*>(Ks + t * kQP + c8) = k;
+    const bf16* vh = reinterpret_cast<const bf16*>(&v);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) Vt[(c8 + e) * kVP + t] = vh[e];
+  }
+  for (int t = threadIdx.x; t < kTP; t += kWarps * 32) {
+    int r = -1;
+    if (t < T) attn_row(p, img, win, t, &r);
+    Rg[t] = r;
+  }
+  __syncthreads();
+
+  for (int rt = warp; rt < kTP / 16; rt += kWarps) {
+    const int r0 = rt * 16;
+    uint32_t a[kKS][4];
+#pragma unroll
+    for (int ks = 0; ks < kKS; ++ks) {
+      const bf16* q0 = Qs + (r0 + g) * kQP + ks * 16 + 2 * t4;
+      a[ks][0] = *reinterpret_cast<const uint32_t*>(q0);
+      a[ks][1] = *reinterpret_cast<const uint32_t*>(q0 + 8 * kQP);
+      a[ks][2] = *reinterpret_cast<const uint32_t*>(q0 + 8);
+      a[ks][3] = *reinterpret_cast<const uint32_t*>(q0 + 8 * kQP + 8);
+    }
+    float s[kNT][4];
+#pragma unroll
+    for (int nt = 0; nt < kNT; ++nt) {
+      s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < kKS; ++ks) {
+        const bf16* k0 = Ks + (nt * 8 + g) * kQP + ks * 16 + 2 * t4;
+        mma_bf16_16816(s[nt], a[ks], *reinterpret_cast<const uint32_t*>(k0), *reinterpret_cast<const uint32_t*>(k0 + 8));
+      }
+    }
+    // scale, relative-position bias, region mask, padding mask; row maxima (rows r0+g and r0+g+8)
+    const int qa = r0 + g, qb = r0 + g + 8;
+    const int rga = Rg[qa], rgb = Rg[qb];
+    float ma = -INFINITY, mb = -INFINITY;
+#pragma unroll
+    for (int nt = 0; nt < kNT; ++nt) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int col = nt * 8 + 2 * t4 + e;
+        const bool valid = col < T;
+        float va = s[nt][e] * p.scale, vb = s[nt][2 + e] * p.scale;
+        if (valid && p.bias) {
+          if (qa < T) va += __ldg(p.bias + ((long long)head * T + qa) * T + col);
+          if (qb < T) vb += __ldg(p.bias + ((long long)head * T + qb) * T + col);
+        }
+        const int rc = Rg[col];
+        if (valid && rc != rga) va += -100.0f;
+        if (valid && rc != rgb) vb += -100.0f;
+        va = valid ? va : -INFINITY; vb = valid ? vb : -INFINITY;
+        s[nt][e] = va; s[nt][2 + e] = vb;
+        ma = fmaxf(ma, va); mb = fmaxf(mb, vb);
+      }
+    }
+    ma = fmaxf(ma, __shfl_xor_sync(0xffffffffu, ma, 1)); ma = fmaxf(ma, __shfl_xor_sync(0xffffffffu, ma, 2));
+    mb = fmaxf(mb, __shfl_xor_sync(0xffffffffu, mb, 1)); mb = fmaxf(mb, __shfl_xor_sync(0xffffffffu, mb, 2));
+    float suma = 0.f, sumb = 0.f;
+#pragma unroll
+    for (int nt = 0; nt < kNT; ++nt) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        s[nt][e] = expf(s[nt][e] - ma); suma += s[nt][e];               // exp(-inf) = 0 for the padded keys
+        s[nt][2 + e] = expf(s[nt][2 + e] - mb); sumb += s[nt][2 + e];
+      }
+    }
+    suma += __shfl_xor_sync(0xffffffffu, suma, 1); suma += __shfl_xor_sync(0xffffffffu, suma, 2);
+    sumb += __shfl_xor_sync(0xffffffffu, sumb, 1); sumb += __shfl_xor_sync(0xffffffffu, sumb, 2);
+    // O = P V
+    float o[kDT][4];
+#pragma unroll
+    for (int dt = 0; dt < kDT; ++dt) o[dt][0] = o[dt][1] = o[dt][2] = o[dt][3] = 0.f;
+#pragma unroll
+    for (int kk = 0; kk < kTP / 16; ++kk) {
+      uint32_t pa[4];
+      pa[0] = pack_bf16x2(s[2 * kk][0], s[2 * kk][1]);
+      pa[1] = pack_bf16x2(s[2 * kk][2], s[2 * kk][3]);
+      pa[2] = pack_bf16x2(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+      pa[3] = pack_bf16x2(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+#pragma unroll
+      for (int dt = 0; dt < kDT; ++dt) {
+        const bf16* v0 = Vt + (dt * 8 + g) * kVP + kk * 16 + 2 * t4;
+        mma_bf16_16816(o[dt], pa, *reinterpret_cast<const uint32_t*>(v0), *reinterpret_cast<const uint32_t*>(v0 + 8));
+      }
+    }
+    const float inva = 1.0f / suma, invb = 1.0f / sumb;
+    if (qa < T) {
+      bf16* dst = p.out + attn_row(p, img, win, qa, nullptr) * p.ld_out + head * kD + 2 * t4;
+#pragma unroll
+      for (int dt = 0; dt < kDT; ++dt) *reinterpret_cast<uint32_t*>(dst + dt * 8) = pack_bf16x2(o[dt][0] * inva, o[dt][1] * inva);
+    }
+    if (qb < T) {
+      bf16* dst = p.out + attn_row(p, img, win, qb, nullptr) * p.ld_out + head * kD + 2 * t4;
+#pragma unroll
+      for (int dt = 0; dt < kDT; ++dt) *reinterpret_cast<uint32_t*>(dst + dt * 8) = pack_bf16x2(o[dt][2] * invb, o[dt][3] * invb);
+    }
+  }
+}
+
+template <int kTP, int kD, int kWarps>
+int launch_attention_mma(const AttnParams& p, long long ctas, cudaStream_t st) {
+  constexpr size_t smem = (size_t)(2 * kTP * (kD + 8) + kD * (kTP + 8)) * 2 + (size_t)kTP * 4;
+  ADV_CHECK_CUDA(cudaFuncSetAttribute(window_attention_mma_kernel<kTP, kD, kWarps>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  window_attention_mma_kernel<kTP, kD, kWarps><<<(unsigned)ctas, kWarps * 32, smem, st>>>(p);
+  ADV_LAUNCHED();
+  return ADVB200_OK;
 }
 
 // ---- Swin patch merging input: fp32 stream [N, gh, gw, c_pad] -> concat of the four 2x2 neighbours
@@ -359,8 +520,23 @@ int advb200_window_attention_bf16(const void* qkv, void* out, const float* bias,
   ADV_CHECK_CUDA(cudaFuncSetAttribute(window_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long ctas = (long long)n_img * p.wins_per_img * heads;
   ADV_CHECK_ARG(ctas < (1ll << 31), "window_attention: too many windows for one launch");
+  // tensor-core path for the two shapes of the transfer targets (16-byte aligned rows); anything else, or
+  // ADVB200_ATTN_SIMT=1, takes the CUDA-core kernel (the cross-check of tests/test_gpu_transformers.py)
+  static const bool simt_only = getenv("ADVB200_ATTN_SIMT") != nullptr;
+  const bool aligned = ((reinterpret_cast<uintptr_t>(qkv) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0 && ld_qkv % 8 == 0 &&
+                       ld_out % 2 == 0 && q_off % 8 == 0 && k_off % 8 == 0 && v_off % 8 == 0;
+  if (!simt_only && !g_attn_force_simt && aligned) {
+    if (T == 197 && D == 64) return launch_attention_mma<208, 64, 8>(p, ctas, as_stream(stream));
+    if (T == 49 && D == 32) return launch_attention_mma<64, 32, 4>(p, ctas, as_stream(stream));
+  }
   window_attention_kernel<<<(unsigned)ctas, kAttnWarps * 32, smem, as_stream(stream)>>>(p);
   ADV_LAUNCHED();
+  return ADVB200_OK;
+}
+
+int advb200_test_attention_simt(int on) {
+  // test hook: route advb200_window_attention_bf16 through the CUDA-core kernel (cross-check of the tensor-core one)
+  g_attn_force_simt = on != 0;
   return ADVB200_OK;
 }
 

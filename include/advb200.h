@@ -280,6 +280,8 @@ int advb200_gelu_bf16(const void* x, void* y, int64_t n, void* stream);
 int advb200_window_attention_bf16(const void* qkv, void* out, const float* bias, int n_img, int tokens_per_window, int heads, int dim,
                                   int ld_qkv, int ld_out, int q_off, int k_off, int v_off, int grid_h, int grid_w, int window,
                                   int shift, float scale, void* stream);
+/* test hook: on != 0 routes advb200_window_attention_bf16 through its CUDA-core kernel instead of the tensor-core one */
+int advb200_test_attention_simt(int on);
 /* Swin PatchMerging input: concat of the four 2x2 neighbours (x0, x1, x2, x3 of torchvision) of the fp32 stream */
 int advb200_patch_merge_gather_f32(const float* x32, float* out, int n, int grid_h, int grid_w, int c_real, int c_pad, void* stream);
 /* head features: mean over `count` tokens from t0 of LayerNorm(x32[n, t, :]) -> fp32 [n, c_real] (ViT: the class token) */

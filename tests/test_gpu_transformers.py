@@ -73,6 +73,18 @@ def test_logits_vs_torchvision_fp32(kind, dev):
     assert torch.equal(one, got[[0, 3]])
     again = nm(attacks_ref.normalize(x[:2], mean.to(dev), std.to(dev)))
     assert float((again - got[:2]).abs().max()) < 2e-2 * float(ref.abs().max())
+    # the tensor-core attention kernel against the CUDA-core one (same arithmetic up to the bf16 rounding of P)
+    from advb200 import _lib
+    _lib.load().advb200_test_attention_simt(1)
+    try:
+        simt = nm.forward(x, mean, std)
+    finally:
+        _lib.load().advb200_test_attention_simt(0)
+    rel_s = float((simt.double() - ref.double()).norm() / ref.double().norm())
+    rel_k = float((simt.double() - got.double()).norm() / got.double().norm())
+    print(f"[{kind}] CUDA-core attention: rel-L2 vs torchvision {rel_s:.2e}; tensor-core vs CUDA-core kernels {rel_k:.2e}")
+    # (two bf16 paths that are each ~8e-3 from the fp32 reference are up to twice that from each other)
+    assert rel_s < 1e-2 and rel_k < 1.5e-2 and not torch.equal(simt, got)
 
 
 def test_error_behaviour(dev):

@@ -138,4 +138,13 @@ vgg = NativeVGG19(torchvision.models.vgg19(weights=None).eval().to(dev))
 xv = x[:128]
 ms = timed(lambda: vgg.forward(xv, mean, std), reps=5, warm=2)
 out["vgg19_forward_batch128"] = {"ms": ms, "images_per_s": 128 / (ms * 1e-3), "tflops": 128 * 2 * 19.63e9 / (ms * 1e-3) / 1e12}
+# transformer transfer targets (forward only): ViT-B/16 (17.56 GFLOP/image nominal: 2 x 8.78 GMAC) and Swin-T (2 x 4.49 GMAC)
+from advb200.transformers import NativeSwinT, NativeViTB16  # noqa: E402
+for name, ctor, cls, gmac in (("vit_b_16", torchvision.models.vit_b_16, NativeViTB16, 17.56 / 2),
+                              ("swin_t", torchvision.models.swin_t, NativeSwinT, 4.49)):
+    torch.manual_seed(4)
+    tm = cls(ctor(weights=None).eval().to(dev))
+    ms = timed(lambda: tm.forward(xv, mean, std), reps=5, warm=2)
+    # share of the attention kernel: time it alone through the same buffers
+    out[name + "_forward_batch128"] = {"ms": ms, "images_per_s": 128 / (ms * 1e-3), "tflops": 128 * 2 * gmac * 1e9 / (ms * 1e-3) / 1e12}
 print(json.dumps(out, indent=1))
