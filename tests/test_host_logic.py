@@ -76,6 +76,42 @@ def test_no_cpu_fallback():
         advb200.defend_input(x)
 
 
+def test_transfer_targets_and_label_checks_without_a_gpu():
+    """The transformer transfer targets have no CPU fallback either; label and noise-shape errors are raised by the host
+    mirror before anything reaches the device."""
+    if torch.cuda.is_available():
+        pytest.skip("checks the no-GPU behaviour")
+    import torchvision
+    from advb200 import attack as A
+    from advb200.transformers import NativeSwinT, NativeViTB16, _pad64
+    vit = torchvision.models.vit_b_16(weights=None).eval()
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        NativeViTB16(vit)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        NativeSwinT(torchvision.models.swin_t(weights=None).eval())
+    assert [_pad64(c) for c in (48, 96, 288, 768, 1536)] == [64, 128, 320, 768, 1536]
+    with pytest.raises(ValueError, match="labels must lie in"):
+        A._check_labels(torch.tensor([0, 1000]), 2)
+    with pytest.raises(ValueError, match="shape"):
+        A._check_labels(torch.tensor([0, 1, 2]), 2)
+    assert A._check_labels(torch.tensor([0, 999]), 2).tolist() == [0, 999]
+
+
+def test_bench_reference_arm_and_shard_seeding():
+    """bench.py: the strong-scaling shards of --config shard8192 tile the 8192 images for every rank count, and the
+    reference arm reports which implementation it times."""
+    import importlib.util
+    from advb200 import dist as adist
+    spec = importlib.util.spec_from_file_location("bench_mod", ROOT / "bench.py")
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    assert bench.REF_KIND in ("reference", "port")
+    assert (bench.REF_KIND == "reference") == (ROOT / "oracle" / "_ref" / "attack.py").is_file()
+    for world in (1, 2, 4, 8):
+        spans = [adist.shard_range(8192, r, world) for r in range(world)]
+        assert all((hi - lo) % 256 == 0 and lo % 256 == 0 for lo, hi in spans) and spans[-1][1] == 8192
+
+
 def test_product_never_imports_the_oracle():
     pkg = ROOT / "image-recognition-adversarial-example-attack_b200"
     for p in pkg.rglob("*.py"):
