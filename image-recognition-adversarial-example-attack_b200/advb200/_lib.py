@@ -38,6 +38,7 @@ SIGNATURES = {
                                    c_int64, c_void_p]),
     "advb200_jpeg_scratch_bytes": (c_int64, [c_int, c_int, c_int]),
     "advb200_jpeg_roundtrip_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p]),
+    "advb200_jpeg_roundtrip_f32_noalloc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "advb200_preprocess_scratch_bytes": (c_int64, [c_int, c_int, c_int, c_int]),
     "advb200_preprocess_u8": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int64, c_void_p]),
     "advb200_to_u8_hwc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),

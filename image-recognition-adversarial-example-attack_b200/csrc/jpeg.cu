@@ -18,6 +18,8 @@
 // algorithmic (24 if the scratch stays in L2, which it does at 224x224: 19 MB per 256 images).
 #include "common.cuh"
 
+#include <mutex>
+
 namespace advb200 {
 namespace {
 
@@ -411,3 +413,55 @@ int advb200_jpeg_roundtrip_f32(const float* x, float* out, int n_img, int h, int
 }
 
 }  // extern "C"
+
+// ---- allocation-free variant ---------------------------------------------------------------------------------------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc): the decoded
+// Y / Cb / Cr planes between the two kernels live in a file-scope device array instead of a caller buffer.  Every GPU
+// that loads the library holds these ADVB200_JPEG_NOALLOC_MAX_BYTES until the process exits.  In host code the array's
+// name is only the host-side handle of the symbol, NOT a device address: the address is looked up once per device,
+// with that device current, by cudaGetSymbolAddress, and that pointer is what the kernels are given.
+namespace advb200 {
+namespace {
+
+static __device__ __align__(256) uint8_t g_jpeg_noalloc_scratch[ADVB200_JPEG_NOALLOC_MAX_BYTES];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[kMaxDevices] = {};     // device address of the array on device i (0 = not looked up yet)
+
+// device address of the scratch array on the CURRENT device; no allocation, one symbol lookup per device
+int noalloc_scratch(void** out) {
+  int dev = -1;
+  ADV_CHECK_CUDA(cudaGetDevice(&dev));
+  ADV_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "jpeg_noalloc: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    void* ptr = nullptr;
+    ADV_CHECK_CUDA(cudaGetSymbolAddress(&ptr, g_jpeg_noalloc_scratch));
+    if (!ptr) return fail(ADVB200_ERR_CUDA, "jpeg_noalloc: cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[dev] = ptr;
+  }
+  *out = g_noalloc_ptr[dev];
+  return ADVB200_OK;
+}
+
+}  // namespace
+}  // namespace advb200
+
+extern "C" int advb200_jpeg_roundtrip_f32_noalloc(const float* x, float* out, int n_img, int h, int w, int quality,
+                                                  void* stream) {
+  ADV_CHECK_ARG(n_img >= 0 && h > 0 && w > 0, "jpeg_noalloc: bad sizes");
+  const int64_t need = advb200_jpeg_scratch_bytes(n_img, h, w);
+  if (need > (int64_t)ADVB200_JPEG_NOALLOC_MAX_BYTES)
+    return fail(ADVB200_ERR_ARG, "jpeg_noalloc: " + std::to_string(n_img) + " x " + std::to_string(h) + " x " +
+                                     std::to_string(w) + " needs " + std::to_string(need) +
+                                     " bytes of scratch, the built-in array holds " +
+                                     std::to_string((long long)ADVB200_JPEG_NOALLOC_MAX_BYTES) +
+                                     "; split the batch or use advb200_jpeg_roundtrip_f32 with a caller buffer");
+  void* scratch = nullptr;
+  const int rc = noalloc_scratch(&scratch);
+  if (rc != ADVB200_OK) return rc;
+  // same two kernels, same launch geometry as the caller-buffer entry point.  Nothing in the array has to start at
+  // zero: every byte jpeg_upsample_rgb_kernel reads was written by jpeg_codec_kernel earlier in this same call.
+  return advb200_jpeg_roundtrip_f32(x, out, n_img, h, w, quality, scratch, (int64_t)ADVB200_JPEG_NOALLOC_MAX_BYTES, stream);
+}

@@ -186,6 +186,20 @@ int64_t advb200_jpeg_scratch_bytes(int n_img, int h, int w);
 int advb200_jpeg_roundtrip_f32(const float* x, float* out, int n_img, int h, int w, int quality, void* scratch,
                                int64_t scratch_bytes, void* stream);
 
+/* Allocation-free variant of advb200_jpeg_roundtrip_f32.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same kernels, same results bit for bit; the uint8 scratch between the two kernels
+ * is a static device array of ADVB200_JPEG_NOALLOC_MAX_BYTES inside the library (every GPU that loads the library
+ * holds it until the process exits) instead of a caller buffer.  The call allocates nothing (no cudaMalloc / cudaFree /
+ * allocating library routine); the first call on each device does one cudaGetSymbolAddress lookup, so make that first
+ * call outside a graph capture.  Sizes with advb200_jpeg_scratch_bytes(n_img,h,w) > ADVB200_JPEG_NOALLOC_MAX_BYTES
+ * (24 MiB: 256 images of 224 x 224, or one image of about 4000 x 4000) return ADVB200_ERR_ARG with the figures in
+ * advb200_last_error().  All calls on one device SHARE the array, which keeps the previous call's bytes (nothing in it
+ * needs to start at zero: every byte read is first written in the same call): two calls that can overlap on the GPU
+ * (different streams without an ordering between them) race on it -- order them, or use the caller-buffer entry. */
+#define ADVB200_JPEG_NOALLOC_MAX_BYTES (24 * 1024 * 1024)
+int advb200_jpeg_roundtrip_f32_noalloc(const float* x, float* out, int n_img, int h, int w, int quality, void* stream);
+
 /* Image preprocessing of `load_image` (ResNet.py:27-31, defense_experiments.py:649-662) for one decoded image:
  * Resize(size) [shorter side -> size; PIL's antialiased bilinear ImagingResample in 22-bit fixed point on uint8] ->
  * CenterCrop(crop) -> ToTensor (/255).  img_hwc: uint8 [h,w,3] on the device; out_chw: fp32 [3,crop,crop].
