@@ -137,19 +137,23 @@ quantize_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n4
 }
 
 // s / 9 with IEEE round-to-nearest, by Markstein's correction instead of the generic division sequence: with
-// y = RN(1/9), q0 = RN(s*y), the remainder r = s - 9*q0 is exact in one FMA and RN(q0 + r*y) is the correctly rounded
-// quotient.  The argument needs no under/overflow in q0 and r, hence the exponent guard (everything else, including
-// inf/nan, takes the generic path; +-0 returns q0 = +-0).  Verified EXHAUSTIVELY over all 2^32 bit patterns against
-// __fdiv_rn on the device (advb200_test_div9, tests/test_gpu_parity.py).
+// y = RN(1/9), q0 = RN(s*y), the remainder r = s - 9*q0 is exact in one FMA (it is a few ulp(q0), and ulp(q0) >= 2^-149
+// whenever q0 != 0) and RN(q0 + r*y) is the correctly rounded quotient -- an FMA rounds once, so neither tiny nor huge
+// finite s needs a guard.  What remains: s = -0 (q1 would come out +0) and s = +-inf / NaN (r = NaN); in all of them r is
+// zero or NaN and q0 is already the answer, so ONE ordered compare selects between q1 and q0 and there is no branch.
+// (Round 1 guarded the exponent range and branched to the generic sequence: a BSSY/BRA/BSYNC region and two FSETPs
+// per output, which also kept ptxas from interleaving the 16 dependent add chains of a strip.)
+// Verified EXHAUSTIVELY over all 2^32 bit patterns: on the device against __fdiv_rn (advb200_test_div9,
+// tests/test_gpu_parity.py) and on the host against IEEE division with C fmaf (oracle/check_div9.c).
 __device__ __forceinline__ float div9(float s) {
   const float y = 0.111111112f;
   const float q0 = __fmul_rn(s, y);
   const float r = __fmaf_rn(-9.0f, q0, s);
   const float q1 = __fmaf_rn(r, y, q0);
-  const float a = fabsf(s);
-  if (a > 1e-30f && a < 1e30f) return q1;
-  if (a == 0.f) return q0;
-  return __fdiv_rn(s, 9.0f);
+  float q;
+  // setp.ne is the ORDERED not-equal (false for NaN); C's != is the unordered one
+  asm("{\n.reg .pred p;\nsetp.ne.f32 p, %1, 0f00000000;\nselp.f32 %0, %2, %3, p;\n}" : "=f"(q) : "f"(r), "f"(q1), "f"(q0));
+  return q;
 }
 
 __global__ void div9_check_kernel(unsigned long long* mismatches, unsigned int* first_bad) {
@@ -214,19 +218,19 @@ __device__ __forceinline__ void load_window(const float* __restrict__ src, int h
 template <bool kDefend, typename Idx>
 __global__ void __launch_bounds__(256, 4)
 smooth3x3_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t planes, int h, int w,
-                 float lm1) {
+                 float lm1, const FastDiv div_groups, const FastDiv div_chunks) {
   __shared__ float tab[kQuantTab];
   const bool use_tab = kDefend && lm1 < (float)kQuantTab;
   if (kDefend) quant_table_init(tab, lm1);
   const int groups = (w + 3) >> 2;                         // 4-wide column groups
   const int row_chunks = (h + kSmoothRows - 1) / kSmoothRows;
-  // Idx = uint32_t whenever the strip count (+ one grid stride) fits 31 bits: two 32-bit divisions per strip instead of
-  // three 64-bit ones (about 80 of the ~620 instructions a strip costs)
+  // Idx = uint32_t whenever the strip count (+ one grid stride) fits 31 bits: the strip index is then split by two
+  // multiply-shift divisions (FastDiv) instead of three 64-bit divisions
   const Idx total = (Idx)(planes * row_chunks * (int64_t)groups);
   for (Idx t = (Idx)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (Idx)gridDim.x * blockDim.x) {
-    const Idx tq = t / (Idx)groups;
+    const Idx tq = fast_div(t, div_groups);
     const int gx = (int)(t - tq * (Idx)groups);
-    const Idx tp = tq / (Idx)row_chunks;
+    const Idx tp = fast_div(tq, div_chunks);
     const int rc = (int)(tq - tp * (Idx)row_chunks);
     const int64_t p = (int64_t)tp;
     const float* src = x + p * (int64_t)h * w;
@@ -462,14 +466,15 @@ __device__ __forceinline__ float med3(float a, float b, float c) {
 }
 template <typename Idx>
 __global__ void __launch_bounds__(256, 4)
-median3x3_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t planes, int h, int w) {
+median3x3_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t planes, int h, int w,
+                 const FastDiv div_groups, const FastDiv div_chunks) {
   const int groups = (w + 3) >> 2;
   const int row_chunks = (h + kSmoothRows - 1) / kSmoothRows;
   const Idx total = (Idx)(planes * row_chunks * (int64_t)groups);      // (32-bit strip index when it fits: see smooth3x3_kernel)
   for (Idx t = (Idx)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (Idx)gridDim.x * blockDim.x) {
-    const Idx tq = t / (Idx)groups;
+    const Idx tq = fast_div(t, div_groups);
     const int gx = (int)(t - tq * (Idx)groups);
-    const Idx tp = tq / (Idx)row_chunks;
+    const Idx tp = fast_div(tq, div_chunks);
     const int rc = (int)(tq - tp * (Idx)row_chunks);
     const int64_t p = (int64_t)tp;
     const float* src = x + p * (int64_t)h * w;
@@ -582,14 +587,15 @@ static int smooth_launch(const float* x, float* out, int64_t planes, int h, int 
   const int64_t total = planes * (int64_t)groups * chunks;
   const int grid = grid_for(total);
   const bool small = total + (int64_t)grid * 256 < (int64_t(1) << 31);
+  const FastDiv dg = make_fastdiv((uint32_t)groups), dc = make_fastdiv((uint32_t)chunks);
   if (defend && small)
-    smooth3x3_kernel<true, uint32_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, (float)(levels - 1));
+    smooth3x3_kernel<true, uint32_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, (float)(levels - 1), dg, dc);
   else if (defend)
-    smooth3x3_kernel<true, int64_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, (float)(levels - 1));
+    smooth3x3_kernel<true, int64_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, (float)(levels - 1), dg, dc);
   else if (small)
-    smooth3x3_kernel<false, uint32_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, 0.f);
+    smooth3x3_kernel<false, uint32_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, 0.f, dg, dc);
   else
-    smooth3x3_kernel<false, int64_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, 0.f);
+    smooth3x3_kernel<false, int64_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, 0.f, dg, dc);
   ADV_LAUNCHED();
   return ADVB200_OK;
 }
@@ -606,10 +612,11 @@ int advb200_median3x3_f32(const float* x, float* out, int64_t planes, int h, int
   const int groups = (w + 3) / 4, chunks = (h + kSmoothRows - 1) / kSmoothRows;
   const int64_t total = planes * (int64_t)groups * chunks;
   const int grid = grid_for(total);
+  const FastDiv dg = make_fastdiv((uint32_t)groups), dc = make_fastdiv((uint32_t)chunks);
   if (total + (int64_t)grid * 256 < (int64_t(1) << 31))
-    median3x3_kernel<uint32_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w);
+    median3x3_kernel<uint32_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, dg, dc);
   else
-    median3x3_kernel<int64_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w);
+    median3x3_kernel<int64_t><<<grid, 256, 0, as_stream(stream)>>>(x, out, planes, h, w, dg, dc);
   ADV_LAUNCHED();
   return ADVB200_OK;
 }

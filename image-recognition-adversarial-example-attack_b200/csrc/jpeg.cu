@@ -129,8 +129,8 @@ __device__ __forceinline__ void codec_block8(uint8_t* blk, int pitch, int* ws, c
     uint2 v = make_uint2(0u, 0u);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      v.x |= (uint32_t)min(max(d[k] + 128, 0), 255) << (8 * k);
-      v.y |= (uint32_t)min(max(d[4 + k] + 128, 0), 255) << (8 * k);
+      v.x |= (uint32_t)__vimin_s32_relu(d[k] + 128, 255) << (8 * k);   // range limit: one VIMNMX.RELU
+      v.y |= (uint32_t)__vimin_s32_relu(d[4 + k] + 128, 255) << (8 * k);
     }
     *reinterpret_cast<uint2*>(blk + l * pitch) = v;
   }
@@ -169,59 +169,126 @@ jpeg_codec_kernel(const float* __restrict__ x, uint8_t* __restrict__ ydec, uint8
     sCrF[r][c] = (uint8_t)((32768 * R - 27439 * G - 5329 * B + (128 << 16) + 32767) >> 16);
   };
   const bool vec = ((w & 3) == 0) && ((reinterpret_cast<uintptr_t>(x) & 15u) == 0);
-  if (vec) {
-    // 16-byte loads, two groups (six loads) in flight per thread; groups wholly past the right edge replicate the
-    // last pixel, which the scalar tail below fills in
-    const int gw = min(kStripW, w - col0) >> 2;                  // whole 4-pixel groups of this strip inside the image
-    for (int i0 = threadIdx.x; i0 < 16 * gw; i0 += 2 * kCodecThreads) {
-      float4 v[2][3];
-      int rr[2], cc[2];
+  // Strips whose 16 rows all lie inside the image (every strip when h % 16 == 0) take the FUSED front end: a thread
+  // converts a 2-row x 4-column patch from six 16-byte loads, keeps the full-resolution chroma in registers, applies
+  // the 2x2 box filter there and writes 8 Y bytes as two words and 2 + 2 chroma samples as two half-words.  No
+  // full-resolution chroma planes in shared memory, no single-byte stores, no second pass, no index divisions; columns
+  // past the image edge are filled only up to the next MCU boundary (nothing beyond it is ever read).  The bottom
+  // strip of other heights keeps the three-stage path below (its chroma rows past the real chroma height replicate a
+  // DIFFERENT row pair than its luma rows do).
+  const bool fused = vec && row0 + 16 <= h;
+  if (fused) {
+    const int wrem = min(kStripW, w - col0);
+    const int gw = wrem >> 2;                                        // 4-pixel groups inside the image
+    const int ng = min(kStripW / 4, ((wrem + 15) >> 4) << 2);        // groups up to the MCU boundary
+    const int cg = threadIdx.x & 63;
+    if (cg < ng) {
+      const int cge = min(cg, gw - 1);                               // groups past the edge re-read the last real group ...
+      const bool rep = cg >= gw;                                     // ... and replicate its last pixel
+      const float* src = xr + (long long)row0 * w + col0 + 4 * cge;
+      const long long pl = (long long)h * w;
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const int i = i0 + u * kCodecThreads;
-        rr[u] = -1;
-        if (i < 16 * gw) {
-          rr[u] = i / gw; cc[u] = (i % gw) * 4;
-          const long long o = (long long)min(row0 + rr[u], h - 1) * w + col0 + cc[u];
-          v[u][0] = __ldg(reinterpret_cast<const float4*>(xr + o));
-          v[u][1] = __ldg(reinterpret_cast<const float4*>(xg + o));
-          v[u][2] = __ldg(reinterpret_cast<const float4*>(xb + o));
+      for (int it = 0; it < 4; it += 2) {                            // two row pairs per pass: twelve loads in flight
+        float4 v[2][2][3];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int rp = (it + u) * 2 + (threadIdx.x >> 6);
+#pragma unroll
+          for (int dr = 0; dr < 2; ++dr)
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+              v[u][dr][c] = __ldg(reinterpret_cast<const float4*>(src + c * pl + (long long)(2 * rp + dr) * w));
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int rp = (it + u) * 2 + (threadIdx.x >> 6);
+          int cb[2][4], cr[2][4];
+#pragma unroll
+          for (int dr = 0; dr < 2; ++dr) {
+            float f[3][4];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+              const float4 q = v[u][dr][c];
+              f[c][0] = rep ? q.w : q.x; f[c][1] = rep ? q.w : q.y; f[c][2] = rep ? q.w : q.z; f[c][3] = q.w;
+            }
+            uint32_t yw = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const int R = to_u8(f[0][k]), G = to_u8(f[1][k]), B = to_u8(f[2][k]);
+              // jccolor.c; all three results lie in 0..255 for R, G, B in 0..255 (the uint8 casts of the staged path
+              // never truncate)
+              yw |= (uint32_t)((19595 * R + 38470 * G + 7471 * B + 32768) >> 16) << (8 * k);
+              cb[dr][k] = (-11059 * R - 21709 * G + 32768 * B + (128 << 16) + 32767) >> 16;
+              cr[dr][k] = (32768 * R - 27439 * G - 5329 * B + (128 << 16) + 32767) >> 16;
+            }
+            *reinterpret_cast<uint32_t*>(&sY[2 * rp + dr][4 * cg]) = yw;
+          }
+          // h2v2 box filter with the alternating 1, 2 bias (jcsample.c): chroma columns 2cg (even) and 2cg + 1 (odd)
+          const uint32_t b0 = (uint32_t)(cb[0][0] + cb[0][1] + cb[1][0] + cb[1][1] + 1) >> 2;
+          const uint32_t b1 = (uint32_t)(cb[0][2] + cb[0][3] + cb[1][2] + cb[1][3] + 2) >> 2;
+          const uint32_t r0 = (uint32_t)(cr[0][0] + cr[0][1] + cr[1][0] + cr[1][1] + 1) >> 2;
+          const uint32_t r1 = (uint32_t)(cr[0][2] + cr[0][3] + cr[1][2] + cr[1][3] + 2) >> 2;
+          *reinterpret_cast<uint16_t*>(&sC[0][rp][2 * cg]) = (uint16_t)(b0 | (b1 << 8));
+          *reinterpret_cast<uint16_t*>(&sC[1][rp][2 * cg]) = (uint16_t)(r0 | (r1 << 8));
         }
       }
-#pragma unroll
-      for (int u = 0; u < 2; ++u)
-        if (rr[u] >= 0) {
-          convert(rr[u], cc[u], v[u][0].x, v[u][1].x, v[u][2].x);
-          convert(rr[u], cc[u] + 1, v[u][0].y, v[u][1].y, v[u][2].y);
-          convert(rr[u], cc[u] + 2, v[u][0].z, v[u][1].z, v[u][2].z);
-          convert(rr[u], cc[u] + 3, v[u][0].w, v[u][1].w, v[u][2].w);
-        }
     }
-    const int done = gw * 4, rest = kStripW - done;              // columns past the image edge (replicated)
-    for (int i = threadIdx.x; i < 16 * rest; i += kCodecThreads) {
-      const int r = i / rest, c = done + i % rest;
-      const long long o = (long long)min(row0 + r, h - 1) * w + (w - 1);
-      convert(r, c, __ldg(xr + o), __ldg(xg + o), __ldg(xb + o));
-    }
+    __syncthreads();
   } else {
-    for (int i = threadIdx.x; i < 16 * kStripW; i += kCodecThreads) {
-      const int r = i / kStripW, c = i % kStripW;
-      const long long o = (long long)min(row0 + r, h - 1) * w + min(col0 + c, w - 1);
-      convert(r, c, __ldg(xr + o), __ldg(xg + o), __ldg(xb + o));
+    if (vec) {
+      // 16-byte loads, two groups (six loads) in flight per thread; groups wholly past the right edge replicate the
+      // last pixel, which the scalar tail below fills in
+      const int gw = min(kStripW, w - col0) >> 2;                  // whole 4-pixel groups of this strip inside the image
+      for (int i0 = threadIdx.x; i0 < 16 * gw; i0 += 2 * kCodecThreads) {
+        float4 v[2][3];
+        int rr[2], cc[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int i = i0 + u * kCodecThreads;
+          rr[u] = -1;
+          if (i < 16 * gw) {
+            rr[u] = i / gw; cc[u] = (i % gw) * 4;
+            const long long o = (long long)min(row0 + rr[u], h - 1) * w + col0 + cc[u];
+            v[u][0] = __ldg(reinterpret_cast<const float4*>(xr + o));
+            v[u][1] = __ldg(reinterpret_cast<const float4*>(xg + o));
+            v[u][2] = __ldg(reinterpret_cast<const float4*>(xb + o));
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+          if (rr[u] >= 0) {
+            convert(rr[u], cc[u], v[u][0].x, v[u][1].x, v[u][2].x);
+            convert(rr[u], cc[u] + 1, v[u][0].y, v[u][1].y, v[u][2].y);
+            convert(rr[u], cc[u] + 2, v[u][0].z, v[u][1].z, v[u][2].z);
+            convert(rr[u], cc[u] + 3, v[u][0].w, v[u][1].w, v[u][2].w);
+          }
+      }
+      const int done = gw * 4, rest = kStripW - done;              // columns past the image edge (replicated)
+      for (int i = threadIdx.x; i < 16 * rest; i += kCodecThreads) {
+        const int r = i / rest, c = done + i % rest;
+        const long long o = (long long)min(row0 + r, h - 1) * w + (w - 1);
+        convert(r, c, __ldg(xr + o), __ldg(xg + o), __ldg(xb + o));
+      }
+    } else {
+      for (int i = threadIdx.x; i < 16 * kStripW; i += kCodecThreads) {
+        const int r = i / kStripW, c = i % kStripW;
+        const long long o = (long long)min(row0 + r, h - 1) * w + min(col0 + c, w - 1);
+        convert(r, c, __ldg(xr + o), __ldg(xg + o), __ldg(xb + o));
+      }
     }
+    __syncthreads();
+    // ---- h2v2 box filter with the alternating 1,2 bias (jcsample.c); chroma rows past the real chroma height
+    //      replicate the last real chroma row (jcprepct.c pads AFTER downsampling)
+    for (int i = threadIdx.x; i < 2 * 8 * (kStripW / 2); i += kCodecThreads) {
+      const int comp = i / (8 * (kStripW / 2)), rr = (i / (kStripW / 2)) % 8, cc = i % (kStripW / 2);
+      const int cr_real = min(mr * 8 + rr, hc - 1) - mr * 8;
+      const uint8_t(*f)[kStripW] = comp ? sCrF : sCbF;
+      const int s = f[2 * cr_real][2 * cc] + f[2 * cr_real][2 * cc + 1] + f[2 * cr_real + 1][2 * cc] +
+                    f[2 * cr_real + 1][2 * cc + 1] + 1 + (cc & 1);
+      sC[comp][rr][cc] = (uint8_t)(s >> 2);
+    }
+    __syncthreads();
   }
-  __syncthreads();
-  // ---- h2v2 box filter with the alternating 1,2 bias (jcsample.c); chroma rows past the real chroma height
-  //      replicate the last real chroma row (jcprepct.c pads AFTER downsampling)
-  for (int i = threadIdx.x; i < 2 * 8 * (kStripW / 2); i += kCodecThreads) {
-    const int comp = i / (8 * (kStripW / 2)), rr = (i / (kStripW / 2)) % 8, cc = i % (kStripW / 2);
-    const int cr_real = min(mr * 8 + rr, hc - 1) - mr * 8;
-    const uint8_t(*f)[kStripW] = comp ? sCrF : sCbF;
-    const int s = f[2 * cr_real][2 * cc] + f[2 * cr_real][2 * cc + 1] + f[2 * cr_real + 1][2 * cc] +
-                  f[2 * cr_real + 1][2 * cc + 1] + 1 + (cc & 1);
-    sC[comp][rr][cc] = (uint8_t)(s >> 2);
-  }
-  __syncthreads();
   // ---- eight lanes per 8x8 block: 64 luma blocks, then 16 + 16 chroma blocks (6 rounds of 16 blocks per CTA)
   {
     const int grp = threadIdx.x >> 3, l = threadIdx.x & 7;
@@ -345,6 +412,83 @@ jpeg_upsample_rgb_kernel(const uint8_t* __restrict__ ydec, const uint8_t* __rest
   }
 }
 
+// Fast path of the second pass for w % 8 == 0 (every ResNet input): one thread per 2 output rows x 8 output columns.
+// The two rows 2rc, 2rc+1 share their nearer chroma row rc, so the three chroma rows rc-1, rc, rc+1 are fetched once
+// (one aligned 4-byte word + the two neighbour bytes per row and component: 18 loads for 16 pixels, where the generic
+// kernel issues 16 single-byte loads for 4), the thread index is split by two multiply-shift divisions, and the Y row
+// arrives as one 8-byte load.  Same integer arithmetic per sample as jpeg_upsample_rgb_kernel, hence the same bits.
+__global__ void __launch_bounds__(256)
+jpeg_upsample_rgb8_kernel(const uint8_t* __restrict__ ydec, const uint8_t* __restrict__ cbdec,
+                          const uint8_t* __restrict__ crdec, float* __restrict__ out, uint32_t total, int h, int w,
+                          const FastDiv div_w8, const FastDiv div_hc) {
+  __shared__ float tab255[256];
+  tab255[threadIdx.x] = __fdiv_rn((float)threadIdx.x, 255.f);
+  __syncthreads();
+  const int hc = (h + 1) >> 1, wc = w >> 1, w8 = w >> 3;
+  const size_t plane = (size_t)h * w, cplane = (size_t)hc * wc;
+  for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < total; i += gridDim.x * 256u) {
+    const uint32_t iq = fast_div(i, div_w8);
+    const int q = (int)(i - iq * (uint32_t)w8);
+    const uint32_t img = fast_div(iq, div_hc);
+    const int rc = (int)(iq - img * (uint32_t)hc);
+    const int j0 = 4 * q;
+    const int jl = max(j0 - 1, 0), jr = min(j0 + 4, wc - 1);           // neighbour columns replicate at the edges
+    const int rows[3] = {max(rc - 1, 0), rc, min(rc + 1, hc - 1)};     // context rows replicate at the edges
+    // c[comp][row][k]: chroma sample of column j0 - 1 + k
+    int c[2][3][6];
+#pragma unroll
+    for (int comp = 0; comp < 2; ++comp) {
+      const uint8_t* base = (comp ? crdec : cbdec) + img * cplane;
+#pragma unroll
+      for (int rr = 0; rr < 3; ++rr) {
+        const uint8_t* row = base + (size_t)rows[rr] * wc;
+        const uint32_t m = *reinterpret_cast<const uint32_t*>(row + j0);
+        c[comp][rr][0] = row[jl];
+        c[comp][rr][1] = m & 0xff; c[comp][rr][2] = (m >> 8) & 0xff; c[comp][rr][3] = (m >> 16) & 0xff; c[comp][rr][4] = m >> 24;
+        c[comp][rr][5] = row[jr];
+      }
+    }
+    const int c0 = 8 * q;
+#pragma unroll
+    for (int par = 0; par < 2; ++par) {
+      const int r = 2 * rc + par;
+      if (r >= h) break;                                                 // odd heights: the last chroma row has one output row
+      const uint2 y8 = *reinterpret_cast<const uint2*>(ydec + (img * (size_t)h + r) * w + c0);
+      int up[2][8];
+#pragma unroll
+      for (int comp = 0; comp < 2; ++comp) {
+        int sc[6];                                                      // jdsample.c colsum: 3 * nearer row + farther row
+#pragma unroll
+        for (int k = 0; k < 6; ++k) sc[k] = 3 * c[comp][1][k] + c[comp][par ? 2 : 0][k];
+#pragma unroll
+        for (int k = 1; k <= 4; ++k) {
+          up[comp][2 * k - 2] = (3 * sc[k] + sc[k - 1] + 8) >> 4;
+          up[comp][2 * k - 1] = (3 * sc[k] + sc[k + 1] + 7) >> 4;
+        }
+      }
+      float rgb[3][8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int y = (int)(((k < 4 ? y8.x : y8.y) >> (8 * (k & 3))) & 0xff);
+        const int xb = up[0][k] - 128, xr = up[1][k] - 128;
+        // jdcolor.c build_ycc_rgb_table / ycc_rgb_convert
+        const int R = y + ((91881 * xr + 32768) >> 16);
+        const int B = y + ((116130 * xb + 32768) >> 16);
+        const int G = y + ((-22554 * xb + 32768 - 46802 * xr) >> 16);
+        rgb[0][k] = tab255[__vimin_s32_relu(R, 255)];                          // ToTensor: div(255)
+        rgb[1][k] = tab255[__vimin_s32_relu(G, 255)];
+        rgb[2][k] = tab255[__vimin_s32_relu(B, 255)];
+      }
+      float* o = out + img * 3 * plane + (size_t)r * w + c0;
+#pragma unroll
+      for (int pl = 0; pl < 3; ++pl) {
+        *reinterpret_cast<float4*>(o + pl * plane) = make_float4(rgb[pl][0], rgb[pl][1], rgb[pl][2], rgb[pl][3]);
+        *reinterpret_cast<float4*>(o + pl * plane + 4) = make_float4(rgb[pl][4], rgb[pl][5], rgb[pl][6], rgb[pl][7]);
+      }
+    }
+  }
+}
+
 int build_tables(int quality, JpegTables* tb) {
   static const uint8_t kLuma[64] = {16, 11, 10, 16, 24,  40,  51,  61,  12, 12, 14, 19, 26,  58,  60,  55,
                                     14, 13, 16, 24, 40,  57,  69,  56,  14, 17, 22, 29, 51,  87,  80,  62,
@@ -400,9 +544,21 @@ int advb200_jpeg_roundtrip_f32(const float* x, float* out, int n_img, int h, int
   cudaStream_t st = as_stream(stream);
   jpeg_codec_kernel<<<(unsigned)ctas, kCodecThreads, 0, st>>>(x, ydec, cbdec, crdec, h, w, strips, mcu_rows, tb);
   ADV_LAUNCHED();
+  const int64_t cap = (int64_t)kNumSMs * 32;
+  // fast path: rows of whole 8-pixel groups, aligned planes, 31-bit thread index
+  const int64_t patches = (int64_t)n_img * hc * (w >> 3);
+  static const bool no_fast = getenv("ADVB200_JPEG_NO_FAST") != nullptr;      // A/B switch for the tests
+  if (!no_fast && (w & 7) == 0 && (reinterpret_cast<uintptr_t>(out) & 15u) == 0 && (reinterpret_cast<uintptr_t>(ydec) & 7u) == 0 &&
+      patches + cap * 256 < (1ll << 31)) {
+    int64_t g8 = (patches + 255) / 256;
+    if (g8 > cap) g8 = cap;
+    jpeg_upsample_rgb8_kernel<<<(unsigned)g8, 256, 0, st>>>(ydec, cbdec, crdec, out, (uint32_t)patches, h, w,
+                                                           make_fastdiv((uint32_t)(w >> 3)), make_fastdiv((uint32_t)hc));
+    ADV_LAUNCHED();
+    return ADVB200_OK;
+  }
   const int64_t quads = (int64_t)n_img * h * ((w + 3) / 4);
   int64_t grid = (quads + 255) / 256;
-  const int64_t cap = (int64_t)kNumSMs * 32;
   if (grid > cap) grid = cap;
   if (quads + grid * 256 < (1ll << 31))
     jpeg_upsample_rgb_kernel<uint32_t><<<(unsigned)grid, 256, 0, st>>>(ydec, cbdec, crdec, out, n_img, h, w);
