@@ -248,7 +248,10 @@ smooth3x3_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t p
 #pragma unroll
       for (int k = 0; k < kSmoothRows + 2; ++k)
 #pragma unroll
-        for (int j = 0; j < 6; ++j) win[k][j] = fminf(fmaxf(win[k][j], 0.f), 1.f);   // clamp(0) = 0: the zero padding survives
+        // one saturating instruction per element instead of two FMNMX: saturate(x) == clamp(x, 0, 1), NaN -> 0 included.
+        // (At most the SIGN of a zero could differ, and that cannot reach the output: a sum is -0 only if all nine taps
+        // are, and the quantiser's table maps both zeros to entry 0 = +0.)
+        for (int j = 0; j < 6; ++j) win[k][j] = __saturatef(win[k][j]);               // saturate(0) = 0: the zero padding survives
     }
 #pragma unroll
     for (int dr = 0; dr < kSmoothRows; ++dr) {
@@ -267,7 +270,9 @@ smooth3x3_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t p
         s = __fadd_rn(s, c[j]); s = __fadd_rn(s, c[j + 1]); s = __fadd_rn(s, c[j + 2]);
         float o = div9(s);
         // (the reference's trailing clamp, defense_experiments.py:217, is the identity on k/(levels-1), k <= levels-1)
-        if (kDefend) o = quant_one_tab(o, lm1, tab, use_tab);
+        // the mean of nine values in [0,1] is in [0,1] (rounded sums of values <= 1 never exceed 9): the quantiser's own
+        // clamp (defense_experiments.py:183) is the identity here and is skipped
+        if (kDefend) o = use_tab ? tab[__float2int_rn(__fmul_rn(o, lm1))] : __fdiv_rn(rintf(__fmul_rn(o, lm1)), lm1);
         o4[j] = o;
       }
       if (vec && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0)) {

@@ -141,13 +141,18 @@ __device__ __forceinline__ int to_u8(float x) {
   return (int)(fminf(fmaxf(x, 0.f), 1.f) * 255.f);
 }
 
-__global__ void __launch_bounds__(kCodecThreads)
+__global__ void __launch_bounds__(kCodecThreads, 8)
 jpeg_codec_kernel(const float* __restrict__ x, uint8_t* __restrict__ ydec, uint8_t* __restrict__ cbdec,
                   uint8_t* __restrict__ crdec, int h, int w, int strips, int mcu_rows, const JpegTables tb) {
-  __shared__ __align__(16) uint8_t sY[16][kStripW];
-  __shared__ __align__(16) uint8_t sCbF[16][kStripW];     // full-resolution chroma of the strip
+  // Row pitches padded by 32 bytes: the eight lanes of a block touch eight consecutive rows at the same column, and with
+  // pitches of 256 / 128 bytes those fell into the same banks (8-way conflict on every block load and store; ncu: 3.5 M
+  // conflict cycles).  With 288 / 160 bytes, row l starts 8 l banks further on and a warp's 256-byte access takes the
+  // minimum of two wavefronts.
+  constexpr int kPitchY = kStripW + 32, kPitchC = kStripW / 2 + 32;
+  __shared__ __align__(16) uint8_t sY[16][kPitchY];
+  __shared__ __align__(16) uint8_t sCbF[16][kStripW];     // full-resolution chroma of the strip (three-stage path only)
   __shared__ __align__(16) uint8_t sCrF[16][kStripW];
-  __shared__ __align__(16) uint8_t sC[2][8][kStripW / 2];  // downsampled, then decoded in place
+  __shared__ __align__(16) uint8_t sC[2][8][kPitchC];      // downsampled, then decoded in place
   __shared__ __align__(16) int sW[(kCodecThreads / 8) * kWsStride];   // per 8-lane group: one block's 64 intermediates
   __shared__ uint16_t sQ[2][64];                            // the tables, indexed by lane (constant memory would serialise)
   __shared__ uint32_t sRecip[2][64];
@@ -296,10 +301,10 @@ jpeg_codec_kernel(const float* __restrict__ x, uint8_t* __restrict__ ydec, uint8
     for (int b = grp; b < 96; b += kCodecThreads / 8) {
       if (b < 64) {
         const int by = b >> 5, bx = b & 31;
-        codec_block8(&sY[by * 8][bx * 8], kStripW, ws, sQ[0], sRecip[0], l, col0 + bx * 8 < w && row0 + by * 8 < h);
+        codec_block8(&sY[by * 8][bx * 8], kPitchY, ws, sQ[0], sRecip[0], l, col0 + bx * 8 < w && row0 + by * 8 < h);
       } else {
         const int comp = (b - 64) >> 4, bx = b & 15;
-        codec_block8(&sC[comp][0][bx * 8], kStripW / 2, ws, sQ[1], sRecip[1], l, (col0 >> 1) + bx * 8 < wc);
+        codec_block8(&sC[comp][0][bx * 8], kPitchC, ws, sQ[1], sRecip[1], l, (col0 >> 1) + bx * 8 < wc);
       }
       __syncwarp();                                  // the group's workspace is reused by its next block
     }
