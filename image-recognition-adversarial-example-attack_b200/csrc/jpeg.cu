@@ -417,6 +417,20 @@ jpeg_upsample_rgb_kernel(const uint8_t* __restrict__ ydec, const uint8_t* __rest
   }
 }
 
+// ToTensor's k / 255 for an integer 0 <= k <= 255, correctly rounded, in registers: k becomes a float through the
+// 2^23 bit pattern (no conversion-pipe instruction), then Markstein's correction as in elementwise.cu::div9 -- with
+// y = RN(1/255), q0 = RN(k y), the remainder r = k - 255 q0 is exact in one FMA and RN(q0 + r y) = RN(k / 255).  All 256
+// values equal __fdiv_rn(k, 255) (checked on the host with fmaf, oracle/check_div9.c, and by the bit-exactness tests).
+// The fast second pass uses it instead of the generic kernel's shared-memory table: its 48 lookups per thread had
+// data-dependent indices, collided in the banks and kept the LSU queue full (ncu: mio-throttle, 2.8 M conflict cycles).
+__device__ __forceinline__ float div255(int k) {
+  const float y = 0.00392156886f;                                   // RN(1/255) = 0x1.010102p-8
+  const float kf = __int_as_float(0x4B000000 | k) - 8388608.0f;
+  const float q0 = __fmul_rn(kf, y);
+  const float r = __fmaf_rn(-255.0f, q0, kf);
+  return __fmaf_rn(r, y, q0);
+}
+
 // Fast path of the second pass for w % 8 == 0 (every ResNet input): one thread per 2 output rows x 8 output columns.
 // The two rows 2rc, 2rc+1 share their nearer chroma row rc, so the three chroma rows rc-1, rc, rc+1 are fetched once
 // (one aligned 4-byte word + the two neighbour bytes per row and component: 18 loads for 16 pixels, where the generic
@@ -426,9 +440,6 @@ __global__ void __launch_bounds__(256)
 jpeg_upsample_rgb8_kernel(const uint8_t* __restrict__ ydec, const uint8_t* __restrict__ cbdec,
                           const uint8_t* __restrict__ crdec, float* __restrict__ out, uint32_t total, int h, int w,
                           const FastDiv div_w8, const FastDiv div_hc) {
-  __shared__ float tab255[256];
-  tab255[threadIdx.x] = __fdiv_rn((float)threadIdx.x, 255.f);
-  __syncthreads();
   const int hc = (h + 1) >> 1, wc = w >> 1, w8 = w >> 3;
   const size_t plane = (size_t)h * w, cplane = (size_t)hc * wc;
   for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < total; i += gridDim.x * 256u) {
@@ -480,9 +491,9 @@ jpeg_upsample_rgb8_kernel(const uint8_t* __restrict__ ydec, const uint8_t* __res
         const int R = y + ((91881 * xr + 32768) >> 16);
         const int B = y + ((116130 * xb + 32768) >> 16);
         const int G = y + ((-22554 * xb + 32768 - 46802 * xr) >> 16);
-        rgb[0][k] = tab255[__vimin_s32_relu(R, 255)];                          // ToTensor: div(255)
-        rgb[1][k] = tab255[__vimin_s32_relu(G, 255)];
-        rgb[2][k] = tab255[__vimin_s32_relu(B, 255)];
+        rgb[0][k] = div255(__vimin_s32_relu(R, 255));                          // ToTensor: div(255)
+        rgb[1][k] = div255(__vimin_s32_relu(G, 255));
+        rgb[2][k] = div255(__vimin_s32_relu(B, 255));
       }
       float* o = out + img * 3 * plane + (size_t)r * w + c0;
 #pragma unroll

@@ -25,5 +25,13 @@ int main(){
       { if ((uint32_t)i < first) first = (uint32_t)i; } }
   }
   printf("mismatches %llu first %08x\n", bad, first);
-  return bad != 0;
+  // jpeg.cu::div255: k / 255 for k = 0..255 by the same correction, y = RN(1/255)
+  int bad255 = 0;
+  const float y255 = 0.00392156886f;
+  for (int k = 0; k < 256; ++k) {
+    const float kf = (float)k, q0 = kf * y255, r = fmaf(-255.0f, q0, kf), q = fmaf(r, y255, q0);
+    if (b(q) != b(kf / 255.0f)) bad255++;
+  }
+  printf("k/255 mismatches %d\n", bad255);
+  return bad != 0 || bad255 != 0;
 }
