@@ -1,6 +1,8 @@
 """Summaries of ncu CSV exports for profiles/ (run here, on files brought back in gpurun_out/):
     python tools/ncu_summarize.py launches <launch-list.csv> <out.csv>      per-kernel-family time shares of a launch list
-    python tools/ncu_summarize.py conv <raw.csv> <out.csv> <traffic.json>   per-launch table + DRAM traffic of the conv family"""
+    python tools/ncu_summarize.py conv <raw.csv> <out.csv> <traffic.json>   per-launch table + DRAM traffic of the conv family
+    python tools/ncu_summarize.py kernels <raw.csv> <out.csv> <out.json>    one row per launch of the HBM-bound update / CW /
+                                                                            defense kernels (tools/defense_pass.py capture)"""
 import csv
 import json
 import re
@@ -70,8 +72,38 @@ def conv(src, dst, traffic_json):
     print(f"{n} conv launches, DRAM read+write {tot / 1e9:.2f} GB per pass, {tot / max(1, n) / 1e6:.1f} MB per launch")
 
 
+KERNEL_COLS = ["Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+               "sm__throughput.avg.pct_of_peak_sustained_elapsed", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+               "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "smsp__inst_executed.sum",
+               "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+               "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
+               "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio",
+               "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum"]
+
+
+def kernels(src, dst_csv, dst_json):
+    rows = list(csv.reader(open(src)))
+    hdr, units = rows[0], rows[1]
+    idx = {h: i for i, h in enumerate(hdr)}
+    cols = [c for c in KERNEL_COLS if c in idx]
+    out = []
+    with open(dst_csv, "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(cols); w.writerow([units[idx[c]] for c in cols])
+        for r in rows[2:]:
+            name = re.sub(r"^void ", "", r[idx["Kernel Name"]]).replace("advb200::<unnamed>::", "").replace("<unnamed>::", "unnamed>::")
+            w.writerow([r[idx[c]] for c in cols])
+            out.append({"name": re.sub(r"\(.*", "", name).replace("unnamed>::", ""),
+                        **{f"{c} [{units[idx[c]]}]": r[idx[c]] for c in cols[1:]}})
+    json.dump({"how": "ncu --set full --clock-control none, one warm launch per kernel at N=256 (tools/defense_pass.py, "
+                      "tools/gpu_defenses.sh); per-launch values", "kernels": out}, open(dst_json, "w"), indent=1)
+    print(f"{len(out)} launches")
+
+
 if __name__ == "__main__":
     if sys.argv[1] == "launches":
         launches(sys.argv[2], sys.argv[3])
+    elif sys.argv[1] == "kernels":
+        kernels(sys.argv[2], sys.argv[3], sys.argv[4])
     else:
         conv(sys.argv[2], sys.argv[3], sys.argv[4])
