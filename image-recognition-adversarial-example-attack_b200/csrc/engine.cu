@@ -108,7 +108,11 @@ inline void apply_force(ConvGemmParams& p) {
 inline TileChoice pick_tile(int gemm_n, long long m_tiles, int ksteps) {
   static const char* force_pair = getenv("ADVB200_PAIR");      // tuning knobs: "0" / "1"
   static const char* force_bn = getenv("ADVB200_BN");
-  if (g_force.bn > 0 && gemm_n % g_force.bn == 0) return TileChoice{g_force.bn, g_force.pair > 0 ? 1 : 0};
+  // a forced BN divides the channel count, or is the 192-column tile whose last column block is partial (the kernel
+  // guards everything per 64-channel sub-tile): 512 channels = 3 blocks, so the 98-unit layer4 launches (1.32 waves of
+  // 74 CTA pairs) become 147 units = 1.99 waves of tiles that are a quarter cheaper
+  if (g_force.bn > 0 && (gemm_n % g_force.bn == 0 || (g_force.bn == 192 && gemm_n >= 256)))
+    return TileChoice{g_force.bn, g_force.pair > 0 ? 1 : 0};
   const int cands[3] = {256, 128, 64};
   TileChoice best{64, 0};
   double best_score = -1;
@@ -169,7 +173,7 @@ int build_pw_ops(std::vector<Op>& ops, const PwSrc* src, int nsrc, Act out, int 
     in_bytes += 2.0 * out.n * lw * lh * src[i].in.c;
   }
   { const TileChoice tcz = pick_tile(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, ksteps); t.bn = tcz.bn; t.pair = tcz.pair; apply_force(p); }
-  p.tiles_c = gemm_n / t.bn;
+  p.tiles_c = cdiv(gemm_n, t.bn);
   p.out_w = lw; p.out_h = lh; p.out_n = out.n; p.cout = gemm_n;
   p.bias = bias; p.relu = relu; p.mask_in = mask; p.mask_out = mask_out;
   p.mask_pixels = (long long)out.n * out.h * out.w;
@@ -214,7 +218,7 @@ int build_pw_s2_ops(std::vector<Op>& ops, Act g_a, const bf16* w1, Act g_sum, co
   p.tiles_w = cdiv(lw, p.bw); p.tiles_h = cdiv(lh, p.bh); p.tiles_n = cdiv(g_x.n, p.bn);
   const int kb1 = g_a.c / 64, kbd = g_sum.c / 64;
   { const TileChoice tcz = pick_tile(gemm_n, 4ll * p.tiles_w * p.tiles_h * p.tiles_n, kb1 + kbd / 4); t.bn = tcz.bn; t.pair = tcz.pair; apply_force(p); }
-  p.tiles_c = gemm_n / t.bn;
+  p.tiles_c = cdiv(gemm_n, t.bn);
   p.out_w = lw; p.out_h = lh; p.out_n = g_x.n; p.cout = gemm_n;
   p.mask_in = mask;
   p.mask_pixels = (long long)g_x.n * g_x.h * g_x.w;
@@ -383,7 +387,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     p.bw = 128; p.bh = 1; p.bn = 1;
     p.tiles_w = (int)((m + 127) / 128); p.tiles_h = 1; p.tiles_n = 1;
     { const TileChoice tcz = pick_tile(gemm_n, p.tiles_w, p.kblocks); t.bn = tcz.bn; t.pair = tcz.pair; apply_force(p); }
-    p.tiles_c = gemm_n / t.bn;
+    p.tiles_c = cdiv(gemm_n, t.bn);
     p.ntaps = 1;
     p.out_w = (int)m; p.out_h = 1; p.out_n = 1;
     p.full_h = 1; p.full_w = (int)m;
@@ -442,7 +446,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     tile_shape(out.w, out.h, p.bw, p.bh, p.bn);
     p.tiles_w = cdiv(out.w, p.bw); p.tiles_h = cdiv(out.h, p.bh); p.tiles_n = cdiv(out.n, p.bn);
     { const TileChoice tcz = pick_tile(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, kk * p.kblocks); t.bn = tcz.bn; t.pair = tcz.pair; apply_force(p); }
-    p.tiles_c = gemm_n / t.bn;
+    p.tiles_c = cdiv(gemm_n, t.bn);
     p.out_w = out.w; p.out_h = out.h; p.out_n = out.n;
     int rc;
     if (stride == 1) {
@@ -485,7 +489,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     tile_shape(out.w, out.h, p.bw, p.bh, p.bn);
     p.tiles_w = cdiv(out.w, p.bw); p.tiles_h = cdiv(out.h, p.bh); p.tiles_n = cdiv(out.n, p.bn);
     { const TileChoice tcz = pick_tile(gemm_n, (long long)p.tiles_w * p.tiles_h * p.tiles_n, kk * p.kblocks); t.bn = tcz.bn; t.pair = tcz.pair; apply_force(p); }
-    p.tiles_c = gemm_n / t.bn;
+    p.tiles_c = cdiv(gemm_n, t.bn);
     p.out_w = out.w; p.out_h = out.h; p.out_n = out.n;
     int rc = make_a(&t.maps.a[0], in, 1, 0, 0, p.bw, p.bh, p.bn);
     if (!rc) rc = make_out_maps(t, out, 1, 0, 0);
@@ -533,7 +537,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
     tile_shape(sw, sh, q.bw, q.bh, q.bn);
     q.tiles_w = cdiv(sw, q.bw); q.tiles_h = cdiv(sh, q.bh); q.tiles_n = cdiv(out.n, q.bn);
     { const TileChoice tcz = pick_tile(gemm_n, 4ll * q.tiles_w * q.tiles_h * q.tiles_n, (q.ntaps * q.kblocks) / 4); t2.bn = tcz.bn; t2.pair = tcz.pair; apply_force(q); }
-    q.tiles_c = gemm_n / t2.bn;
+    q.tiles_c = cdiv(gemm_n, t2.bn);
     q.out_w = sw; q.out_h = sh; q.out_n = out.n;
     q.pix_sub = 2;
     int rc = make_a(&t2.maps.a[0], in, 1, 0, 0, q.bw, q.bh, q.bn);
@@ -564,7 +568,7 @@ int build_tc_ops(std::vector<Op>& ops, const bf16* wpack, int ksize, int stride,
       tile_shape(sw, sh, q.bw, q.bh, q.bn);
       q.tiles_w = cdiv(sw, q.bw); q.tiles_h = cdiv(sh, q.bh); q.tiles_n = cdiv(out.n, q.bn);
       { const TileChoice tcz = pick_tile(gemm_n, (long long)q.tiles_w * q.tiles_h * q.tiles_n, q.ntaps * q.kblocks); t2.bn = tcz.bn; t2.pair = tcz.pair; apply_force(q); }
-      q.tiles_c = gemm_n / t2.bn;
+      q.tiles_c = cdiv(gemm_n, t2.bn);
       q.out_w = sw; q.out_h = sh; q.out_n = out.n;
       q.pix_sub = 2; q.pix_ph = ph; q.pix_pw = pw;
       int rc = make_a(&t2.maps.a[0], in, 1, 0, 0, q.bw, q.bh, q.bn);
@@ -795,8 +799,8 @@ struct Tuner {
       if (halo) {      // halo-mode 3x3: the tile is fixed; only the output path (staging slots / direct stores) is open
         for (int slots : {1, 2, 4}) { TileForce f; f.pair = 0; f.slots = slots; cands.push_back(f); }
       } else
-      for (int bn : {256, 128, 64}) {
-        if (cout % bn || (bn == 64 && cout >= 256)) continue;
+      for (int bn : {256, 192, 128, 64}) {
+        if (bn == 192 ? cout < 512 : (cout % bn || (bn == 64 && cout >= 256))) continue;
         for (int pair = 0; pair < 2; ++pair)
           for (int bres : {-1, 0})
             for (int slots : {1, 2, 4}) { TileForce f; f.bn = bn; f.pair = pair; f.bres = bres; f.slots = slots; cands.push_back(f); }

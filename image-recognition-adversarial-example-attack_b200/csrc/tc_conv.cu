@@ -39,7 +39,8 @@ template <int BN, bool kPair> struct Cfg {
   static constexpr int kBRows = kPair ? BN / 2 : BN;
   static constexpr int kBTileBytes = kBRows * kBlockK * 2;
   static constexpr int kStageBytes = kATileBytes + kBTileBytes;
-  static constexpr int kTmemCols = (2 * BN < 32) ? 32 : 2 * BN;  // two accumulators
+  // two accumulators; tcgen05.alloc takes a power of two >= 32 (BN = 192: 384 -> 512)
+  static constexpr int kTmemCols = 2 * BN <= 32 ? 32 : 2 * BN <= 64 ? 64 : 2 * BN <= 128 ? 128 : 2 * BN <= 256 ? 256 : 512;
 };
 
 // ---------------------------------------------------------------- PTX wrappers
@@ -384,7 +385,11 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
   if (warp >= kEpiWarp0 && p.bias && BN != 16) {
     // folded-BN shift of the first tile's column block (accumulator 0's copy)
     const int i = threadIdx.x - kEpiWarp0 * 32;
-    if (i < BN && tile0 < total_tiles) bias_smem[i] = __ldg(p.bias + tile_coord<kPair>(p, tile0, BN, rank).c0 + i);
+    // (BN = 192 leaves the last column block partial: channels >= cout have no shift, no masks and are never stored)
+    if (i < BN && tile0 < total_tiles) {
+      const int ch = tile_coord<kPair>(p, tile0, BN, rank).c0 + i;
+      bias_smem[i] = ch < p.cout ? __ldg(p.bias + ch) : 0.f;
+    }
   }
   if (warp >= kEpiWarp0 && p.has_add) {
     // identity operand for the residual k-steps: I[n][k] = (n == k), rows of 128 B, 16-byte chunks
@@ -778,7 +783,8 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
         const long long px2 = ((long long)n2 * p.full_h + (h2 * p.pix_sub + ph2)) * p.full_w + (w2 * p.pix_sub + pw2);
         const long long m0 = ((long long)(t2.c0 >> 6) * p.mask_pixels + px2) * 2 + half;
 #pragma unroll
-        for (int j = 0; j < kSub; ++j) mw[j] = ok ? __ldg(p.mask_in + m0 + (long long)j * p.mask_pixels * 2) : 0u;
+        for (int j = 0; j < kSub; ++j)
+          mw[j] = (ok && t2.c0 + 64 * j < p.cout) ? __ldg(p.mask_in + m0 + (long long)j * p.mask_pixels * 2) : 0u;
       };
       uint32_t mnext[kSub];
 #pragma unroll
@@ -798,8 +804,10 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
         // shift copy that slower warps still read for the previous tile (found by the candidate-equivalence test)
         if (n_out_slots == 0 && has_bias) epi_bar();
         // folded-BN shift of the NEXT tile goes to the other accumulator's copy
-        if (has_bias && etid < BN && tile + tile_step < total_tiles)
-          bias_smem[(acc ^ 1) * 256 + etid] = __ldg(p.bias + tile_coord<kPair>(p, tile + tile_step, BN, rank).c0 + etid);
+        if (has_bias && etid < BN && tile + tile_step < total_tiles) {
+          const int ch = tile_coord<kPair>(p, tile + tile_step, BN, rank).c0 + etid;
+          bias_smem[(acc ^ 1) * 256 + etid] = ch < p.cout ? __ldg(p.bias + ch) : 0.f;
+        }
         uint32_t mword[kSub];
 #pragma unroll
         for (int j = 0; j < kSub; ++j) mword[j] = mnext[j];
@@ -837,7 +845,7 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
             uint32_t bits = 0;
 #pragma unroll
             for (int i = 0; i < 32; ++i) bits |= (f[i] > 0.f ? 1u : 0u) << i;
-            if (valid) p.mask_out[mword0 + (long long)j * p.mask_pixels * 2] = bits;
+            if (valid && tc.c0 + 64 * j < p.cout) p.mask_out[mword0 + (long long)j * p.mask_pixels * 2] = bits;
           }
           if (has_mask_in) {
             const uint32_t mw = mword[j];
@@ -859,7 +867,7 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           if (n_out_slots == 0) {
             // direct mode: this thread's 32 channels (64 contiguous bytes of its pixel) go straight to global
             // memory — no staging tile, no barrier, and the smem goes to the operand ring instead
-            if (valid) {
+            if (valid && tc.c0 + 64 * j < p.cout) {
               uint4* gp = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + pixel * p.cout + tc.c0 + 64 * j + half * 32);
 #pragma unroll
               for (int i = 0; i < 4; ++i) gp[i] = o[i];
@@ -871,7 +879,8 @@ conv_gemm_kernel(const __grid_constant__ ConvGemmMaps maps, const __grid_constan
           fence_async_smem();          // generic-proxy smem writes -> visible to the TMA store
           epi_bar();
           if (leader) {
-            tma_store_4d(&maps.out[tc.cls], out_smem + oslot * kSubTileBytes, tc.c0 + 64 * j, tc.w0, tc.h0, tc.n0);
+            if (tc.c0 + 64 * j < p.cout)
+              tma_store_4d(&maps.out[tc.cls], out_smem + oslot * kSubTileBytes, tc.c0 + 64 * j, tc.w0, tc.h0, tc.n0);
             bulk_commit();
             // n staging slots: before the next barrier all but the newest (n - 2) stores must have
             // finished reading their slot
@@ -952,7 +961,7 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
   // activations stream through the ring: halves the L2 -> SM traffic of the wide 1x1 layers
   static const char* no_bres = getenv("ADVB200_NO_BRES");
   p.bres = 0;
-  if (!p.halo && !no_bres && BN != 16 && !p.bres_off) {
+  if (!p.halo && !no_bres && BN != 16 && !p.bres_off && p.cout % BN == 0) {
     const int res_bytes = p.ksteps * C::kBTileBytes;
     const int slots = p.out_slots == 4 && res_bytes > 64 * 1024 ? 2 : p.out_slots;
     const int ring_room = kSmemBudget - Smem<BN>::fixed_bytes(slots) - res_bytes;
@@ -1378,6 +1387,7 @@ int launch_conv_gemm(int bn_cols, int pair, const ConvGemmMaps& maps, ConvGemmPa
     case 16: return launch_impl<16, false>(maps, p, stream);
     case 64: return pair ? launch_impl<64, true>(maps, p, stream) : launch_impl<64, false>(maps, p, stream);
     case 128: return pair ? launch_impl<128, true>(maps, p, stream) : launch_impl<128, false>(maps, p, stream);
+    case 192: return pair ? launch_impl<192, true>(maps, p, stream) : launch_impl<192, false>(maps, p, stream);
     case 256: return pair ? launch_impl<256, true>(maps, p, stream) : launch_impl<256, false>(maps, p, stream);
     default: return fail(ADVB200_ERR_ARG, "conv_gemm: BN must be 16, 64, 128 or 256");
   }
