@@ -50,7 +50,8 @@ def conv(src, dst, traffic_json):
     keep = ["Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
             "sm__ops_path_tensor_op_utchmma_src_bf16_dst_fp32.sum.pct_of_peak_sustained_elapsed" if False else None,
             "sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_elapsed", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
-            "lts__t_sectors_srcunit_tex_op_read.sum", "l1tex__m_xbar2l1tex_read_bytes.sum", "smsp__inst_executed.sum"]
+            "lts__t_sectors_srcunit_tex_op_read.sum", "l1tex__m_xbar2l1tex_read_bytes.sum", "smsp__inst_executed.sum",
+            "sm__ops_path_tensor_op_utchmma_src_bf16_dst_fp32_sparsity_off.avg.pct_of_peak_sustained_elapsed"]
     keep = [k for k in keep if k and k in idx]
     tensor_cols = [h for h in hdr if "utchmma" in h or "tensor" in h and "pct_of_peak" in h][:4]
     cols = keep + [c for c in tensor_cols if c not in keep]
@@ -70,6 +71,12 @@ def conv(src, dst, traffic_json):
     json.dump({"source": f"{dst} (ncu --set full --clock-control none, one forward + input-gradient pass at batch 256; caches flushed per launch by ncu)",
                "launches": n, "dram_bytes_read_plus_write_total": tot, "dram_bytes_per_launch": tot / max(1, n)}, open(traffic_json, "w"), indent=1)
     print(f"{n} conv launches, DRAM read+write {tot / 1e9:.2f} GB per pass, {tot / max(1, n) / 1e6:.1f} MB per launch")
+    tcol = "sm__ops_path_tensor_op_utchmma_src_bf16_dst_fp32_sparsity_off.avg.pct_of_peak_sustained_elapsed"
+    if tcol in idx:
+        sel = [r for r in rows[2:] if "conv_gemm" in r[idx["Kernel Name"]] or "fused_block" in r[idx["Kernel Name"]]]
+        tt = sum(float(r[idx["gpu__time_duration.sum"]]) for r in sel)
+        print("time-weighted bf16 tensor-op (UTCHMMA) rate: %.1f %% of peak over %.0f us" % (
+            sum(float(r[idx["gpu__time_duration.sum"]]) * float(r[idx[tcol]]) for r in sel) / tt, tt))
 
 
 KERNEL_COLS = ["Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
