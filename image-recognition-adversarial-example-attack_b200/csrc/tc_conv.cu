@@ -307,8 +307,21 @@ __device__ __forceinline__ TileCoord tile_coord(const ConvGemmParams& p, int til
   const int tc = tile - q * p.tiles_c; tile = q;
   t.cls = 0;
   if (p.nclass > 1) {
-    t.cls = (int)(((unsigned long long)(unsigned)tile * p.magic_cls) >> 40);
-    tile -= t.cls * p.units_per_class;
+    // The four parity classes of one pixel tile are CONSECUTIVE units (class-minor order), so they run at the same time
+    // on neighbouring SMs and share the gradient tile they all read through the L2.  In class-major order every class
+    // swept the whole tensor on its own and it came from DRAM four times (ncu, bwd l2.0.c2: 212 MB read against 64 MB
+    // algorithmic).  The classes cost 1 / 2 / 2 / 4 taps; with a grid that is a multiple of four a CTA would always draw
+    // the same class, hence the rotation by the pixel-tile index.
+    // Launches of only a few waves keep the class-major order: there the unequal classes inside ONE wave cost more than
+    // the re-reads (layer 4: +4 / +6 us when interleaved), and their gradient tensor stays in the L2 anyway.
+    if (p.cls_minor) {
+      const int pix = tile >> 2;
+      t.cls = (tile + pix) & 3;
+      tile = pix;
+    } else {
+      t.cls = (int)(((unsigned long long)(unsigned)tile * p.magic_cls) >> 40);
+      tile -= t.cls * p.units_per_class;
+    }
   }
   if (kPair) tile = 2 * tile + rank;
   q = (int)(((unsigned long long)(unsigned)tile * p.magic_w) >> 40);
@@ -935,7 +948,7 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
     p.ksteps = p.ntaps * p.kblocks;
   }
   if (nclass > 1) {
-    ADV_CHECK_ARG(!p.halo && nclass <= 4, "conv_gemm: multi-class launches are generic-mode, at most 4 classes");
+    ADV_CHECK_ARG(!p.halo && nclass == 4, "conv_gemm: multi-class launches are generic-mode with the 4 parity classes of a stride-2 gradient");
     p.bres_off = 1;                          // classes have different weights: no resident-weight mode
     p.ksteps = 0;
     for (int c = 0; c < nclass; ++c) {
@@ -956,6 +969,8 @@ int launch_impl(const ConvGemmMaps& maps, ConvGemmParams& p, cudaStream_t stream
   static const char* force_slots = getenv("ADVB200_OUT_SLOTS");   // tuning knob
   p.out_slots = p.slots_req == 1 ? 0 : p.slots_req ? p.slots_req : force_slots ? atoi(force_slots) : (p.ksteps >= 8 ? 2 : 4);
   int units = kPair ? kNumSMs / 2 : kNumSMs;            // CTAs or CTA pairs
+  static const char* cls_env = getenv("ADVB200_CLS_ORDER");   // A/B knob: "major" / "minor" force one order
+  p.cls_minor = nclass > 1 && (cls_env ? cls_env[1] == 'i' : total >= 8ll * units);   // interleave only in many-wave launches
   // resident-weight mode (pointwise convs): when all k-blocks of one column block fit beside a >= 3-deep ring of
   // A tiles, each CTA keeps one column block for all of its tiles (tile stride = multiple of tiles_c) and only
   // activations stream through the ring: halves the L2 -> SM traffic of the wide 1x1 layers

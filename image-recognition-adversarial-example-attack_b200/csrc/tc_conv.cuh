@@ -34,13 +34,15 @@ struct ConvGemmParams {
   int tap_bmap[kMaxTaps];
   int ksteps;
   int has_b2;
-  // multi-class launches (stride-2 input gradients): the output splits into nclass (<= 4) parity classes of equal
-  // tile count; class c owns taps [cls_tap0[c], cls_tap0[c] + cls_ntaps[c]) (cls_ksteps[c] k-steps), writes the
+  // multi-class launches (stride-2 input gradients): the output splits into its 4 parity classes of equal tile count
+  // (many-wave launches: unit index -> pixel tile = index / 4, class = (index + pixel tile) % 4, so the classes of a pixel
+  // tile run side by side and share their input through the L2; few-wave launches: class-major); class c owns taps [cls_tap0[c], cls_tap0[c] + cls_ntaps[c]) (cls_ksteps[c] k-steps), writes the
   // (cls_ph[c], cls_pw[c]) sub-lattice of the output through maps.out[c].  nclass <= 1: a plain launch.
   int nclass;
   int cls_tap0[4], cls_ntaps[4], cls_ksteps[4], cls_ph[4], cls_pw[4];
   int units_per_class;            // tiles (or CTA-pair tiles) of one class and column block (launcher-filled)
   unsigned long long magic_cls;
+  int cls_minor;                  // launcher-filled: 1 = class-minor unit order (>= 8 waves), 0 = class-major
   // halo mode (kblocks == 1, tiles_c == 1): ONE TMA box of (bw+halo) x (bh+halo) input pixels per tile
   // serves every tap — tap t reads the rows starting at tap_row[t], 8-row groups sbo_rows rows apart
   // (tcgen05 applies the 128B swizzle to absolute smem addresses, so row-shifted descriptors are legal;
