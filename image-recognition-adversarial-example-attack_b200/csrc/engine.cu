@@ -113,6 +113,9 @@ inline TileChoice pick_tile(int gemm_n, long long m_tiles, int ksteps) {
   // 74 CTA pairs) become 147 units = 1.99 waves of tiles that are a quarter cheaper
   if (g_force.bn > 0 && (gemm_n % g_force.bn == 0 || (g_force.bn == 192 && gemm_n >= 256)))
     return TileChoice{g_force.bn, g_force.pair > 0 ? 1 : 0};
+  // ADVB200_BN=192 (test / tuning knob): the 192-column tile wherever the autotuner would consider it
+  if (force_bn && atoi(force_bn) == 192 && gemm_n >= 512)
+    return TileChoice{192, force_pair ? atoi(force_pair) : (ksteps >= 16 ? 1 : 0)};
   const int cands[3] = {256, 128, 64};
   TileChoice best{64, 0};
   double best_score = -1;

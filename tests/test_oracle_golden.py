@@ -235,3 +235,20 @@ def test_launch_by_launch_oracle_reproduces_the_autograd_emulator(cond_model, pr
     rel, bad = trace_ref.compare(w["grad"], grad, precision == "bf16")
     assert bad == 0
     assert trace_ref.canonical("bwd l2.0.c2/*") == "bwd l2.0.c2" and trace_ref.canonical("bwd l3.0.c1+ds/3") == "bwd l3.0.c1+ds"
+
+
+def test_exact_constant_divisions_host_checker(tmp_path):
+    """oracle/check_div9.c: the branch-free s/9 of the smoothing kernels against IEEE division for ALL 2^32 floats, and the
+    k/255 of the JPEG second pass for all 256 k, with C's correctly rounded fmaf (the device-side twin is
+    advb200_test_div9 in the GPU suite).  About half a minute on 8 cores."""
+    import shutil
+    import subprocess
+    from pathlib import Path
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    exe = tmp_path / "check_div9"
+    src = Path(__file__).resolve().parent.parent / "oracle" / "check_div9.c"
+    subprocess.run(["gcc", "-O2", "-mfma", "-fopenmp", "-ffp-contract=off", str(src), "-o", str(exe), "-lm"], check=True)
+    r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=1200)
+    assert r.returncode == 0, r.stdout
+    assert "mismatches 0 " in r.stdout and "k/255 mismatches 0" in r.stdout
